@@ -1,0 +1,120 @@
+"""CPU ops (ctypes over libdmlp_cpu.so): oracle, strategies, parser, generator."""
+import ctypes as C
+
+import numpy as np
+
+from .._native import cpu_lib
+
+_d = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_i = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_u = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+
+_ready = False
+
+
+def _lib():
+    global _ready
+    lib = cpu_lib()
+    if not _ready:
+        lib.dmlp_cpu_last_error.restype = C.c_char_p
+        lib.dmlp_cpu_knn.argtypes = [_d, _i, C.c_int64, _d, _i, C.c_int64, C.c_int, C.c_char_p,
+                                     C.c_int, C.c_int, C.c_int, C.c_int, _i, _u, _i, _d]
+        lib.dmlp_exact_sqdist.argtypes = [_d, _d, C.c_int]
+        lib.dmlp_exact_sqdist.restype = C.c_double
+        lib.dmlp_result_checksum.argtypes = [C.c_int, _i, C.c_int64]
+        lib.dmlp_result_checksum.restype = C.c_uint64
+        lib.dmlp_merge_topk.argtypes = [_d, _i, _d, _i, C.c_int, _d, _i]
+        lib.dmlp_parse_header.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int64),
+                                          C.POINTER(C.c_int64), C.POINTER(C.c_int)]
+        lib.dmlp_parse_text.argtypes = [C.c_char_p, C.c_size_t, C.c_int, _d, _i, _d, _i]
+        lib.dmlp_synth_fill.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_int,
+                                        C.c_int, C.c_int, C.c_uint64, _d, _i, _d, _i]
+        lib.dmlp_choose_grid.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        lib.dmlp_block_begin.argtypes = [C.c_int64, C.c_int, C.c_int]
+        lib.dmlp_block_begin.restype = C.c_int64
+        lib.dmlp_block_count.argtypes = [C.c_int64, C.c_int, C.c_int]
+        lib.dmlp_block_count.restype = C.c_int64
+        _ready = True
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError(_lib().dmlp_cpu_last_error().decode())
+
+
+def knn(data, labels, queries, k, strategy="serial", ranks=1, rows=0, cols=0, threads=0):
+    """Run the whole job on the CPU.  Returns (label[q], checksum[q], ids, dist, offsets)."""
+    data = np.ascontiguousarray(data, dtype=np.float64)
+    queries = np.ascontiguousarray(queries, dtype=np.float64)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    k = np.ascontiguousarray(k, dtype=np.int32)
+    n, q = data.shape[0], queries.shape[0]
+    a = data.shape[1] if data.ndim == 2 else queries.shape[1]
+    off = np.zeros(q + 1, dtype=np.int64)
+    np.cumsum(np.maximum(k, 0), out=off[1:])
+    out_label = np.empty(q, dtype=np.int32)
+    out_sum = np.empty(q, dtype=np.uint64)
+    out_ids = np.empty(int(off[-1]), dtype=np.int32)
+    out_dist = np.empty(int(off[-1]), dtype=np.float64)
+    _check(_lib().dmlp_cpu_knn(data.reshape(-1), labels, n, queries.reshape(-1), k, q, a,
+                               strategy.encode(), ranks, rows, cols, threads,
+                               out_label, out_sum, out_ids, out_dist))
+    return out_label, out_sum, out_ids, out_dist, off
+
+
+def exact_sqdist(a, b):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    return _lib().dmlp_exact_sqdist(a, b, a.shape[0])
+
+
+def result_checksum(label, ids):
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    return int(_lib().dmlp_result_checksum(int(label), ids, ids.shape[0]))
+
+
+def merge_topk(xd, xi, yd, yi):
+    k = len(xd)
+    od, oi = np.empty(k, np.float64), np.empty(k, np.int32)
+    _lib().dmlp_merge_topk(np.ascontiguousarray(xd, np.float64), np.ascontiguousarray(xi, np.int32),
+                           np.ascontiguousarray(yd, np.float64), np.ascontiguousarray(yi, np.int32), k, od, oi)
+    return od, oi
+
+
+def parse_text(text, threads=0):
+    """Parse the reference text grammar.  Returns (data, labels, queries, k)."""
+    if isinstance(text, str):
+        text = text.encode()
+    n, q, a = C.c_int64(), C.c_int64(), C.c_int()
+    _check(_lib().dmlp_parse_header(text, len(text), C.byref(n), C.byref(q), C.byref(a)))
+    data = np.empty((n.value, a.value), np.float64)
+    labels = np.empty(n.value, np.int32)
+    queries = np.empty((q.value, a.value), np.float64)
+    k = np.empty(q.value, np.int32)
+    _check(_lib().dmlp_parse_text(text, len(text), threads, data.reshape(-1), labels,
+                                  queries.reshape(-1), k))
+    return data, labels, queries, k
+
+
+def synth(n, q, a, lo=-100.0, hi=100.0, min_k=1, max_k=1, num_labels=2, seed=42):
+    """Host twin of the device fill kernel.  Returns (data, labels, queries, k)."""
+    data = np.empty((n, a), np.float64)
+    labels = np.empty(n, np.int32)
+    queries = np.empty((q, a), np.float64)
+    k = np.empty(q, np.int32)
+    _check(_lib().dmlp_synth_fill(n, q, a, lo, hi, min_k, max_k, num_labels, seed,
+                                  data.reshape(-1), labels, queries.reshape(-1), k))
+    return data, labels, queries, k
+
+
+def choose_grid(ranks):
+    r, c = C.c_int(), C.c_int()
+    _lib().dmlp_choose_grid(ranks, C.byref(r), C.byref(c))
+    return r.value, c.value
+
+
+def block_range(total, parts, p):
+    lib = _lib()
+    b = lib.dmlp_block_begin(total, parts, p)
+    return int(b), int(b + lib.dmlp_block_count(total, parts, p))

@@ -1,0 +1,68 @@
+// Public entry point of the k-NN engine.
+//
+// `Engine::KNN` keeps the reference signature (reference: engine.h:6-12) so the
+// fixed driver contract -- parse on the root, call KNN once, one reportResult per
+// query -- carries over unchanged.  `KNNFlat` is the native form of the same call:
+// it takes flat, ideally page-locked, arrays and can hand the results back in a
+// ResultSet instead of printing them.
+#ifndef DMLP_ENGINE_H_
+#define DMLP_ENGINE_H_
+
+#include <string>
+#include <vector>
+
+#include "common.h"
+#include "dmlp/cpu.h"
+#include "dmlp/views.h"
+
+namespace dmlp {
+
+/// Which implementation runs the job.
+enum class Backend {
+  kAuto,        ///< fused GPU path when a CUDA device is visible, else CPU
+  kCpu,         ///< CPU strategies of include/dmlp/cpu.h
+  kGpuFused,    ///< sm_100a pipeline: tcgen05 filter GEMM + fused top-k + exact re-rank
+  kGpuExact,    ///< sm_100a direct fp64 brute force (small problems, any k)
+};
+
+/// Run-time configuration.  `from_env()` reads
+///   DMLP_BACKEND  = auto | cpu | gpu | gpu_exact
+///   DMLP_STRATEGY = serial | grid | gather | tree | farm | kdtree   (CPU backend)
+///   DMLP_RANKS    = number of emulated ranks for the CPU strategies
+///   DMLP_GRID     = RxC grid shape (data shards x query shards)
+///   DMLP_NGPU     = number of GPUs to use (default: all visible)
+///   DMLP_THREADS  = host worker threads
+///   DMLP_TRACE    = 1 prints per-phase device timings on stderr
+struct EngineConfig {
+  Backend backend = Backend::kAuto;
+  CpuOptions cpu;
+  int ngpu = 0;
+  int grid_rows = 0, grid_cols = 0;
+  bool trace = false;
+  static EngineConfig from_env();
+};
+
+}  // namespace dmlp
+
+class Engine {
+ public:
+  /// Present in the reference's class and unused there too (engine.h:8).
+  std::vector<DataPoint> dataPoint;
+
+  /// Settings for this engine instance; defaults come from the environment.
+  dmlp::EngineConfig config = dmlp::EngineConfig::from_env();
+
+  /// Reference-compatible call: classify every query against the dataset and
+  /// report each result exactly once through reportResult().
+  void KNN(Params &p, std::vector<DataPoint> &dataset, std::vector<Query> &queries);
+
+  /// Native call on flat arrays.  With `out == nullptr` results go to
+  /// reportResult(); otherwise they are stored in `*out` and nothing is printed.
+  void KNNFlat(const dmlp::DatasetView &data, const dmlp::QueryView &queries,
+               dmlp::ResultSet *out = nullptr);
+
+  /// Name of the backend the last call actually used ("cpu:serial", "gpu:fused", ...).
+  std::string last_backend;
+};
+
+#endif  // DMLP_ENGINE_H_

@@ -1,0 +1,119 @@
+// C ABI over the CPU backends and the loader.  See include/dmlp_cpu.h.
+#include "dmlp_cpu.h"
+
+#include <cstring>
+#include <cstdio>
+#include <exception>
+#include <stdexcept>
+#include <vector>
+#include <string>
+
+#include "dmlp/cpu.h"
+#include "dmlp/io.h"
+
+namespace {
+thread_local std::string g_err;
+template <class F>
+int guarded(F &&f) {
+  try { f(); return 0; }
+  catch (const std::exception &e) { g_err = e.what(); return -1; }
+  catch (...) { g_err = "unknown error"; return -1; }
+}
+// A Problem that borrows caller memory: allocator hands out the caller's
+// arrays in the order Problem::resize asks for them and never frees.
+thread_local void *g_borrow[4];
+thread_local int g_borrow_next;
+dmlp::HostAllocator borrowing_allocator() {
+  dmlp::HostAllocator a;
+  a.alloc = [](size_t) -> void * { return g_borrow[g_borrow_next++ & 3]; };
+  a.release = [](void *) {};
+  return a;
+}
+}  // namespace
+
+extern "C" {
+
+const char *dmlp_cpu_last_error(void) { return g_err.c_str(); }
+
+int dmlp_cpu_knn(const double *data_attrs, const int *data_labels, int64_t n,
+                 const double *query_attrs, const int *query_k, int64_t q, int a,
+                 const char *strategy, int ranks, int rows, int cols, int threads,
+                 int *out_label, uint64_t *out_checksum, int *out_ids, double *out_dist) {
+  return guarded([&] {
+    dmlp::DatasetView d; d.n = n; d.a = a; d.attrs = data_attrs; d.labels = data_labels;
+    dmlp::QueryView qv; qv.q = q; qv.a = a; qv.attrs = query_attrs; qv.k = query_k;
+    dmlp::CpuOptions opt;
+    if (!dmlp::parse_strategy(strategy ? strategy : "serial", &opt.strategy))
+      throw std::invalid_argument(std::string("unknown strategy: ") + strategy);
+    opt.ranks = ranks; opt.rows = rows; opt.cols = cols; opt.threads = threads;
+    dmlp::ResultSet rs;
+    dmlp::knn_cpu(d, qv, opt, &rs);
+    if (out_label) std::memcpy(out_label, rs.label.data(), sizeof(int) * size_t(q));
+    if (out_checksum) std::memcpy(out_checksum, rs.checksum.data(), sizeof(uint64_t) * size_t(q));
+    if (out_ids) std::memcpy(out_ids, rs.ids.data(), sizeof(int) * rs.ids.size());
+    if (out_dist) std::memcpy(out_dist, rs.dist.data(), sizeof(double) * rs.dist.size());
+  });
+}
+
+double dmlp_exact_sqdist(const double *a, const double *b, int dim) {
+  return dmlp::exact_sqdist(a, b, dim);
+}
+
+uint64_t dmlp_result_checksum(int label, const int *ids, int64_t k) {
+  return dmlp::result_checksum(label, ids, k);
+}
+
+void dmlp_merge_topk(const double *xd, const int *xi, const double *yd, const int *yi, int k,
+                     double *od, int *oi) {
+  const size_t kk = static_cast<size_t>(k);
+  std::vector<dmlp::Neighbor> x(kk), y(kk), o(kk);
+  for (int i = 0; i < k; ++i) { x[i] = {xd[i], xi[i], 0}; y[i] = {yd[i], yi[i], 0}; }
+  dmlp::merge_topk(x.data(), y.data(), k, o.data());
+  for (int i = 0; i < k; ++i) { od[i] = o[i].dist; oi[i] = o[i].id; }
+}
+
+int dmlp_parse_header(const char *text, size_t len, int64_t *n, int64_t *q, int *a) {
+  return guarded([&] {
+    long long nn = 0, qq = 0; int aa = 0;
+    std::string head(text, len < 256 ? len : 256);
+    if (std::sscanf(head.c_str(), "%lld %lld %d", &nn, &qq, &aa) != 3)
+      throw std::runtime_error("malformed header line");
+    *n = nn; *q = qq; *a = aa;
+  });
+}
+
+int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attrs, int *data_labels,
+                    double *query_attrs, int *query_k) {
+  return guarded([&] {
+    g_borrow[0] = data_attrs; g_borrow[1] = data_labels;
+    g_borrow[2] = query_attrs; g_borrow[3] = query_k;
+    g_borrow_next = 0;
+    dmlp::Problem p(borrowing_allocator());
+    dmlp::parse_problem(text, len, threads, &p);
+  });
+}
+
+int dmlp_synth_fill(int64_t n, int64_t q, int a, double lo, double hi, int min_k, int max_k,
+                    int num_labels, uint64_t seed, double *data_attrs, int *data_labels,
+                    double *query_attrs, int *query_k) {
+  return guarded([&] {
+    g_borrow[0] = data_attrs; g_borrow[1] = data_labels;
+    g_borrow[2] = query_attrs; g_borrow[3] = query_k;
+    g_borrow_next = 0;
+    dmlp::Problem p(borrowing_allocator());
+    dmlp::SynthSpec s;
+    s.n = n; s.q = q; s.a = a; s.lo = lo; s.hi = hi; s.min_k = min_k; s.max_k = max_k;
+    s.num_labels = num_labels; s.seed = seed;
+    dmlp::synth_problem(s, &p);
+  });
+}
+
+void dmlp_choose_grid(int ranks, int *rows, int *cols) { dmlp::choose_grid(ranks, rows, cols); }
+int64_t dmlp_block_begin(int64_t total, int parts, int p) {
+  return dmlp::BlockPartition{total, parts}.begin(p);
+}
+int64_t dmlp_block_count(int64_t total, int parts, int p) {
+  return dmlp::BlockPartition{total, parts}.count(p);
+}
+
+}  // extern "C"

@@ -1,0 +1,395 @@
+// CPU backends (oracle + multi-"rank" strategies).  See include/dmlp/cpu.h.
+//
+// Build note: this file must be compiled with -ffp-contract=off so that the
+// distance loop keeps the reference's mul-then-add rounding.
+#include "dmlp/cpu.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <stdexcept>
+#include <thread>
+
+namespace dmlp {
+
+// ---------------------------------------------------------------------------
+// small shared helpers
+// ---------------------------------------------------------------------------
+
+int vote_label(const Neighbor *nb, int64_t k) {
+  std::vector<int> labels;
+  labels.reserve(static_cast<size_t>(k));
+  for (int64_t i = 0; i < k; ++i)
+    if (nb[i].id >= 0) labels.push_back(nb[i].label);
+  if (labels.empty()) return -1;
+  std::sort(labels.begin(), labels.end());
+  int best = labels[0], best_count = 0;
+  size_t i = 0;
+  while (i < labels.size()) {
+    size_t j = i;
+    while (j < labels.size() && labels[j] == labels[i]) ++j;
+    int count = static_cast<int>(j - i);
+    if (count >= best_count) {  // ascending scan + ">=" => larger label wins ties
+      best_count = count;
+      best = labels[i];
+    }
+    i = j;
+  }
+  return best;
+}
+
+void choose_grid(int ranks, int *rows, int *cols) {
+  if (ranks < 1) ranks = 1;
+  int c = 1;
+  for (int d = 1; d * d <= ranks; ++d)
+    if (ranks % d == 0) c = d;
+  *cols = c;
+  *rows = ranks / c;
+}
+
+bool parse_strategy(const std::string &name, Strategy *out) {
+  static const struct { const char *n; Strategy s; } table[] = {
+      {"serial", Strategy::kSerial},   {"grid", Strategy::kGrid2D},
+      {"gather", Strategy::kShardGather}, {"tree", Strategy::kShardTreeReduce},
+      {"farm", Strategy::kQueryFarm},  {"kdtree", Strategy::kKdTree}};
+  for (auto &e : table)
+    if (name == e.n) { *out = e.s; return true; }
+  return false;
+}
+
+const char *strategy_name(Strategy s) {
+  switch (s) {
+    case Strategy::kSerial: return "serial";
+    case Strategy::kGrid2D: return "grid";
+    case Strategy::kShardGather: return "gather";
+    case Strategy::kShardTreeReduce: return "tree";
+    case Strategy::kQueryFarm: return "farm";
+    case Strategy::kKdTree: return "kdtree";
+  }
+  return "?";
+}
+
+double exact_sqdist(const double *a, const double *b, int dim) {
+  double acc = 0.0;
+  for (int i = 0; i < dim; ++i) {
+    double d = a[i] - b[i];
+    double sq = d * d;
+    acc = acc + sq;
+  }
+  return acc;
+}
+
+namespace {
+
+// Four independent accumulation chains (four different points) so the oracle is
+// not bound by the latency of one add chain; each chain is still sequential.
+inline void exact_sqdist_x4(const double *q, const double *p0, const double *p1,
+                            const double *p2, const double *p3, int dim, double out[4]) {
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  for (int i = 0; i < dim; ++i) {
+    double qi = q[i];
+    double d0 = qi - p0[i], d1 = qi - p1[i], d2 = qi - p2[i], d3 = qi - p3[i];
+    double m0 = d0 * d0, m1 = d1 * d1, m2 = d2 * d2, m3 = d3 * d3;
+    s0 = s0 + m0; s1 = s1 + m1; s2 = s2 + m2; s3 = s3 + m3;
+  }
+  out[0] = s0; out[1] = s1; out[2] = s2; out[3] = s3;
+}
+
+// Max-heap on `closer`: the root is the farthest of the kept candidates.
+struct BoundedHeap {
+  Neighbor *h;
+  int cap;
+  int size = 0;
+  BoundedHeap(Neighbor *storage, int k) : h(storage), cap(k) {}
+  inline void offer(const Neighbor &c) {
+    if (cap == 0) return;
+    if (size < cap) {
+      h[size++] = c;
+      std::push_heap(h, h + size, closer);
+    } else if (closer(c, h[0])) {
+      std::pop_heap(h, h + size, closer);
+      h[size - 1] = c;
+      std::push_heap(h, h + size, closer);
+    }
+  }
+  inline bool full() const { return size == cap; }
+  inline const Neighbor &worst() const { return h[0]; }
+  // Sort ascending and pad with sentinels up to capacity.
+  void finish() {
+    std::sort_heap(h, h + size, closer);
+    for (int i = size; i < cap; ++i) h[i] = Neighbor{kSentinelDist, kSentinelId, -1};
+  }
+};
+
+void parallel_for(int64_t n, int threads, const std::function<void(int64_t, int64_t, int)> &fn) {
+  if (threads <= 0) threads = static_cast<int>(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  if (n < threads) threads = static_cast<int>(std::max<int64_t>(n, 1));
+  if (threads == 1) { fn(0, n, 0); return; }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t) {
+    int64_t b = n * t / threads, e = n * (t + 1) / threads;
+    pool.emplace_back([=, &fn] { fn(b, e, t); });
+  }
+  for (auto &th : pool) th.join();
+}
+
+DatasetView data_slice(const DatasetView &d, int64_t begin, int64_t count) {
+  DatasetView s = d;
+  s.n = count;
+  s.attrs = d.attrs + begin * d.a;
+  s.labels = d.labels + begin;
+  s.id_base = d.id_base + static_cast<int>(begin);
+  return s;
+}
+
+int clamp_k(int k) { return k < 0 ? 0 : k; }
+
+// CSR offsets of the per-query k's.
+std::vector<int64_t> k_offsets(const QueryView &qv) {
+  std::vector<int64_t> off(static_cast<size_t>(qv.q) + 1, 0);
+  for (int64_t i = 0; i < qv.q; ++i) off[i + 1] = off[i] + clamp_k(qv.k[i]);
+  return off;
+}
+
+}  // namespace
+
+void local_topk(const DatasetView &data, const double *query, int k, Neighbor *out) {
+  k = clamp_k(k);
+  BoundedHeap heap(out, k);
+  int64_t r = 0;
+  const int a = data.a;
+  for (; r + 4 <= data.n; r += 4) {
+    double d[4];
+    const double *p = data.attrs + r * a;
+    exact_sqdist_x4(query, p, p + a, p + 2 * a, p + 3 * a, a, d);
+    for (int j = 0; j < 4; ++j)
+      heap.offer(Neighbor{d[j], data.id_base + static_cast<int>(r + j), data.labels[r + j]});
+  }
+  for (; r < data.n; ++r)
+    heap.offer(Neighbor{exact_sqdist(query, data.attrs + r * a, a),
+                        data.id_base + static_cast<int>(r), data.labels[r]});
+  heap.finish();
+}
+
+void merge_topk(const Neighbor *x, const Neighbor *y, int k, Neighbor *out) {
+  int i = 0, j = 0;
+  for (int o = 0; o < k; ++o) {
+    if (closer(y[j], x[i])) out[o] = y[j++];
+    else out[o] = x[i++];
+  }
+}
+
+void finalize_query(const Neighbor *nb, int k, ResultSet *out) {
+  if (out->offset.empty()) out->offset.push_back(0);
+  int label = vote_label(nb, k);
+  size_t base = out->ids.size();
+  for (int i = 0; i < k; ++i) {
+    out->dist.push_back(nb[i].dist);
+    out->ids.push_back(nb[i].id);
+  }
+  out->offset.push_back(static_cast<int64_t>(out->ids.size()));
+  out->label.push_back(label);
+  out->checksum.push_back(result_checksum(label, out->ids.data() + base, k));
+}
+
+namespace {
+
+// Final lists for all queries (CSR by k) -> ResultSet, in query order.
+void finalize_all(const QueryView &qv, const std::vector<int64_t> &off,
+                  const std::vector<Neighbor> &lists, ResultSet *out) {
+  out->clear();
+  out->offset.push_back(0);
+  for (int64_t i = 0; i < qv.q; ++i)
+    finalize_query(lists.data() + off[i], static_cast<int>(off[i + 1] - off[i]), out);
+}
+
+// ---- strategy: serial / oracle -------------------------------------------
+void run_serial(const DatasetView &data, const QueryView &qv, int threads, ResultSet *out) {
+  auto off = k_offsets(qv);
+  std::vector<Neighbor> lists(static_cast<size_t>(off.back()));
+  parallel_for(qv.q, threads, [&](int64_t b, int64_t e, int) {
+    for (int64_t i = b; i < e; ++i)
+      local_topk(data, qv.attrs + i * qv.a, qv.k[i], lists.data() + off[i]);
+  });
+  finalize_all(qv, off, lists, out);
+}
+
+// ---- strategy: R x C grid (covers gather and tree as C == 1 special cases) --
+//
+// Rank (r, c) owns data shard r and query shard c.  Phase 1: every rank writes
+// its per-query sorted, sentinel-padded k-lists into its own mailbox.  Phase 2
+// (the "reduction" along the data axis, reference: engine.cpp:273-309) runs per
+// grid column, either as gather-then-select at row 0 or as a pairwise tree of
+// `merge_topk` operators.
+enum class Reduce { kGatherSelect, kTree };
+
+void run_grid(const DatasetView &data, const QueryView &qv, int rows, int cols, Reduce how,
+              ResultSet *out) {
+  BlockPartition dp{data.n, rows}, qp{qv.q, cols};
+  auto off = k_offsets(qv);
+  // mailbox[r] holds lists for ALL queries (each column fills its own slice).
+  std::vector<std::vector<Neighbor>> mailbox(static_cast<size_t>(rows));
+  for (auto &m : mailbox) m.resize(static_cast<size_t>(off.back()));
+
+  std::vector<std::thread> ranks;
+  for (int r = 0; r < rows; ++r)
+    for (int c = 0; c < cols; ++c)
+      ranks.emplace_back([&, r, c] {
+        DatasetView shard = data_slice(data, dp.begin(r), dp.count(r));
+        int64_t qb = qp.begin(c), qe = qb + qp.count(c);
+        for (int64_t i = qb; i < qe; ++i)
+          local_topk(shard, qv.attrs + i * qv.a, qv.k[i], mailbox[r].data() + off[i]);
+      });
+  for (auto &t : ranks) t.join();
+
+  std::vector<Neighbor> final_lists(static_cast<size_t>(off.back()));
+  std::vector<std::thread> owners;
+  for (int c = 0; c < cols; ++c)
+    owners.emplace_back([&, c] {
+      int64_t qb = qp.begin(c), qe = qb + qp.count(c);
+      std::vector<Neighbor> scratch, tmp;
+      for (int64_t i = qb; i < qe; ++i) {
+        int k = static_cast<int>(off[i + 1] - off[i]);
+        Neighbor *dst = final_lists.data() + off[i];
+        if (how == Reduce::kGatherSelect) {
+          scratch.clear();
+          for (int r = 0; r < rows; ++r)
+            scratch.insert(scratch.end(), mailbox[r].data() + off[i], mailbox[r].data() + off[i] + k);
+          std::partial_sort(scratch.begin(), scratch.begin() + k, scratch.end(), closer);
+          std::copy(scratch.begin(), scratch.begin() + k, dst);
+        } else {
+          // pairwise tree: stride doubling, result accumulates in row 0's slot
+          tmp.resize(static_cast<size_t>(k));
+          for (int stride = 1; stride < rows; stride *= 2)
+            for (int r = 0; r + stride < rows; r += 2 * stride) {
+              Neighbor *x = mailbox[r].data() + off[i];
+              const Neighbor *y = mailbox[r + stride].data() + off[i];
+              merge_topk(x, y, k, tmp.data());
+              std::copy(tmp.begin(), tmp.end(), x);
+            }
+          std::copy(mailbox[0].data() + off[i], mailbox[0].data() + off[i] + k, dst);
+        }
+      }
+    });
+  for (auto &t : owners) t.join();
+  finalize_all(qv, off, final_lists, out);
+}
+
+// ---- strategy: dynamic query farm ------------------------------------------
+// Every worker sees the whole dataset and pulls the next query index from a
+// shared counter, the shared-memory analogue of bench_4's master handing out
+// one query at a time over Send/Recv.
+void run_farm(const DatasetView &data, const QueryView &qv, int workers, ResultSet *out) {
+  auto off = k_offsets(qv);
+  std::vector<Neighbor> lists(static_cast<size_t>(off.back()));
+  std::atomic<int64_t> next{0};
+  if (workers < 1) workers = 1;
+  std::vector<std::thread> pool;
+  for (int w = 0; w < workers; ++w)
+    pool.emplace_back([&] {
+      for (;;) {
+        int64_t i = next.fetch_add(1, std::memory_order_relaxed);
+        if (i >= qv.q) break;
+        local_topk(data, qv.attrs + i * qv.a, qv.k[i], lists.data() + off[i]);
+      }
+    });
+  for (auto &t : pool) t.join();
+  finalize_all(qv, off, lists, out);
+}
+
+// ---- strategy: exact kd-tree -------------------------------------------------
+// Median-split tree over row indices.  Distances are still evaluated with
+// exact_sqdist so results are bit-identical to brute force; pruning compares the
+// squared plane offset against the current worst kept distance and only prunes
+// on strict ">" because an equal-distance point with a larger id still wins.
+struct KdTree {
+  struct Node { int axis; int row; int left; int right; };
+  const DatasetView &d;
+  std::vector<Node> nodes;
+  std::vector<int> order;
+  explicit KdTree(const DatasetView &data) : d(data) {
+    order.resize(static_cast<size_t>(d.n));
+    for (int64_t i = 0; i < d.n; ++i) order[i] = static_cast<int>(i);
+    nodes.reserve(order.size());
+    if (d.n > 0) build(0, static_cast<int>(d.n), 0);
+  }
+  int build(int lo, int hi, int depth) {
+    if (lo >= hi) return -1;
+    int axis = d.a > 0 ? depth % d.a : 0;
+    int mid = lo + (hi - lo) / 2;
+    std::nth_element(order.begin() + lo, order.begin() + mid, order.begin() + hi,
+                     [&](int x, int y) {
+                       return d.attrs[int64_t(x) * d.a + axis] < d.attrs[int64_t(y) * d.a + axis];
+                     });
+    int me = static_cast<int>(nodes.size());
+    nodes.push_back(Node{axis, order[mid], -1, -1});
+    int l = build(lo, mid, depth + 1);
+    int r = build(mid + 1, hi, depth + 1);
+    nodes[me].left = l;
+    nodes[me].right = r;
+    return me;
+  }
+  void search(int ni, const double *q, BoundedHeap &heap) const {
+    if (ni < 0) return;
+    const Node &nd = nodes[ni];
+    const double *p = d.attrs + int64_t(nd.row) * d.a;
+    heap.offer(Neighbor{exact_sqdist(q, p, d.a), d.id_base + nd.row, d.labels[nd.row]});
+    double diff = q[nd.axis] - p[nd.axis];
+    int near = diff < 0 ? nd.left : nd.right;
+    int far = diff < 0 ? nd.right : nd.left;
+    search(near, q, heap);
+    double plane = diff * diff;
+    if (!heap.full() || !(plane > heap.worst().dist)) search(far, q, heap);
+  }
+};
+
+void run_kdtree(const DatasetView &data, const QueryView &qv, ResultSet *out) {
+  auto off = k_offsets(qv);
+  std::vector<Neighbor> lists(static_cast<size_t>(off.back()));
+  KdTree tree(data);
+  for (int64_t i = 0; i < qv.q; ++i) {
+    BoundedHeap heap(lists.data() + off[i], static_cast<int>(off[i + 1] - off[i]));
+    if (data.a > 0) tree.search(data.n > 0 ? 0 : -1, qv.attrs + i * qv.a, heap);
+    else for (int64_t r = 0; r < data.n; ++r)
+      heap.offer(Neighbor{0.0, data.id_base + static_cast<int>(r), data.labels[r]});
+    heap.finish();
+  }
+  finalize_all(qv, off, lists, out);
+}
+
+}  // namespace
+
+void knn_cpu(const DatasetView &data, const QueryView &queries, const CpuOptions &opt,
+             ResultSet *out) {
+  if (data.a != queries.a && queries.q > 0 && data.n > 0)
+    throw std::invalid_argument("dataset and queries disagree on num_attrs");
+  int ranks = opt.ranks < 1 ? 1 : opt.ranks;
+  switch (opt.strategy) {
+    case Strategy::kSerial:
+      run_serial(data, queries, opt.threads, out);
+      return;
+    case Strategy::kGrid2D: {
+      int rows = opt.rows, cols = opt.cols;
+      if (rows <= 0 || cols <= 0) choose_grid(ranks, &rows, &cols);
+      run_grid(data, queries, rows, cols, Reduce::kGatherSelect, out);
+      return;
+    }
+    case Strategy::kShardGather:
+      run_grid(data, queries, ranks, 1, Reduce::kGatherSelect, out);
+      return;
+    case Strategy::kShardTreeReduce:
+      run_grid(data, queries, ranks, 1, Reduce::kTree, out);
+      return;
+    case Strategy::kQueryFarm:
+      run_farm(data, queries, ranks, out);
+      return;
+    case Strategy::kKdTree:
+      run_kdtree(data, queries, out);
+      return;
+  }
+}
+
+}  // namespace dmlp

@@ -1,0 +1,227 @@
+// Text loader, synthetic generator and text writer.  See include/dmlp/io.h.
+#include "dmlp/io.h"
+
+#include <charconv>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace dmlp {
+
+HostAllocator malloc_allocator() {
+  HostAllocator a;
+  a.alloc = [](size_t bytes) -> void * { return std::malloc(bytes ? bytes : 1); };
+  a.release = [](void *p) { std::free(p); };
+  return a;
+}
+
+Problem::~Problem() { free_all(); }
+
+void Problem::free_all() {
+  if (alloc_.release) {
+    if (data_attrs) alloc_.release(data_attrs);
+    if (data_labels) alloc_.release(data_labels);
+    if (query_attrs) alloc_.release(query_attrs);
+    if (query_k) alloc_.release(query_k);
+  }
+  data_attrs = query_attrs = nullptr;
+  data_labels = query_k = nullptr;
+}
+
+Problem::Problem(Problem &&o) noexcept { *this = std::move(o); }
+
+Problem &Problem::operator=(Problem &&o) noexcept {
+  if (this != &o) {
+    free_all();
+    alloc_ = o.alloc_;
+    num_data = o.num_data; num_queries = o.num_queries; num_attrs = o.num_attrs;
+    data_attrs = o.data_attrs; data_labels = o.data_labels;
+    query_attrs = o.query_attrs; query_k = o.query_k;
+    o.data_attrs = o.query_attrs = nullptr;
+    o.data_labels = o.query_k = nullptr;
+    o.num_data = o.num_queries = 0; o.num_attrs = 0;
+  }
+  return *this;
+}
+
+void Problem::resize(int64_t n, int64_t q, int a) {
+  free_all();
+  if (n < 0 || q < 0 || a < 0) throw std::runtime_error("negative problem dimension");
+  num_data = n; num_queries = q; num_attrs = a;
+  auto get = [&](size_t bytes) {
+    void *p = alloc_.alloc(bytes);
+    if (!p) throw std::bad_alloc();
+    return p;
+  };
+  data_attrs = static_cast<double *>(get(sizeof(double) * size_t(n) * size_t(a)));
+  data_labels = static_cast<int *>(get(sizeof(int) * size_t(n)));
+  query_attrs = static_cast<double *>(get(sizeof(double) * size_t(q) * size_t(a)));
+  query_k = static_cast<int *>(get(sizeof(int) * size_t(q)));
+}
+
+namespace {
+
+inline const char *skip_blank(const char *p, const char *end) {
+  while (p < end && (*p == ' ' || *p == '\t' || *p == '\r')) ++p;
+  return p;
+}
+
+// One whitespace-delimited number; a missing or malformed token yields 0, the
+// value a failed stream extraction leaves behind in the reference's parser.
+inline const char *take_double(const char *p, const char *end, double *v) {
+  p = skip_blank(p, end);
+  if (p < end && *p == '+') ++p;
+  auto r = std::from_chars(p, end, *v);
+  if (r.ec != std::errc()) { *v = 0.0; return end; }
+  return r.ptr;
+}
+
+inline const char *take_int(const char *p, const char *end, int *v) {
+  p = skip_blank(p, end);
+  if (p < end && *p == '+') ++p;
+  auto r = std::from_chars(p, end, *v);
+  if (r.ec != std::errc()) { *v = 0; return end; }
+  return r.ptr;
+}
+
+struct Line { const char *b; const char *e; };
+
+}  // namespace
+
+void parse_problem(const char *text, size_t len, int threads, Problem *out) {
+  const char *end = text + len;
+  // header
+  const char *nl = static_cast<const char *>(std::memchr(text, '\n', len));
+  const char *hend = nl ? nl : end;
+  int n = 0, q = 0, a = 0;
+  const char *p = take_int(text, hend, &n);
+  p = take_int(p, hend, &q);
+  take_int(p, hend, &a);
+  out->resize(n, q, a);
+
+  // index the N + Q payload lines
+  const size_t want = size_t(n) + size_t(q);
+  std::vector<Line> lines;
+  lines.reserve(want);
+  const char *cur = nl ? nl + 1 : end;
+  while (lines.size() < want) {
+    if (cur >= end) { lines.push_back(Line{end, end}); continue; }
+    const char *e = static_cast<const char *>(std::memchr(cur, '\n', size_t(end - cur)));
+    if (!e) e = end;
+    lines.push_back(Line{cur, e});
+    cur = e + 1;
+  }
+
+  if (threads <= 0) threads = int(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  if (size_t(threads) > want) threads = int(want ? want : 1);
+
+  std::vector<std::string> errors;
+  errors.resize(static_cast<size_t>(threads));
+  auto work = [&](int t) {
+    size_t b = want * size_t(t) / size_t(threads), e = want * size_t(t + 1) / size_t(threads);
+    for (size_t i = b; i < e; ++i) {
+      const char *s = lines[i].b, *le = lines[i].e;
+      while (le > s && (le[-1] == '\r')) --le;
+      if (i < size_t(n)) {
+        if (s == le) { errors[t] = "Line is empty"; return; }
+        s = take_int(s, le, &out->data_labels[i]);
+        double *row = out->data_attrs + i * size_t(a);
+        for (int j = 0; j < a; ++j) s = take_double(s, le, &row[j]);
+      } else {
+        size_t qi = i - size_t(n);
+        if (s == le || *s != 'Q') {
+          errors[t] = "Line is wrongly formatted";
+          return;
+        }
+        ++s;
+        s = take_int(s, le, &out->query_k[qi]);
+        double *row = out->query_attrs + qi * size_t(a);
+        for (int j = 0; j < a; ++j) s = take_double(s, le, &row[j]);
+      }
+    }
+  };
+  if (threads == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t) pool.emplace_back(work, t);
+    for (auto &th : pool) th.join();
+  }
+  for (auto &e : errors)
+    if (!e.empty()) throw std::runtime_error(e);
+}
+
+void read_problem(std::FILE *f, int threads, Problem *out) {
+  std::vector<char> buf;
+  size_t used = 0;
+  buf.resize(1 << 22);
+  for (;;) {
+    if (used == buf.size()) buf.resize(buf.size() * 2);
+    size_t got = std::fread(buf.data() + used, 1, buf.size() - used, f);
+    if (got == 0) break;
+    used += got;
+  }
+  parse_problem(buf.data(), used, threads, out);
+}
+
+void synth_problem(const SynthSpec &s, Problem *out) {
+  out->resize(s.n, s.q, s.a);
+  int threads = int(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  int kmax = s.max_k < s.n ? s.max_k : int(s.n);
+  int kmin = s.min_k < kmax ? s.min_k : kmax;
+  if (kmin < 0) kmin = 0;
+  auto fill = [&](int t) {
+    int64_t b = s.n * t / threads, e = s.n * (t + 1) / threads;
+    for (int64_t i = b; i < e; ++i) {
+      out->data_labels[i] = int(synth_hash(s.seed, 1, uint64_t(i)) % uint64_t(s.num_labels));
+      double *row = out->data_attrs + i * s.a;
+      for (int j = 0; j < s.a; ++j)
+        row[j] = synth_attr(synth_hash(s.seed, 0, uint64_t(i) * uint64_t(s.a) + uint64_t(j)), s.lo, s.hi);
+    }
+    b = s.q * t / threads; e = s.q * (t + 1) / threads;
+    for (int64_t i = b; i < e; ++i) {
+      out->query_k[i] = kmin + int(synth_hash(s.seed, 3, uint64_t(i)) % uint64_t(kmax - kmin + 1));
+      double *row = out->query_attrs + i * s.a;
+      for (int j = 0; j < s.a; ++j)
+        row[j] = synth_attr(synth_hash(s.seed, 2, uint64_t(i) * uint64_t(s.a) + uint64_t(j)), s.lo, s.hi);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t) pool.emplace_back(fill, t);
+  for (auto &th : pool) th.join();
+}
+
+void write_problem_text(const Problem &p, std::FILE *f) {
+  std::fprintf(f, "%lld %lld %d\n", (long long)p.num_data, (long long)p.num_queries, p.num_attrs);
+  std::string line;
+  char tmp[64];
+  for (int64_t i = 0; i < p.num_data; ++i) {
+    line.clear();
+    line += std::to_string(p.data_labels[i]);
+    const double *row = p.data_attrs + i * p.num_attrs;
+    for (int j = 0; j < p.num_attrs; ++j) {
+      int m = std::snprintf(tmp, sizeof tmp, " %.6f", row[j]);
+      line.append(tmp, size_t(m));
+    }
+    line += '\n';
+    std::fwrite(line.data(), 1, line.size(), f);
+  }
+  for (int64_t i = 0; i < p.num_queries; ++i) {
+    line.assign("Q ");
+    line += std::to_string(p.query_k[i]);
+    const double *row = p.query_attrs + i * p.num_attrs;
+    for (int j = 0; j < p.num_attrs; ++j) {
+      int m = std::snprintf(tmp, sizeof tmp, " %.6f", row[j]);
+      line.append(tmp, size_t(m));
+    }
+    line += '\n';
+    std::fwrite(line.data(), 1, line.size(), f);
+  }
+}
+
+}  // namespace dmlp

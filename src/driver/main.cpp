@@ -1,0 +1,99 @@
+// Driver: stdin -> flat (pinned) problem -> Engine -> stdout / stderr.
+//
+// Contract kept from the reference driver (reference: common.cpp:81-135): the
+// input is parsed outside the timer; the timed region covers distribution,
+// compute, merge and result printing; `Time taken: <ms> ms` goes to stderr and
+// one `Query <id> checksum: <h>` line per query goes to stdout.
+//
+// Extras (all opt-in, none change the contract):
+//   --synth N Q A [lo hi minK maxK labels seed]  build the problem in memory instead of stdin
+//   --aos                                        go through the AoS Engine::KNN signature
+//   --json                                       also print a JSON timing line on stderr
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <stdexcept>
+#include <string>
+
+#include "dmlp/gpu.h"
+#include "dmlp/io.h"
+#include "engine.h"
+
+int main(int argc, char **argv) {
+  std::ios::sync_with_stdio(false);
+  std::cin.tie(nullptr);
+
+  bool use_aos = false, json = false, synth = false;
+  dmlp::SynthSpec spec;
+  for (int i = 1; i < argc; ++i) {
+    std::string arg = argv[i];
+    if (arg == "--aos") use_aos = true;
+    else if (arg == "--json") json = true;
+    else if (arg == "--synth" && i + 3 < argc) {
+      synth = true;
+      spec.n = std::atoll(argv[++i]);
+      spec.q = std::atoll(argv[++i]);
+      spec.a = std::atoi(argv[++i]);
+      double *dopt[] = {&spec.lo, &spec.hi};
+      for (int j = 0; j < 2 && i + 1 < argc && argv[i + 1][0] != '-' ; ++j) *dopt[j] = std::atof(argv[++i]);
+      int *iopt[] = {&spec.min_k, &spec.max_k, &spec.num_labels};
+      for (int j = 0; j < 3 && i + 1 < argc && argv[i + 1][0] != '-'; ++j) *iopt[j] = std::atoi(argv[++i]);
+      if (i + 1 < argc && argv[i + 1][0] != '-') spec.seed = std::strtoull(argv[++i], nullptr, 10);
+    } else {
+      std::fprintf(stderr, "usage: %s [--aos] [--json] [--synth N Q A [lo hi minK maxK labels seed]] < input\n", argv[0]);
+      return 2;
+    }
+  }
+
+  try {
+    Engine eng;
+    bool gpu_possible = eng.config.backend != dmlp::Backend::kCpu && dmlp::gpu::device_count() > 0;
+    dmlp::Problem prob(gpu_possible ? dmlp::gpu::pinned_allocator() : dmlp::malloc_allocator());
+    auto t_parse0 = std::chrono::steady_clock::now();
+    if (synth) dmlp::synth_problem(spec, &prob);
+    else dmlp::read_problem(stdin, eng.config.cpu.threads, &prob);
+    auto t_parse1 = std::chrono::steady_clock::now();
+
+    Params params{int(prob.num_data), int(prob.num_queries), prob.num_attrs};
+    auto start = std::chrono::steady_clock::now();
+    if (use_aos) {
+      std::vector<DataPoint> dataset(size_t(prob.num_data));
+      std::vector<Query> queries(size_t(prob.num_queries));
+      for (int64_t i = 0; i < prob.num_data; ++i) {
+        dataset[size_t(i)].id = int(i);
+        dataset[size_t(i)].label = prob.data_labels[i];
+        dataset[size_t(i)].attrs.assign(prob.data_attrs + i * prob.num_attrs,
+                                        prob.data_attrs + (i + 1) * prob.num_attrs);
+      }
+      for (int64_t i = 0; i < prob.num_queries; ++i) {
+        queries[size_t(i)].id = int(i);
+        queries[size_t(i)].k = prob.query_k[i];
+        queries[size_t(i)].attrs.assign(prob.query_attrs + i * prob.num_attrs,
+                                        prob.query_attrs + (i + 1) * prob.num_attrs);
+      }
+      start = std::chrono::steady_clock::now();
+      eng.KNN(params, dataset, queries);
+    } else {
+      eng.KNNFlat(prob.dataset(), prob.queries(), nullptr);
+    }
+    std::cout.flush();
+    auto stop = std::chrono::steady_clock::now();
+    long long ms = std::chrono::duration_cast<std::chrono::milliseconds>(stop - start).count();
+    std::cerr << "Time taken: " << ms << " ms\n";
+    if (json) {
+      double us = std::chrono::duration<double, std::micro>(stop - start).count();
+      double parse_ms = std::chrono::duration<double, std::milli>(t_parse1 - t_parse0).count();
+      std::fprintf(stderr,
+                   "{\"backend\": \"%s\", \"num_data\": %d, \"num_queries\": %d, \"num_attrs\": %d, "
+                   "\"time_ms\": %.3f, \"queries_per_sec\": %.3f, \"load_ms\": %.3f}\n",
+                   eng.last_backend.c_str(), params.num_data, params.num_queries, params.num_attrs,
+                   us / 1e3, us > 0 ? params.num_queries / (us * 1e-6) : 0.0, parse_ms);
+    }
+  } catch (const std::exception &e) {
+    std::cerr << "engine: " << e.what() << "\n";
+    return 1;
+  }
+  return 0;
+}

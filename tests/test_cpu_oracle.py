@@ -1,0 +1,165 @@
+"""Golden vectors and property tests for the CPU backends."""
+import hashlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from dmlp_b200.ops import cpu
+
+STRATEGIES = ["serial", "grid", "gather", "tree", "farm", "kdtree"]
+
+
+def gen_reference_stream(tmp_path, repo_root, **kw):
+    out = tmp_path / "in.txt"
+    args = [sys.executable, os.path.join(repo_root, "tools", "generate_input.py")]
+    for key, val in kw.items():
+        args += [f"--{key}", str(val)]
+    args += ["--output", str(out)]
+    subprocess.check_call(args, stdout=subprocess.DEVNULL)
+    return out.read_bytes()
+
+
+def brute_numpy(data, labels, queries, k):
+    """Independent restatement of the spec in plain Python/numpy."""
+    sums = []
+    for qi in range(queries.shape[0]):
+        acc = np.zeros(data.shape[0])
+        for j in range(data.shape[1]):  # sequential, non-fused: same rounding as the reference
+            d = queries[qi, j] - data[:, j]
+            acc = acc + d * d
+        order = sorted(range(data.shape[0]), key=lambda r: (acc[r], -r))[: max(int(k[qi]), 0)]
+        votes = {}
+        for r in order:
+            votes[int(labels[r])] = votes.get(int(labels[r]), 0) + 1
+        label = -1
+        best = 0
+        for lab, cnt in votes.items():
+            if cnt > best or (cnt == best and lab > label):
+                best, label = cnt, lab
+        h = 1469598103934665603
+        h = ((h ^ (label & (2**64 - 1))) * 1099511628211) % 2**64
+        for r in order:
+            h = ((h ^ (r + 1)) * 1099511628211) % 2**64
+        sums.append(h)
+    return np.array(sums, dtype=np.uint64)
+
+
+def test_golden_constant_k(tmp_path, repo_root):
+    text = gen_reference_stream(tmp_path, repo_root, num_data=12, num_queries=3, num_attrs=2, min=0, max=10,
+                                minK=3, maxK=3, num_labels=3, seed=42)
+    data, labels, queries, k = cpu.parse_text(text)
+    label, checksum, ids, dist, off = cpu.knn(data, labels, queries, k)
+    assert checksum.tolist() == [1048314657462637447, 17629266663427905930, 6436800073062518871]
+    assert label.tolist() == [0, 0, 2]
+    assert ids[:3].tolist() == [11, 9, 1]
+    np.testing.assert_allclose(dist[:3], [3.21078, 14.6927, 15.3981], rtol=1e-5)
+
+
+def test_golden_variable_k(tmp_path, repo_root):
+    text = gen_reference_stream(tmp_path, repo_root, num_data=12, num_queries=3, num_attrs=2, min=0, max=10,
+                                minK=2, maxK=4, num_labels=3, seed=42)
+    data, labels, queries, k = cpu.parse_text(text)
+    for s in STRATEGIES:
+        _, checksum, *_ = cpu.knn(data, labels, queries, k, strategy=s, ranks=3)
+        assert checksum.tolist() == [1698155651117006534, 17629266663427905930, 15745963786526292968], s
+
+
+@pytest.mark.parametrize("strategy,ranks,rows,cols", [
+    ("serial", 1, 0, 0), ("grid", 2, 0, 0), ("grid", 8, 0, 0), ("grid", 8, 8, 1), ("grid", 8, 1, 8),
+    ("grid", 6, 3, 2), ("grid", 6, 2, 3), ("gather", 5, 0, 0), ("tree", 7, 0, 0), ("tree", 8, 0, 0),
+    ("farm", 4, 0, 0), ("kdtree", 1, 0, 0)])
+def test_strategies_agree_with_spec(strategy, ranks, rows, cols):
+    data, labels, queries, k = cpu.synth(157, 23, 5, -3.0, 3.0, 1, 9, 4, seed=7)
+    want = brute_numpy(data, labels, queries, k)
+    _, got, *_ = cpu.knn(data, labels, queries, k, strategy=strategy, ranks=ranks, rows=rows, cols=cols)
+    assert got.tolist() == want.tolist()
+
+
+def test_ties_prefer_larger_id_and_label():
+    # four identical points: ties resolved by larger id; label vote ties -> larger label
+    data = np.zeros((4, 3))
+    labels = np.array([5, 1, 9, 1], dtype=np.int32)
+    queries = np.ones((1, 3))
+    for s in STRATEGIES:
+        label, _, ids, *_ = cpu.knn(data, labels, queries, np.array([2], np.int32), strategy=s, ranks=2)
+        assert ids.tolist() == [3, 2], s
+        assert label.tolist() == [9], s  # labels {1, 9} tie 1-1 -> 9
+
+
+def test_k_equals_num_data_and_shard_smaller_than_k():
+    data, labels, queries, k = cpu.synth(9, 4, 3, 0.0, 1.0, 9, 9, 3, seed=3)
+    want = brute_numpy(data, labels, queries, k)
+    for s, ranks in [("grid", 4), ("gather", 8), ("tree", 8), ("farm", 3), ("kdtree", 1)]:
+        _, got, ids, *_ = cpu.knn(data, labels, queries, k, strategy=s, ranks=ranks)
+        assert got.tolist() == want.tolist(), s
+        assert (ids >= 0).all()
+
+
+def test_edge_shapes():
+    data, labels, queries, k = cpu.synth(10, 0, 2, 0.0, 1.0, 1, 3, 2, seed=1)
+    label, checksum, ids, dist, off = cpu.knn(data, labels, queries, k, strategy="grid", ranks=4)
+    assert label.shape == (0,) and off.tolist() == [0]
+    data, labels, queries, k = cpu.synth(10, 3, 1, 0.0, 1.0, 1, 3, 1, seed=1)
+    want = brute_numpy(data, labels, queries, k)
+    assert cpu.knn(data, labels, queries, k, strategy="tree", ranks=3)[1].tolist() == want.tolist()
+
+
+def test_merge_operator_is_commutative_and_associative():
+    rng = np.random.default_rng(0)
+    k = 6
+
+    def rand_list(base):
+        d = np.sort(rng.integers(0, 5, k).astype(np.float64))
+        i = base + np.arange(k, dtype=np.int32)
+        order = sorted(range(k), key=lambda t: (d[t], -i[t]))
+        return d[order], i[order].astype(np.int32)
+    a, b, c = rand_list(0), rand_list(100), rand_list(200)
+    ab = cpu.merge_topk(*a, *b)
+    ba = cpu.merge_topk(*b, *a)
+    assert ab[1].tolist() == ba[1].tolist()
+    left = cpu.merge_topk(*cpu.merge_topk(*a, *b), *c)
+    right = cpu.merge_topk(*a, *cpu.merge_topk(*b, *c))
+    assert left[1].tolist() == right[1].tolist()
+
+
+def test_parser_errors_match_reference_messages():
+    with pytest.raises(RuntimeError, match="Line is wrongly formatted"):
+        cpu.parse_text("1 1 1\n0 1.0\n2 1.0\n")
+    with pytest.raises(RuntimeError, match="Line is empty"):
+        cpu.parse_text("2 0 1\n0 1.0\n\n")
+    # 'Q4 ...' and 'Q 4 ...' both parse (reference strips the leading Q only)
+    _, _, _, k = cpu.parse_text("1 2 1\n0 1.0\nQ1 0.5\nQ 1 0.5\n")
+    assert k.tolist() == [1, 1]
+
+
+def test_exact_distance_is_sequential_non_fused():
+    rng = np.random.default_rng(1)
+    a, b = rng.uniform(-100, 100, 257), rng.uniform(-100, 100, 257)
+    acc = 0.0
+    for x, y in zip(a, b):
+        acc = acc + (x - y) * (x - y)
+    assert cpu.exact_sqdist(a, b) == acc
+
+
+def test_synth_matches_text_round_trip(tmp_path, repo_root):
+    data, labels, queries, k = cpu.synth(20, 5, 3, -100.0, 100.0, 1, 4, 3, seed=11)
+    out = tmp_path / "hash.in"
+    subprocess.check_call([sys.executable, os.path.join(repo_root, "tools", "generate_input.py"),
+                           "--num_data", "20", "--num_queries", "5", "--num_attrs", "3", "--min", "-100",
+                           "--max", "100", "--minK", "1", "--maxK", "4", "--num_labels", "3", "--seed", "11",
+                           "--stream", "hash", "--output", str(out)], stdout=subprocess.DEVNULL)
+    d2, l2, q2, k2 = cpu.parse_text(out.read_bytes())
+    assert (d2 == data).all() and (q2 == queries).all() and (l2 == labels).all() and (k2 == k).all()
+
+
+@pytest.mark.slow
+def test_midsize_md5(tmp_path, repo_root):
+    text = gen_reference_stream(tmp_path, repo_root, num_data=100000, num_queries=1000, num_attrs=64, min=-100,
+                                max=100, minK=16, maxK=16, num_labels=10, seed=42)
+    data, labels, queries, k = cpu.parse_text(text)
+    _, checksum, *_ = cpu.knn(data, labels, queries, k)
+    lines = sorted(f"Query {i} checksum: {int(c)}\n" for i, c in enumerate(checksum))
+    assert hashlib.md5("".join(lines).encode()).hexdigest() == "8cf1102ad3eb629255188098e0cfb4a1"

@@ -1,0 +1,72 @@
+"""The `engine` binary keeps the reference driver contract."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+
+@pytest.fixture(scope="module")
+def engine_bins(repo_root):
+    exe = os.path.join(repo_root, "engine")
+    dbg = os.path.join(repo_root, "engine.debug")
+    if not (os.path.exists(exe) and os.path.exists(dbg)):
+        subprocess.check_call(["make", "-C", repo_root, "-j8", "all"], stdout=subprocess.DEVNULL,
+                              stderr=subprocess.DEVNULL)
+    return exe, dbg
+
+
+def _gen(tmp_path, repo_root, *extra):
+    out = tmp_path / "in.txt"
+    subprocess.check_call([sys.executable, os.path.join(repo_root, "tools", "generate_input.py"),
+                           "--num_data", "12", "--num_queries", "3", "--num_attrs", "2", "--min", "0", "--max", "10",
+                           "--num_labels", "3", "--seed", "42", "--output", str(out), *extra],
+                          stdout=subprocess.DEVNULL)
+    return out
+
+
+def _run(exe, path, env_extra=None, args=()):
+    env = dict(os.environ, DMLP_BACKEND="cpu")
+    env.update(env_extra or {})
+    with open(path, "rb") as f:
+        return subprocess.run([exe, *args], stdin=f, capture_output=True, env=env, text=True)
+
+
+def test_release_contract(engine_bins, tmp_path, repo_root):
+    res = _run(engine_bins[0], _gen(tmp_path, repo_root, "--minK", "3", "--maxK", "3"))
+    assert res.returncode == 0
+    assert sorted(res.stdout.splitlines()) == sorted([
+        "Query 0 checksum: 1048314657462637447",
+        "Query 1 checksum: 17629266663427905930",
+        "Query 2 checksum: 6436800073062518871"])
+    assert re.fullmatch(r"Time taken: \d+ ms\n", res.stderr)
+
+
+def test_debug_contract(engine_bins, tmp_path, repo_root):
+    res = _run(engine_bins[1], _gen(tmp_path, repo_root, "--minK", "3", "--maxK", "3"))
+    lines = res.stdout.splitlines()
+    assert lines[0] == "Label for Query 0 : 0"
+    assert lines[1] == "Top-3 neighbors:"
+    assert lines[2].startswith("11 : 3.21078")
+
+
+@pytest.mark.parametrize("env", [
+    {"DMLP_STRATEGY": "grid", "DMLP_GRID": "2x1"}, {"DMLP_STRATEGY": "grid", "DMLP_GRID": "4x2"},
+    {"DMLP_STRATEGY": "tree", "DMLP_RANKS": "8"}, {"DMLP_STRATEGY": "farm", "DMLP_RANKS": "3"},
+    {"DMLP_STRATEGY": "gather", "DMLP_RANKS": "2"}, {"DMLP_STRATEGY": "kdtree"}])
+def test_strategies_and_aos_api(engine_bins, tmp_path, repo_root, env):
+    path = _gen(tmp_path, repo_root, "--minK", "2", "--maxK", "4")
+    want = ["Query 0 checksum: 1698155651117006534", "Query 1 checksum: 17629266663427905930",
+            "Query 2 checksum: 15745963786526292968"]
+    for args in ((), ("--aos",)):
+        res = _run(engine_bins[0], path, env, args)
+        assert res.returncode == 0, res.stderr
+        assert sorted(res.stdout.splitlines()) == sorted(want)  # each query exactly once
+
+
+def test_bad_input_fails_cleanly(engine_bins, tmp_path):
+    bad = tmp_path / "bad.in"
+    bad.write_text("1 1 1\n0 1.0\nX 1 1.0\n")
+    res = _run(engine_bins[0], bad)
+    assert res.returncode != 0 and "wrongly formatted" in res.stderr
