@@ -1,50 +1,67 @@
 # Same user-facing targets as the reference build (reference: Makefile:4-15):
 #   make all | engine | engine.debug | clean
-# plus the shared libraries the Python package loads and a few tools.
-#   make NO_CUDA=1 ...   builds the CPU-only driver (no nvcc needed)
-CXX      ?= g++
-NVCC     ?= /usr/local/cuda/bin/nvcc
-CUDA_HOME ?= /usr/local/cuda
-CXXFLAGS ?= -O3 -std=c++17 -ffp-contract=off -fPIC -Wall -Wextra -pthread -Iinclude
-SM_FLAGS  = -gencode arch=compute_100a,code=sm_100a
-NVFLAGS  ?= -O3 -std=c++17 $(SM_FLAGS) -lineinfo -Xcompiler -fPIC,-ffp-contract=off,-pthread -Iinclude --fmad=true
+# plus the shared libraries the Python package loads (make libs) and tools.
+#   make NO_CUDA=1 ...   builds a CPU-only driver (no nvcc needed)
+CXX       ?= g++
+NVCC      ?= /usr/local/cuda/bin/nvcc
+CXXFLAGS  ?= -O3 -std=c++17 -ffp-contract=off -fPIC -Wall -Wextra -pthread -Iinclude -MMD -MP
+SM_FLAGS   = -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   ?= -O3 -std=c++17 --expt-relaxed-constexpr $(SM_FLAGS) -lineinfo \
+             -Xcompiler -fPIC,-ffp-contract=off,-pthread -Iinclude -MMD -MP
 
-HOST_SRCS = src/driver/main.cpp src/driver/report.cpp src/driver/io.cpp \
-            src/engine/engine.cpp src/cpu/cpu_backends.cpp
-KERNEL_SRCS = $(wildcard src/kernels/*.cu)
-RUNTIME_SRCS = $(wildcard src/runtime/*.cu) $(wildcard src/engine/*.cu)
-LIBDIR = distributed-machine-learning-project_b200/lib
+B       = build
+LIBDIR  = distributed-machine-learning-project_b200/lib
 
-.PHONY: all clean libs tools test
+HOST_CPP   = src/driver/report.cpp src/driver/io.cpp src/engine/engine.cpp src/cpu/cpu_backends.cpp
+KERNEL_CU  = $(wildcard src/kernels/*.cu) $(wildcard src/runtime/*.cu)
+ENGINE_CU  = src/engine/gpu_engine.cu
 
+HOST_O     = $(HOST_CPP:%.cpp=$(B)/%.o)
+HOST_DBG_O = $(HOST_CPP:%.cpp=$(B)/%.dbg.o)
+KERNEL_O   = $(KERNEL_CU:%.cu=$(B)/%.o)
+ENGINE_O   = $(ENGINE_CU:%.cu=$(B)/%.o)
+
+.PHONY: all clean libs tools
 all: engine engine.debug
 
+$(B)/%.o: %.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+$(B)/%.dbg.o: %.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -g -DDEBUG -c $< -o $@
+$(B)/%.o: %.cu
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
 ifeq ($(NO_CUDA),1)
-engine: $(HOST_SRCS) src/engine/gpu_stub.cpp
-	$(CXX) $(CXXFLAGS) $^ -o $@
-engine.debug: $(HOST_SRCS) src/engine/gpu_stub.cpp
-	$(CXX) $(CXXFLAGS) -g -DDEBUG $^ -o $@
+engine: $(HOST_O) $(B)/src/driver/main.o $(B)/src/engine/gpu_stub.o
+	$(CXX) -pthread $^ -o $@
+engine.debug: $(HOST_DBG_O) $(B)/src/driver/main.dbg.o $(B)/src/engine/gpu_stub.dbg.o
+	$(CXX) -pthread $^ -o $@
 else
-engine: $(HOST_SRCS) $(KERNEL_SRCS) $(RUNTIME_SRCS)
-	$(NVCC) $(NVFLAGS) $^ -o $@ -lcudart
-engine.debug: $(HOST_SRCS) $(KERNEL_SRCS) $(RUNTIME_SRCS)
-	$(NVCC) $(NVFLAGS) -g -DDEBUG $^ -o $@ -lcudart
+engine: $(HOST_O) $(B)/src/driver/main.o $(KERNEL_O) $(ENGINE_O)
+	$(NVCC) $(SM_FLAGS) $^ -o $@ -lcudart -lpthread
+engine.debug: $(HOST_DBG_O) $(B)/src/driver/main.dbg.o $(KERNEL_O) $(ENGINE_O)
+	$(NVCC) $(SM_FLAGS) $^ -o $@ -lcudart -lpthread
 endif
 
 # Shared objects loaded by the Python package through ctypes.
 libs: $(LIBDIR)/libdmlp_cpu.so $(LIBDIR)/libdmlp_knn.so
 
-$(LIBDIR)/libdmlp_cpu.so: src/cpu/cpu_backends.cpp src/driver/io.cpp src/cpu/c_api.cpp
-	mkdir -p $(LIBDIR)
-	$(CXX) $(CXXFLAGS) -shared $^ -o $@
+$(LIBDIR)/libdmlp_cpu.so: $(B)/src/cpu/cpu_backends.o $(B)/src/driver/io.o $(B)/src/cpu/c_api.o
+	@mkdir -p $(LIBDIR)
+	$(CXX) -shared -pthread $^ -o $@
 
-$(LIBDIR)/libdmlp_knn.so: $(KERNEL_SRCS) $(wildcard src/runtime/*.cu)
-	mkdir -p $(LIBDIR)
-	$(NVCC) $(NVFLAGS) -shared $^ -o $@ -lcudart
+$(LIBDIR)/libdmlp_knn.so: $(KERNEL_O)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(SM_FLAGS) -shared $^ -o $@ -lcudart
 
 tools: tools/dmlp-gen
-tools/dmlp-gen: tools/dmlp_gen.cpp src/driver/io.cpp
-	$(CXX) $(CXXFLAGS) $^ -o $@
+tools/dmlp-gen: $(B)/tools/dmlp_gen.o $(B)/src/driver/io.o
+	$(CXX) -pthread $^ -o $@
 
 clean:
-	rm -rf engine engine.debug $(LIBDIR)/*.so tools/dmlp-gen outputs/tmp.*
+	rm -rf $(B) engine engine.debug $(LIBDIR)/*.so tools/dmlp-gen outputs/tmp.*
+
+-include $(shell find $(B) -name '*.d' 2>/dev/null)

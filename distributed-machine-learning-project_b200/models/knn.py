@@ -1,0 +1,120 @@
+"""The k-NN classifier: the engine's one "model" (reference: Engine::KNN, engine.h:6-12).
+
+``KNNClassifier`` runs the whole reference job on one B200: host (pinned)
+arrays -> async H2D -> pack -> tcgen05 filter GEMM with fused top-k -> exact
+fp64 re-rank -> vote + checksum -> D2H.  Queries the filter cannot certify, and
+problems outside the fused path's envelope (k > 24, tiny shapes), run on the
+direct fp64 kernel instead; the answer is bit-identical either way.
+"""
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from ..ops import cuda as K
+
+
+@dataclass
+class KNNResult:
+    label: torch.Tensor      # [q] int32 predicted label
+    checksum: torch.Tensor   # [q] int64 holding the uint64 bit pattern
+    ids: torch.Tensor        # [q, kmax] int32 neighbour ids (-1 padded) or None
+    dist: torch.Tensor       # [q, kmax] float64 distances or None
+    flagged: int = 0         # queries that took the exact fallback
+    path: str = ""
+
+    def checksums_u64(self):
+        return self.checksum.cpu().numpy().view(np.uint64)
+
+
+def _as_device(x, dtype, device, non_blocking=True):
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(np.ascontiguousarray(x))
+    if x.dtype != dtype:
+        x = x.to(dtype)
+    if x.device != device:
+        x = x.to(device, non_blocking=non_blocking)
+    return x.contiguous()
+
+
+def choose_path(n, q, a, kmax, mode="auto"):
+    """fused | exact.  The fused path needs kmax within the epilogue's list capacity."""
+    if mode in ("fused", "exact"):
+        if mode == "fused" and kmax > K.FUSED_MAX_K:
+            raise ValueError(f"fused path supports k <= {K.FUSED_MAX_K}, got {kmax}")
+        return mode
+    if kmax > K.FUSED_MAX_K or n < 1 or q < 1:
+        return "exact"
+    # tiny jobs: one tensor-core tile is mostly padding, go direct
+    if n * q * max(a, 1) < (1 << 22):
+        return "exact"
+    return "fused"
+
+
+class KNNClassifier:
+    def __init__(self, device=None, mode="auto", want_lists=False):
+        self.device = torch.device(device if device is not None else "cuda")
+        self.mode = mode
+        self.want_lists = want_lists
+        self.data = self.labels = None
+
+    def fit(self, data, labels):
+        """Make the labelled points resident on the device (fp64, row-major)."""
+        self.data = _as_device(data, torch.float64, self.device)
+        self.labels = _as_device(labels, torch.int32, self.device)
+        return self
+
+    def classify(self, queries, k, kmax=None, id_base=0):
+        """Classify `queries` ([q, a]) asking k[i] neighbours each."""
+        with torch.cuda.device(self.device):
+            qd = _as_device(queries, torch.float64, self.device)
+            if kmax is None:
+                kh = k if isinstance(k, np.ndarray) else (k.cpu().numpy() if torch.is_tensor(k) else np.asarray(k))
+                kmax = int(max(1, kh.max())) if kh.size else 1
+            kd = _as_device(k, torch.int32, self.device)
+            n, a = self.data.shape
+            q = qd.shape[0]
+            if q == 0:
+                e = torch.empty(0, dtype=torch.int32, device=self.device)
+                return KNNResult(e, torch.empty(0, dtype=torch.int64, device=self.device), None, None, 0, "empty")
+            path = choose_path(n, q, a, kmax, self.mode)
+            flagged = 0
+            if path == "fused":
+                od, oi, ol, flags, nflag = K.knn_local(qd, kd, self.data, self.labels, kmax, id_base)
+                label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
+                flagged = int(nflag.item())  # the only host sync of the call
+                if flagged:
+                    rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)
+                    K.exact(qd, self.data, self.labels, kd, kmax, id_base, rows, out=(od, oi, ol))
+                    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
+            else:
+                od, oi, ol = K.exact(qd, self.data, self.labels, kd, kmax, id_base)
+                if kmax <= 1024:
+                    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
+                else:
+                    label, checksum, ids, dist = _finalize_host(od, oi, ol, kd, self.device)
+            return KNNResult(label, checksum, ids, dist, flagged, path)
+
+
+def _finalize_host(od, oi, ol, kd, device):
+    """Vote + checksum on the host for k beyond the device merge capacity."""
+    from ..ops import cpu
+    ids, labels, kk = oi.cpu().numpy(), ol.cpu().numpy(), kd.cpu().numpy()
+    q = ids.shape[0]
+    out_label = np.empty(q, np.int32)
+    out_sum = np.empty(q, np.uint64)
+    for i in range(q):
+        kq = max(int(kk[i]), 0)
+        labs = labels[i, :kq][ids[i, :kq] >= 0]
+        if labs.size:
+            vals, counts = np.unique(labs, return_counts=True)
+            out_label[i] = vals[counts == counts.max()].max()
+        else:
+            out_label[i] = -1
+        out_sum[i] = cpu.result_checksum(int(out_label[i]), ids[i, :kq])
+    return (torch.from_numpy(out_label).to(device), torch.from_numpy(out_sum.view(np.int64)).to(device), oi, od)
+
+
+def knn(data, labels, queries, k, device=None, mode="auto", want_lists=False):
+    """One-shot job, the call the reference driver makes (common.cpp:126)."""
+    return KNNClassifier(device, mode, want_lists).fit(data, labels).classify(queries, k)

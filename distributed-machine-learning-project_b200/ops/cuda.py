@@ -1,0 +1,217 @@
+"""sm_100a ops (ctypes over libdmlp_knn.so) on torch CUDA tensors.
+
+Each wrapper launches on the current torch CUDA stream and never falls back to
+PyTorch math: if the library is missing or a launch fails, it raises.
+"""
+import ctypes as C
+
+import torch
+
+from .._native import knn_lib
+
+STATS_BYTES = 32
+KP = 32          # keys kept per (query, chunk) by the fused epilogue
+FUSED_MAX_K = 24  # largest k sent to the fused path: each chunk list keeps 32 keys and the
+#                   certified survivor set needs head-room above k
+
+_ready = False
+_vp, _i, _i64, _u64, _sz, _dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_size_t, C.c_double
+
+
+def _lib():
+    global _ready
+    lib = knn_lib()
+    if not _ready:
+        lib.dmlp_last_error.restype = C.c_char_p
+        lib.dmlp_device_info.argtypes = [C.POINTER(_i)] * 3
+        lib.dmlp_stats_reset.argtypes = [_vp, _vp]
+        lib.dmlp_stats_update.argtypes = [_vp, _i64, _vp, _vp]
+        lib.dmlp_pack.argtypes = [_vp, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]
+        lib.dmlp_topk_plan.argtypes = [_i, _i, _i, _i, C.POINTER(_i * 8)]
+        lib.dmlp_dist_topk.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]
+        lib.dmlp_rerank.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
+                                    _vp, _vp, _vp, _vp, _vp, _vp]
+        lib.dmlp_exact_workspace_bytes.argtypes = [_i, _i]
+        lib.dmlp_exact_workspace_bytes.restype = _sz
+        lib.dmlp_exact.argtypes = [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]
+        lib.dmlp_finalize.argtypes = [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]
+        lib.dmlp_synth_attrs.argtypes = [_vp, _i64, _i, _i64, _dbl, _dbl, _u64, _u64, _vp]
+        lib.dmlp_synth_labels.argtypes = [_vp, _i64, _i64, _i, _u64, _vp]
+        lib.dmlp_synth_k.argtypes = [_vp, _i64, _i64, _i, _i, _u64, _vp]
+        lib.dmlp_knn_local_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.dmlp_knn_local_workspace_bytes.restype = _sz
+        lib.dmlp_knn_local.argtypes = [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _vp, _vp, _vp, _vp,
+                                       _vp, _vp]
+        _ready = True
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError("dmlp_knn: " + _lib().dmlp_last_error().decode())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def pad64(a):
+    return (max(a, 1) + 63) // 64 * 64
+
+
+_sm_cache = {}
+
+
+def sm_count():
+    dev = torch.cuda.current_device()
+    if dev not in _sm_cache:
+        sm, ma, mi = _i(), _i(), _i()
+        _check(_lib().dmlp_device_info(C.byref(sm), C.byref(ma), C.byref(mi)))
+        _sm_cache[dev] = sm.value
+    return _sm_cache[dev]
+
+
+def new_stats(device=None):
+    """A zeroed 32-byte stats block (as 4 float64 words), reset on the device."""
+    st = torch.empty(4, dtype=torch.float64, device=device or "cuda")
+    _check(_lib().dmlp_stats_reset(_p(st), _stream()))
+    return st
+
+
+def stats_reset(st):
+    _check(_lib().dmlp_stats_reset(_p(st), _stream()))
+
+
+def stats_update(src, st):
+    _check(_lib().dmlp_stats_update(_p(src), src.numel(), _p(st), _stream()))
+
+
+def pack(src, rng, maxima=None, out=None):
+    """fp64 [rows, a] -> (fp16 [rows, a_pad], norm2 [rows], errn [rows])."""
+    rows, a = src.shape
+    a_pad = pad64(a)
+    if out is None:
+        out = (torch.empty((rows, a_pad), dtype=torch.float16, device=src.device),
+               torch.empty(rows, dtype=torch.float32, device=src.device),
+               torch.empty(rows, dtype=torch.float32, device=src.device))
+    h, n2, en = out
+    _check(_lib().dmlp_pack(_p(src), rows, a, a_pad, _p(rng), _p(h), _p(n2), _p(en), _p(maxima), _stream()))
+    return h, n2, en
+
+
+def topk_plan(q, n, a_pad, sms=None):
+    arr = (_i * 8)()
+    _check(_lib().dmlp_topk_plan(q, n, a_pad, sms or sm_count(), C.byref(arr)))
+    keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp"]
+    return dict(zip(keys, list(arr)[:7]))
+
+
+def dist_topk(qh, xh, xnorm2, cand=None, sms=None):
+    """Filter GEMM + fused top-k.  Returns uint64-as-int64 keys [q, chunks, kp]."""
+    q, a_pad = qh.shape
+    n = xh.shape[0]
+    plan = topk_plan(q, n, a_pad, sms)
+    if cand is None:
+        cand = torch.empty((q, plan["chunks"], plan["kp"]), dtype=torch.int64, device=qh.device)
+    _check(_lib().dmlp_dist_topk(_p(qh), _p(xh), _p(xnorm2), q, n, a_pad, sms or sm_count(), _p(cand), _stream()))
+    return cand
+
+
+def rerank(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, id_base, kmax, out=None):
+    q, chunks, kp = cand.shape
+    n, a = x_attrs.shape
+    dev = cand.device
+    if out is None:
+        out = (torch.empty((q, kmax), dtype=torch.float64, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev),
+               torch.empty(q, dtype=torch.int32, device=dev),
+               torch.zeros(1, dtype=torch.int32, device=dev))
+    od, oi, ol, flags, nflag = out
+    _check(_lib().dmlp_rerank(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
+                              _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax,
+                              _p(od), _p(oi), _p(ol), _p(flags), _p(nflag), _stream()))
+    return od, oi, ol, flags, nflag
+
+
+def exact_workspace_bytes(n, batch):
+    return int(_lib().dmlp_exact_workspace_bytes(n, batch))
+
+
+def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=None, workspace=None):
+    """Direct fp64 brute force for all query rows, or the subset `query_rows` (int32)."""
+    q, a = q_attrs.shape
+    n = x_attrs.shape[0]
+    dev = q_attrs.device
+    count = q if query_rows is None else int(query_rows.numel())
+    if out is None:
+        out = (torch.empty((q, kmax), dtype=torch.float64, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev))
+    if workspace is None:
+        batch = max(1, min(count, (256 << 20) // max(1, 24 * n)))
+        workspace = torch.empty(exact_workspace_bytes(n, batch), dtype=torch.uint8, device=dev)
+    od, oi, ol = out
+    _check(_lib().dmlp_exact(_p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(query_rows), count, n, a, id_base,
+                             kmax, _p(od), _p(oi), _p(ol), _p(workspace), workspace.numel(), _stream()))
+    return od, oi, ol
+
+
+def finalize(dist, ids, labels, k, want_lists=False):
+    """Merge [sources, q, kmax] exact lists, vote, checksum."""
+    sources, q, kmax = dist.shape
+    dev = dist.device
+    out_label = torch.empty(q, dtype=torch.int32, device=dev)
+    out_sum = torch.empty(q, dtype=torch.int64, device=dev)  # uint64 bit pattern
+    out_id = torch.empty((q, kmax), dtype=torch.int32, device=dev) if want_lists else None
+    out_dist = torch.empty((q, kmax), dtype=torch.float64, device=dev) if want_lists else None
+    _check(_lib().dmlp_finalize(_p(dist), _p(ids), _p(labels), q * kmax, sources, q, kmax, _p(k), _p(out_label),
+                                _p(out_sum), _p(out_id), _p(out_dist), _stream()))
+    return out_label, out_sum, out_id, out_dist
+
+
+def synth_attrs(rows, a, row_base, lo, hi, seed, stream_id, device="cuda", out=None):
+    if out is None:
+        out = torch.empty((rows, a), dtype=torch.float64, device=device)
+    _check(_lib().dmlp_synth_attrs(_p(out), rows, a, row_base, lo, hi, seed, stream_id, _stream()))
+    return out
+
+
+def synth_labels(rows, row_base, num_labels, seed, device="cuda"):
+    out = torch.empty(rows, dtype=torch.int32, device=device)
+    _check(_lib().dmlp_synth_labels(_p(out), rows, row_base, num_labels, seed, _stream()))
+    return out
+
+
+def synth_k(rows, row_base, min_k, max_k, seed, device="cuda"):
+    out = torch.empty(rows, dtype=torch.int32, device=device)
+    _check(_lib().dmlp_synth_k(_p(out), rows, row_base, min_k, max_k, seed, _stream()))
+    return out
+
+
+def knn_local_workspace_bytes(q, n, a):
+    return int(_lib().dmlp_knn_local_workspace_bytes(q, n, a, sm_count()))
+
+
+def knn_local(q_attrs, k, x_attrs, x_labels, kmax, id_base=0, rng=None, workspace=None, out=None):
+    """stats -> pack -> dist_topk -> rerank in one call on caller-provided scratch."""
+    q, a = q_attrs.shape
+    n = x_attrs.shape[0]
+    dev = q_attrs.device
+    if workspace is None:
+        workspace = torch.empty(knn_local_workspace_bytes(q, n, a), dtype=torch.uint8, device=dev)
+    if out is None:
+        out = (torch.empty((q, kmax), dtype=torch.float64, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev),
+               torch.empty((q, kmax), dtype=torch.int32, device=dev),
+               torch.empty(q, dtype=torch.int32, device=dev),
+               torch.zeros(1, dtype=torch.int32, device=dev))
+    od, oi, ol, flags, nflag = out
+    _check(_lib().dmlp_knn_local(_p(q_attrs), _p(k), q, _p(x_attrs), _p(x_labels), n, a, id_base, kmax, _p(rng),
+                                 _p(workspace), workspace.numel(), _p(od), _p(oi), _p(ol), _p(flags), _p(nflag),
+                                 _stream()))
+    return od, oi, ol, flags, nflag

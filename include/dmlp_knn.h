@@ -1,0 +1,92 @@
+/* C ABI of libdmlp_knn.so: the sm_100a kernels of the k-NN engine.
+ *
+ * Every function takes device pointers and a CUDA stream (as void*; NULL is the
+ * default stream), launches asynchronously on that stream and returns 0, or a
+ * negative value after recording a message for dmlp_last_error().  Nothing here
+ * allocates device memory: callers own all buffers, including scratch.
+ *
+ * Pipeline (one shard of datapoints x one block of queries):
+ *   stats -> pack (queries, data) -> dist_topk -> rerank [-> exact for flagged]
+ *   -> finalize (merges the lists of all data shards, votes, checksums)
+ */
+#ifndef DMLP_KNN_C_H_
+#define DMLP_KNN_C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char *dmlp_last_error(void);
+
+/* Device properties the planners need: SM count and compute capability. */
+int dmlp_device_info(int *sm_count, int *cc_major, int *cc_minor);
+
+/* ---- K7 pack_norms (reference: engine.cpp:79-96, 154-184 repack) -------------
+ * A "stats" block is 32 bytes of device memory: {double max(-v), double max(v),
+ * float max row norm, float max row error norm}.  The first two fields merge
+ * across ranks with one MAX all-reduce over two doubles. */
+#define DMLP_STATS_BYTES 32
+int dmlp_stats_reset(void *stats, void *stream);
+int dmlp_stats_update(const double *src, int64_t count, void *stats, void *stream);
+/* src [rows][a] fp64 -> dst [rows][a_pad] fp16 (centred, scaled by a power of two
+ * derived from `range`), norm2[rows] = ||x^||^2, errn[rows] >= ||x' - x^||.
+ * a_pad must be a multiple of 64.  Row maxima accumulate into `maxima` (may be
+ * NULL). */
+int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16,
+              float *norm2, float *errn, void *maxima, void *stream);
+
+/* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
+ * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, 0}.  The
+ * candidate buffer holds q * chunks * kp 64-bit keys. */
+int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]);
+int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
+                   int num_sms, uint64_t *cand, void *stream);
+
+/* ---- K2 exact_rerank (reference: engine.cpp:12-18 semantics) ------------------
+ * Writes, per query, kmax slots of (dist, id, label): the exact local top-k in
+ * (distance asc, id desc) order, padded with (1e18, -1, -1).  flags[q] != 0 marks
+ * a query the filter could not certify; *num_flagged counts them. */
+int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
+                const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
+                const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax,
+                double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *stream);
+
+/* ---- exact fp64 brute force (reference: engine.cpp:233-257 as written) --------
+ * Processes `count` queries: rows query_rows[0..count) or, with NULL, rows
+ * 0..count.  Scratch comes from the caller. */
+size_t dmlp_exact_workspace_bytes(int n, int batch);
+int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels, const int *k,
+               const int *query_rows, int count, int n, int a, int id_base, int kmax, double *out_dist,
+               int *out_id, int *out_label, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---- K5 owner merge + K6 vote/checksum (reference: engine.cpp:289-347) --------
+ * dist/id/label: `sources` arrays of [q][kmax], source_stride elements apart. */
+int dmlp_finalize(const double *dist, const int *id, const int *label, int64_t source_stride, int sources,
+                  int q, int kmax, const int *k, int *out_label, uint64_t *out_checksum, int *out_id,
+                  double *out_dist, void *stream);
+
+/* ---- K8 synthetic_fill (reference: generate_input.py:13-21) -------------------
+ * stream_id 0 = data attributes, 2 = query attributes. */
+int dmlp_synth_attrs(double *dst, int64_t rows, int a, int64_t row_base, double lo, double hi, uint64_t seed,
+                     uint64_t stream_id, void *stream);
+int dmlp_synth_labels(int *dst, int64_t rows, int64_t row_base, int num_labels, uint64_t seed, void *stream);
+int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k, uint64_t seed, void *stream);
+
+/* ---- whole local pipeline on caller-provided scratch --------------------------
+ * stats -> pack -> dist_topk -> rerank for one data shard and one query block.
+ * `range` may be NULL (the range is then computed from these two arrays) or a
+ * stats block already merged across ranks.  Scratch layout is private; size it
+ * with dmlp_knn_local_workspace_bytes. */
+size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms);
+int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels,
+                   int n, int a, int id_base, int kmax, const void *range, void *workspace,
+                   size_t workspace_bytes, double *out_dist, int *out_id, int *out_label, int *flags,
+                   int *num_flagged, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMLP_KNN_C_H_ */

@@ -1,0 +1,137 @@
+// Internal launch interface of the sm_100a kernels (host side).  The public C
+// ABI in include/dmlp_knn.h is a thin layer over these.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+
+namespace dmlp {
+namespace k {
+
+/// Device-resident range and row maxima produced by the stats / pack kernels.
+/// `neg_lo` and `hi` are both max-reductions so one MAX all-reduce merges ranks.
+struct PackStats {
+  double neg_lo;   ///< max over all values of -v
+  double hi;       ///< max over all values of v
+  float max_norm;  ///< max over packed rows of ||x^||
+  float max_err;   ///< max over packed rows of ||x' - x^||
+};
+
+struct ScaleParams {
+  double center;
+  double scale;  ///< power of two
+};
+
+/// Midpoint centring and power-of-two scaling so that |(v - c) * s| < 2^15.
+__host__ __device__ inline ScaleParams derive_scale(double neg_lo, double hi) {
+  ScaleParams p;
+  p.center = 0.0;
+  p.scale = 1.0;
+  double lo = -neg_lo;
+  if (!(lo <= hi)) return p;  // empty or NaN range
+  p.center = 0.5 * lo + 0.5 * hi;
+  double m = fmax(hi - p.center, p.center - lo);
+  if (!(m > 0.0) || !isfinite(m)) return p;
+  int e = ilogb(m);  // m in [2^e, 2^(e+1))
+  int sh = 14 - e;
+  if (sh > 1000) sh = 1000;
+  if (sh < -1000) sh = -1000;
+  p.scale = scalbn(1.0, sh);
+  return p;
+}
+
+/// Work decomposition of the filter GEMM (host decides, kernel follows).
+struct TopkPlan {
+  int q_rows;      ///< queries
+  int n;           ///< local datapoints
+  int a_pad;       ///< fp16 row length (multiple of 8)
+  int kp;          ///< candidates kept per (query, chunk)
+  int m_blocks;    ///< ceil(q_rows / 128)
+  int n_tiles;     ///< ceil(n / 256)
+  int group_m;     ///< row blocks that share one wave
+  int chunks;      ///< column chunks per query (lists per query)
+  int k_blocks;    ///< ceil(a_pad / 64)
+  int grid;        ///< persistent CTAs
+};
+TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms);
+
+// pack.cu
+int launch_stats_reset(PackStats *st, cudaStream_t s);
+int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t s);
+int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
+                float *norm2, float *errn, PackStats *maxima, cudaStream_t s);
+
+// dist_topk.cu  (cand: [q_rows][chunks][kp] keys, ascending per list)
+int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
+                     unsigned long long *cand, cudaStream_t s);
+
+// rerank.cu
+struct RerankArgs {
+  const unsigned long long *cand;  // [q][chunks][kp]
+  int chunks, kp;
+  const double *q_attrs;           // [q][a] original fp64
+  const double *x_attrs;           // [n][a]
+  const int *x_labels;             // [n]
+  const int *k;                    // [q]
+  const float *q_norm2;            // [q]  ||q^||^2 (scaled units)
+  const float *q_errn;             // [q]  ||dq||
+  const PackStats *range;          // scale parameters
+  const PackStats *x_maxima;       // max ||x^||, max ||dx|| over the local shard
+  int q, n, a, a_pad;
+  int id_base;                     // global id of local row 0
+  int kmax;                        // output stride
+  double *out_dist;                // [q][kmax]
+  int *out_id;                     // [q][kmax] global ids, -1 padded
+  int *out_label;                  // [q][kmax]
+  int *flags;                      // [q] 0 = certified, else reason bits
+  int *num_flagged;                // device counter
+};
+int launch_rerank(const RerankArgs &args, cudaStream_t s);
+
+// finalize.cu: merge `sources` sorted lists per query, vote, checksum
+struct FinalizeArgs {
+  const double *dist;   // [sources][q][kmax]
+  const int *id;        // [sources][q][kmax]
+  const int *label;     // [sources][q][kmax]
+  long long source_stride;  // elements between sources (>= q*kmax)
+  int sources, q, kmax;
+  const int *k;         // [q]
+  int *out_label;       // [q]
+  unsigned long long *out_checksum;  // [q]
+  int *out_id;          // [q][kmax] optional (nullptr to skip)
+  double *out_dist;     // [q][kmax] optional
+};
+int launch_finalize(const FinalizeArgs &args, cudaStream_t s);
+
+// exact.cu: brute-force fp64 path (any k), used for tiny problems, large k and
+// queries the filter could not certify
+struct ExactArgs {
+  const double *q_attrs;  // [q][a]
+  const double *x_attrs;  // [n][a]
+  const int *x_labels;
+  const int *k;           // [q]
+  const int *query_rows;  // optional [count] subset of query rows (nullptr = all q rows)
+  int count;              // number of queries to process
+  int n, a, id_base, kmax;
+  double *out_dist;       // [q][kmax] (written at the query's own row)
+  int *out_id;
+  int *out_label;
+  void *workspace;        // >= exact_workspace_bytes()
+  size_t workspace_bytes;
+};
+size_t exact_workspace_bytes(int n, int batch);
+int launch_exact(const ExactArgs &args, cudaStream_t s);
+
+// synth.cu
+int launch_synth_attrs(double *dst, long long rows, int a, long long row_base, double lo, double hi,
+                       unsigned long long seed, unsigned long long stream_id, cudaStream_t s);
+int launch_synth_labels(int *dst, long long rows, long long row_base, int num_labels, unsigned long long seed,
+                        cudaStream_t s);
+int launch_synth_k(int *dst, long long rows, long long row_base, int min_k, int max_k,
+                   unsigned long long seed, cudaStream_t s);
+
+}  // namespace k
+}  // namespace dmlp

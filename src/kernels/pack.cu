@@ -1,0 +1,147 @@
+// K7 pack_norms: fp64 rows -> centred, scaled fp16 rows + row norms + rounding-error norms.
+//
+// Replaces the reference's AoS->SoA repack before its scatters (reference:
+// engine.cpp:79-96, 154-184).  The fp16 rows feed the tcgen05 filter GEMM; the
+// norms turn its dot products into distances; the error norms make the filter
+// certifiable (see rerank.cu).  A value v is mapped to x' = (v - c) * s with c
+// the midpoint of the global value range and s a power of two chosen so that
+// |x'| < 2^15 (fp16 keeps 11 significant bits at every magnitude up to 65504).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace dmlp {
+namespace k {
+
+__device__ __forceinline__ void atomic_max_double(double *addr, double v) {
+  unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
+  unsigned long long old = *a, assumed;
+  do {
+    assumed = old;
+    if (__longlong_as_double(static_cast<long long>(assumed)) >= v) break;
+    old = atomicCAS(a, assumed, static_cast<unsigned long long>(__double_as_longlong(v)));
+  } while (assumed != old);
+}
+
+__global__ void stats_reset_kernel(PackStats *st) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    st->neg_lo = -INFINITY;
+    st->hi = -INFINITY;
+    st->max_norm = 0.f;
+    st->max_err = 0.f;
+  }
+}
+
+// Range of all values: max(-v) and max(v), reduced per block then one atomic.
+__global__ void __launch_bounds__(256) stats_kernel(const double *__restrict__ src, long long count,
+                                                    PackStats *st) {
+  double hi = -INFINITY, nlo = -INFINITY;
+  long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
+    double v = src[i];
+    hi = fmax(hi, v);
+    nlo = fmax(nlo, -v);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    hi = fmax(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, o));
+    nlo = fmax(nlo, __shfl_xor_sync(0xFFFFFFFFu, nlo, o));
+  }
+  __shared__ double s_hi[8], s_nlo[8];
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_hi[warp] = hi; s_nlo[warp] = nlo; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) { hi = fmax(hi, s_hi[w]); nlo = fmax(nlo, s_nlo[w]); }
+    atomic_max_double(&st->hi, hi);
+    atomic_max_double(&st->neg_lo, nlo);
+  }
+}
+
+// One warp per row, grid-stride over rows.  Lanes own adjacent column pairs so
+// the fp16 stores are 4-byte, 128 B per warp instruction.
+__global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ src, long long rows, int a,
+                                                   int a_pad, const PackStats *__restrict__ range,
+                                                   __half *__restrict__ dst, float *__restrict__ norm2,
+                                                   float *__restrict__ errn, PackStats *maxima) {
+  const ScaleParams sp = derive_scale(range->neg_lo, range->hi);
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const bool vec_ok = (a & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  float my_max_norm = 0.f, my_max_err = 0.f;
+
+  for (long long r = warp_global; r < rows; r += warps_total) {
+    const double *in = src + r * a;
+    __half2 *out = reinterpret_cast<__half2 *>(dst + r * a_pad);
+    double nsum = 0.0, esum = 0.0, xsum = 0.0;
+#pragma unroll 4
+    for (int c = lane * 2; c < a_pad; c += 64) {
+      double v0 = 0.0, v1 = 0.0;
+      bool in0 = c < a, in1 = c + 1 < a;
+      if (vec_ok && in1) {
+        double2 t = *reinterpret_cast<const double2 *>(in + c);
+        v0 = t.x; v1 = t.y;
+      } else {
+        if (in0) v0 = in[c];
+        if (in1) v1 = in[c + 1];
+      }
+      double x0 = in0 ? __dmul_rn(__dsub_rn(v0, sp.center), sp.scale) : 0.0;
+      double x1 = in1 ? __dmul_rn(__dsub_rn(v1, sp.center), sp.scale) : 0.0;
+      __half h0 = __double2half(x0), h1 = __double2half(x1);
+      double f0 = static_cast<double>(__half2float(h0)), f1 = static_cast<double>(__half2float(h1));
+      double d0 = x0 - f0, d1 = x1 - f1;
+      nsum += f0 * f0 + f1 * f1;
+      esum += d0 * d0 + d1 * d1;
+      xsum += x0 * x0 + x1 * x1;
+      out[c >> 1] = __halves2half2(h0, h1);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      nsum += __shfl_xor_sync(0xFFFFFFFFu, nsum, o);
+      esum += __shfl_xor_sync(0xFFFFFFFFu, esum, o);
+      xsum += __shfl_xor_sync(0xFFFFFFFFu, xsum, o);
+    }
+    if (lane == 0) {
+      // error norm: fp16 rounding plus the fp64 rounding of (v - c) * s, rounded up
+      double e = (sqrt(esum) + 4.0 * 2.220446049250313e-16 * sqrt(xsum)) * (1.0 + 1e-9);
+      float ef = __double2float_ru(e);
+      float nf = __double2float_rn(nsum);
+      norm2[r] = nf;
+      errn[r] = ef;
+      my_max_norm = fmaxf(my_max_norm, __double2float_ru(sqrt(nsum)));
+      my_max_err = fmaxf(my_max_err, ef);
+    }
+  }
+  if (lane == 0 && maxima != nullptr) {
+    // non-negative floats order like their bit patterns
+    atomicMax(reinterpret_cast<int *>(&maxima->max_norm), __float_as_int(my_max_norm));
+    atomicMax(reinterpret_cast<int *>(&maxima->max_err), __float_as_int(my_max_err));
+  }
+}
+
+int launch_stats_reset(PackStats *st, cudaStream_t s) {
+  stats_reset_kernel<<<1, 32, 0, s>>>(st);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t s) {
+  if (count <= 0) return 0;
+  long long blocks = (count + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  stats_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, count, st);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
+                float *norm2, float *errn, PackStats *maxima, cudaStream_t s) {
+  if (rows <= 0) return 0;
+  DMLP_REQUIRE(a_pad >= a && (a_pad % 8) == 0, "pack: a_pad must be a multiple of 8 and >= a");
+  long long blocks = (rows + 7) / 8;  // 8 warps per block
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  pack_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn, maxima);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace k
+}  // namespace dmlp

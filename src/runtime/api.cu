@@ -1,0 +1,203 @@
+// C ABI over the kernel launchers.  See include/dmlp_knn.h.
+#include "dmlp_knn.h"
+
+#include <string>
+
+#include "../kernels/common.cuh"
+#include "../kernels/kernels.h"
+
+namespace dmlp {
+namespace k {
+namespace {
+thread_local std::string g_error;
+}
+void set_error(const std::string &msg) { g_error = msg; }
+const char *get_error() { return g_error.c_str(); }
+}  // namespace k
+}  // namespace dmlp
+
+using namespace dmlp::k;
+
+static_assert(sizeof(PackStats) <= DMLP_STATS_BYTES, "stats block size");
+
+namespace {
+inline cudaStream_t st(void *s) { return static_cast<cudaStream_t>(s); }
+inline size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+inline int pad64(int a) { return (a + 63) / 64 * 64; }
+
+int current_sm_count(int *out) {
+  int dev = 0;
+  DMLP_CUDA_OK(cudaGetDevice(&dev));
+  DMLP_CUDA_OK(cudaDeviceGetAttribute(out, cudaDevAttrMultiProcessorCount, dev));
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+const char *dmlp_last_error(void) { return get_error(); }
+
+int dmlp_device_info(int *sm_count, int *cc_major, int *cc_minor) {
+  int dev = 0;
+  DMLP_CUDA_OK(cudaGetDevice(&dev));
+  DMLP_CUDA_OK(cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, dev));
+  DMLP_CUDA_OK(cudaDeviceGetAttribute(cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+  DMLP_CUDA_OK(cudaDeviceGetAttribute(cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+  return 0;
+}
+
+int dmlp_stats_reset(void *stats, void *stream) {
+  return launch_stats_reset(static_cast<PackStats *>(stats), st(stream));
+}
+
+int dmlp_stats_update(const double *src, int64_t count, void *stats, void *stream) {
+  return launch_stats(src, count, static_cast<PackStats *>(stats), st(stream));
+}
+
+int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
+              float *errn, void *maxima, void *stream) {
+  DMLP_REQUIRE(a_pad % 64 == 0, "pack: a_pad must be a multiple of 64");
+  return launch_pack(src, rows, a, a_pad, static_cast<const PackStats *>(range), static_cast<__half *>(dst_fp16),
+                     norm2, errn, static_cast<PackStats *>(maxima), st(stream));
+}
+
+int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]) {
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+  plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.chunks;
+  plan_out[4] = p.k_blocks; plan_out[5] = p.grid; plan_out[6] = p.kp; plan_out[7] = 0;
+  return 0;
+}
+
+int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
+                   int num_sms, uint64_t *cand, void *stream) {
+  if (num_sms <= 0)
+    if (int rc = current_sm_count(&num_sms)) return rc;
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+  return launch_dist_topk(static_cast<const __half *>(q_fp16), static_cast<const __half *>(x_fp16), x_norm2, p,
+                          reinterpret_cast<unsigned long long *>(cand), st(stream));
+}
+
+int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
+                const int *x_labels, const int *k, const float *q_norm2, const float *q_errn, const void *range,
+                const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax, double *out_dist,
+                int *out_id, int *out_label, int *flags, int *num_flagged, void *stream) {
+  RerankArgs r;
+  r.cand = reinterpret_cast<const unsigned long long *>(cand);
+  r.chunks = chunks; r.kp = kp;
+  r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
+  r.q_norm2 = q_norm2; r.q_errn = q_errn;
+  r.range = static_cast<const PackStats *>(range);
+  r.x_maxima = static_cast<const PackStats *>(x_maxima);
+  r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
+  r.out_dist = out_dist; r.out_id = out_id; r.out_label = out_label;
+  r.flags = flags; r.num_flagged = num_flagged;
+  return launch_rerank(r, st(stream));
+}
+
+size_t dmlp_exact_workspace_bytes(int n, int batch) { return exact_workspace_bytes(n, batch); }
+
+int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels, const int *k,
+               const int *query_rows, int count, int n, int a, int id_base, int kmax, double *out_dist,
+               int *out_id, int *out_label, void *workspace, size_t workspace_bytes, void *stream) {
+  ExactArgs e;
+  e.q_attrs = q_attrs; e.x_attrs = x_attrs; e.x_labels = x_labels; e.k = k; e.query_rows = query_rows;
+  e.count = count; e.n = n; e.a = a; e.id_base = id_base; e.kmax = kmax;
+  e.out_dist = out_dist; e.out_id = out_id; e.out_label = out_label;
+  e.workspace = workspace; e.workspace_bytes = workspace_bytes;
+  return launch_exact(e, st(stream));
+}
+
+int dmlp_finalize(const double *dist, const int *id, const int *label, int64_t source_stride, int sources, int q,
+                  int kmax, const int *k, int *out_label, uint64_t *out_checksum, int *out_id, double *out_dist,
+                  void *stream) {
+  FinalizeArgs f;
+  f.dist = dist; f.id = id; f.label = label; f.source_stride = source_stride;
+  f.sources = sources; f.q = q; f.kmax = kmax; f.k = k;
+  f.out_label = out_label; f.out_checksum = reinterpret_cast<unsigned long long *>(out_checksum);
+  f.out_id = out_id; f.out_dist = out_dist;
+  return launch_finalize(f, st(stream));
+}
+
+int dmlp_synth_attrs(double *dst, int64_t rows, int a, int64_t row_base, double lo, double hi, uint64_t seed,
+                     uint64_t stream_id, void *stream) {
+  return launch_synth_attrs(dst, rows, a, row_base, lo, hi, seed, stream_id, st(stream));
+}
+int dmlp_synth_labels(int *dst, int64_t rows, int64_t row_base, int num_labels, uint64_t seed, void *stream) {
+  return launch_synth_labels(dst, rows, row_base, num_labels, seed, st(stream));
+}
+int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k, uint64_t seed, void *stream) {
+  return launch_synth_k(dst, rows, row_base, min_k, max_k, seed, st(stream));
+}
+
+// ---- whole local pipeline ------------------------------------------------------
+namespace {
+struct LocalLayout {
+  size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, total;
+  int a_pad, chunks;
+};
+LocalLayout local_layout(int q, int n, int a, int num_sms) {
+  LocalLayout L;
+  L.a_pad = pad64(a > 0 ? a : 1);
+  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, num_sms);
+  L.chunks = p.chunks;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
+  L.stats = take(DMLP_STATS_BYTES);
+  L.q_stats = take(DMLP_STATS_BYTES);
+  L.xh = take(size_t(n) * L.a_pad * 2);
+  L.qh = take(size_t(q) * L.a_pad * 2);
+  L.xn = take(size_t(n) * 4);
+  L.xe = take(size_t(n) * 4);
+  L.qn = take(size_t(q) * 4);
+  L.qe = take(size_t(q) * 4);
+  L.cand = take(size_t(q) * p.chunks * 32 * 8);
+  L.total = off;
+  return L;
+}
+}  // namespace
+
+size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms) {
+  if (num_sms <= 0) num_sms = 148;
+  return local_layout(q, n, a, num_sms).total;
+}
+
+int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels, int n,
+                   int a, int id_base, int kmax, const void *range, void *workspace, size_t workspace_bytes,
+                   double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *stream) {
+  int sms = 0;
+  if (int rc = current_sm_count(&sms)) return rc;
+  LocalLayout L = local_layout(q, n, a, sms);
+  DMLP_REQUIRE(workspace_bytes >= L.total, "knn_local: workspace too small");
+  DMLP_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "knn_local: workspace must be 256-byte aligned");
+  unsigned char *w = static_cast<unsigned char *>(workspace);
+  cudaStream_t s = st(stream);
+  PackStats *stats = reinterpret_cast<PackStats *>(w + L.stats);
+  PackStats *q_stats = reinterpret_cast<PackStats *>(w + L.q_stats);
+  if (int rc = launch_stats_reset(stats, s)) return rc;
+  if (int rc = launch_stats_reset(q_stats, s)) return rc;
+  const PackStats *rng = static_cast<const PackStats *>(range);
+  if (rng == nullptr) {
+    if (int rc = launch_stats(x_attrs, static_cast<long long>(n) * a, stats, s)) return rc;
+    if (int rc = launch_stats(q_attrs, static_cast<long long>(q) * a, stats, s)) return rc;
+    rng = stats;
+  }
+  __half *xh = reinterpret_cast<__half *>(w + L.xh), *qh = reinterpret_cast<__half *>(w + L.qh);
+  float *xn = reinterpret_cast<float *>(w + L.xn), *xe = reinterpret_cast<float *>(w + L.xe);
+  float *qn = reinterpret_cast<float *>(w + L.qn), *qe = reinterpret_cast<float *>(w + L.qe);
+  unsigned long long *cand = reinterpret_cast<unsigned long long *>(w + L.cand);
+  // the row maxima live in the stats blocks (range fields of q_stats stay unused)
+  if (int rc = launch_pack(x_attrs, n, a, L.a_pad, rng, xh, xn, xe, stats, s)) return rc;
+  if (int rc = launch_pack(q_attrs, q, a, L.a_pad, rng, qh, qn, qe, q_stats, s)) return rc;
+  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms);
+  if (int rc = launch_dist_topk(qh, xh, xn, p, cand, s)) return rc;
+  if (num_flagged) DMLP_CUDA_OK(cudaMemsetAsync(num_flagged, 0, sizeof(int), s));
+  RerankArgs r;
+  r.cand = cand; r.chunks = p.chunks; r.kp = 32;
+  r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
+  r.q_norm2 = qn; r.q_errn = qe; r.range = rng; r.x_maxima = stats;
+  r.q = q; r.n = n; r.a = a; r.a_pad = L.a_pad; r.id_base = id_base; r.kmax = kmax;
+  r.out_dist = out_dist; r.out_id = out_id; r.out_label = out_label; r.flags = flags; r.num_flagged = num_flagged;
+  return launch_rerank(r, s);
+}
+
+}  // extern "C"

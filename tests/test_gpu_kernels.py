@@ -1,0 +1,165 @@
+"""GPU numerics: every kernel against the CPU oracle / a plain fp32-fp64 PyTorch restatement."""
+import numpy as np
+import pytest
+import torch
+
+from dmlp_b200.ops import cpu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from dmlp_b200.ops import cuda
+    return cuda
+
+
+def _dev(x):
+    return torch.from_numpy(x).cuda()
+
+
+def test_synth_matches_host_twin(K):
+    data, labels, queries, k = cpu.synth(300, 40, 37, -100.0, 100.0, 2, 9, 5, seed=9)
+    d = K.synth_attrs(300, 37, 0, -100.0, 100.0, 9, 0)
+    q = K.synth_attrs(40, 37, 0, -100.0, 100.0, 9, 2)
+    assert (d.cpu().numpy() == data).all() and (q.cpu().numpy() == queries).all()
+    assert (K.synth_labels(300, 0, 5, 9).cpu().numpy() == labels).all()
+    assert (K.synth_k(40, 0, 2, 9, 9).cpu().numpy() == k).all()
+    # shards are addressable independently
+    part = K.synth_attrs(100, 37, 150, -100.0, 100.0, 9, 0)
+    assert (part.cpu().numpy() == data[150:250]).all()
+
+
+def test_pack_against_torch(K):
+    data, *_ = cpu.synth(257, 1, 70, -50.0, 150.0, 1, 1, 2, seed=3)
+    x = _dev(data)
+    st = K.new_stats()
+    K.stats_update(x, st)
+    h, n2, en = K.pack(x, st, st)
+    torch.cuda.synchronize()
+    neg_lo, hi = st[:2].cpu().tolist()
+    assert -neg_lo == data.min() and hi == data.max()
+    c = 0.5 * data.min() + 0.5 * data.max()
+    m = max(data.max() - c, c - data.min())
+    s = 2.0 ** (14 - int(np.floor(np.log2(m))))
+    xp = (x - c) * s
+    ref_h = xp.to(torch.float16)
+    assert h.shape == (257, 128)
+    assert torch.equal(h[:, :70], ref_h) and (h[:, 70:] == 0).all()
+    ref_n2 = (ref_h.double() ** 2).sum(1)
+    torch.testing.assert_close(n2.double(), ref_n2, rtol=1e-6, atol=0)
+    ref_err = ((xp - ref_h.double()) ** 2).sum(1).sqrt()
+    assert (en.double() >= ref_err).all() and (en.double() <= ref_err * 1.001 + 1e-6).all()
+    maxima = st.view(torch.float32)[4:6].cpu().tolist()
+    assert abs(maxima[0] - ref_n2.sqrt().max().item()) <= 1e-3 * maxima[0]
+
+
+@pytest.mark.parametrize("q,n,a", [(128, 256, 64), (130, 1000, 100), (300, 5000, 256), (64, 300, 8)])
+def test_dist_topk_against_torch(K, q, n, a):
+    """Fused GEMM + top-k: each chunk list must equal the 32 smallest scores of its
+    column range, scores computed in fp32 from the same fp16 operands."""
+    data, _, queries, _ = cpu.synth(n, q, a, -100.0, 100.0, 1, 1, 2, seed=5)
+    x, qq = _dev(data), _dev(queries)
+    st = K.new_stats()
+    K.stats_update(x, st)
+    K.stats_update(qq, st)
+    xh, xn, _ = K.pack(x, st, st)
+    qh, _, _ = K.pack(qq, st)
+    cand = K.dist_topk(qh, xh, xn)
+    torch.cuda.synchronize()
+    plan = K.topk_plan(q, n, xh.shape[1])
+    chunks, nt = plan["chunks"], plan["n_tiles"]
+    assert cand.shape == (q, chunks, 32)
+    scores = xn[None, :].double() - 2.0 * (qh.double() @ xh.double().T)   # [q, n], fp64 reference
+    keys = cand.cpu().numpy().view(np.uint64)
+    ids = (keys & np.uint64(0xFFFFFFFF)).astype(np.int64)
+    valid = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
+    sc = scores.cpu().numpy()
+    mag = np.abs(sc).max()
+    for c in range(chunks):
+        lo, hi = (c * nt // chunks) * 256, min(((c + 1) * nt // chunks) * 256, n)
+        want_cnt = min(32, hi - lo)
+        assert (valid[:, c, :].sum(1) == want_cnt).all()
+        for r in range(0, q, max(1, q // 16)):
+            got = ids[r, c, :want_cnt]
+            assert ((got >= lo) & (got < hi)).all() and len(set(got.tolist())) == want_cnt
+            kth = np.partition(sc[r, lo:hi], want_cnt - 1)[want_cnt - 1]
+            # everything kept is within fp32 accumulation error of the true 32 best
+            assert (sc[r, got] <= kth + 1e-5 * mag).all()
+            assert (np.diff(sc[r, got]) >= -1e-5 * mag).all()  # emitted ascending
+
+
+@pytest.mark.parametrize("n,q,a,kmin,kmax,lo,hi", [
+    (5000, 300, 64, 1, 16, -100.0, 100.0), (2049, 257, 33, 3, 24, 0.0, 10.0), (900, 129, 7, 1, 5, -1.0, 1.0),
+    (40000, 256, 128, 16, 16, -100.0, 100.0), (300, 130, 256, 1, 8, 0.0, 1000.0)])
+def test_knn_local_matches_oracle(K, n, q, a, kmin, kmax, lo, hi):
+    data, labels, queries, k = cpu.synth(n, q, a, lo, hi, kmin, kmax, 7, seed=13)
+    want_label, want_sum, want_ids, want_dist, off = cpu.knn(data, labels, queries, k)
+    od, oi, ol, flags, nflag = K.knn_local(_dev(queries), _dev(k), _dev(data), _dev(labels), kmax)
+    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], _dev(k), True)
+    torch.cuda.synchronize()
+    assert int(nflag.item()) == 0, f"filter failed to certify {int(nflag.item())} queries"
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+    assert (label.cpu().numpy() == want_label).all()
+    got_ids, got_dist = ids.cpu().numpy(), dist.cpu().numpy()
+    for i in range(q):
+        assert (got_ids[i, :k[i]] == want_ids[off[i]:off[i + 1]]).all()
+        assert (got_dist[i, :k[i]] == want_dist[off[i]:off[i + 1]]).all()   # bit-identical fp64
+
+
+@pytest.mark.parametrize("n,q,a,kmin,kmax", [(1000, 50, 5, 1, 70), (37, 20, 3, 37, 37), (5000, 33, 16, 100, 300)])
+def test_exact_path_matches_oracle(K, n, q, a, kmin, kmax):
+    data, labels, queries, k = cpu.synth(n, q, a, -5.0, 5.0, kmin, kmax, 3, seed=21)
+    want_label, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    km = int(k.max())
+    od, oi, ol = K.exact(_dev(queries), _dev(data), _dev(labels), _dev(k), km)
+    label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], _dev(k))
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+    assert (label.cpu().numpy() == want_label).all()
+
+
+def test_duplicates_tie_break_on_gpu(K):
+    rng = np.random.default_rng(0)
+    base = rng.uniform(-1, 1, (50, 16))
+    data = np.concatenate([base, base, base])          # every point three times
+    labels = rng.integers(0, 4, 150).astype(np.int32)
+    queries = rng.uniform(-1, 1, (140, 16))
+    k = np.full(140, 7, np.int32)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    for fn in ("fused", "exact"):
+        if fn == "fused":
+            od, oi, ol, flags, nflag = K.knn_local(_dev(queries), _dev(k), _dev(data), _dev(labels), 7)
+            rows = torch.nonzero(flags).flatten().to(torch.int32)
+            if rows.numel():
+                K.exact(_dev(queries), _dev(data), _dev(labels), _dev(k), 7, 0, rows, out=(od, oi, ol))
+        else:
+            od, oi, ol = K.exact(_dev(queries), _dev(data), _dev(labels), _dev(k), 7)
+        _, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], _dev(k))
+        assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all(), fn
+
+
+def test_finalize_merges_shards(K):
+    data, labels, queries, k = cpu.synth(3000, 200, 24, -100.0, 100.0, 2, 12, 5, seed=17)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    parts = []
+    for lo, hi in [(0, 1100), (1100, 1900), (1900, 3000)]:
+        od, oi, ol, flags, nflag = K.knn_local(_dev(queries), _dev(k), _dev(data[lo:hi]), _dev(labels[lo:hi]), 12, lo)
+        assert int(nflag.item()) == 0
+        parts.append((od, oi, ol))
+    dist = torch.stack([p[0] for p in parts])
+    ids = torch.stack([p[1] for p in parts])
+    labs = torch.stack([p[2] for p in parts])
+    _, checksum, _, _ = K.finalize(dist, ids, labs, _dev(k))
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+
+
+def test_model_api_all_paths(K):
+    from dmlp_b200.models import knn
+    data, labels, queries, k = cpu.synth(6000, 300, 48, -100.0, 100.0, 1, 20, 6, seed=4)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    for mode in ("auto", "fused", "exact"):
+        res = knn(data, labels, queries, k, mode=mode)
+        assert (res.checksums_u64() == want_sum).all(), mode
+    big_k = np.full(300, 64, np.int32)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, big_k)
+    assert (knn(data, labels, queries, big_k).checksums_u64() == want_sum).all()
