@@ -36,11 +36,17 @@ int main(int argc, char **argv) {
       spec.n = std::atoll(argv[++i]);
       spec.q = std::atoll(argv[++i]);
       spec.a = std::atoi(argv[++i]);
+      auto numeric = [&](int j) {  // negative numbers are values, "--x" is a flag
+        if (j >= argc) return false;
+        char *endp = nullptr;
+        std::strtod(argv[j], &endp);
+        return endp != argv[j] && *endp == '\0';
+      };
       double *dopt[] = {&spec.lo, &spec.hi};
-      for (int j = 0; j < 2 && i + 1 < argc && argv[i + 1][0] != '-' ; ++j) *dopt[j] = std::atof(argv[++i]);
+      for (int j = 0; j < 2 && numeric(i + 1); ++j) *dopt[j] = std::atof(argv[++i]);
       int *iopt[] = {&spec.min_k, &spec.max_k, &spec.num_labels};
-      for (int j = 0; j < 3 && i + 1 < argc && argv[i + 1][0] != '-'; ++j) *iopt[j] = std::atoi(argv[++i]);
-      if (i + 1 < argc && argv[i + 1][0] != '-') spec.seed = std::strtoull(argv[++i], nullptr, 10);
+      for (int j = 0; j < 3 && numeric(i + 1); ++j) *iopt[j] = std::atoi(argv[++i]);
+      if (numeric(i + 1)) spec.seed = std::strtoull(argv[++i], nullptr, 10);
     } else {
       std::fprintf(stderr, "usage: %s [--aos] [--json] [--synth N Q A [lo hi minK maxK labels seed]] < input\n", argv[0]);
       return 2;

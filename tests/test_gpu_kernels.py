@@ -45,7 +45,12 @@ def test_pack_against_torch(K):
     xp = (x - c) * s
     ref_h = xp.to(torch.float16)
     assert h.shape == (257, 128)
-    assert torch.equal(h[:, :70], ref_h) and (h[:, 70:] == 0).all()
+    # the kernel rounds fp64 -> fp16 directly; torch may round through fp32 first, so
+    # compare as "at least as close to the exact value, and almost always equal"
+    got = h[:, :70].double()
+    assert ((got - xp).abs() <= (ref_h.double() - xp).abs()).all() and (h[:, 70:] == 0).all()
+    assert (got != ref_h.double()).float().mean().item() < 1e-3
+    ref_h = h[:, :70]
     ref_n2 = (ref_h.double() ** 2).sum(1)
     torch.testing.assert_close(n2.double(), ref_n2, rtol=1e-6, atol=0)
     ref_err = ((xp - ref_h.double()) ** 2).sum(1).sqrt()
