@@ -86,6 +86,28 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
                    size_t workspace_bytes, double *out_dist, int *out_id, int *out_label, int *flags,
                    int *num_flagged, void *stream);
 
+/* ---- the same pipeline for callers that cannot allocate -------------------------
+ * (No counterpart in the reference: it has no GPU code and no scratch buffers.)
+ * Same inputs, outputs and results as dmlp_knn_local with range == NULL, but the
+ * scratch is a fixed DMLP_STATIC_SCRATCH_BYTES array built into the library, so
+ * the call needs no workspace and performs no cudaMalloc/cudaFree or any other
+ * allocating call.  It exists for hosts that must not allocate once running:
+ * plug-ins inside another program's CUDA context, real-time or certified loops
+ * where allocation latency and failure are unacceptable, processes confined to a
+ * memory reservation they do not control.
+ *  - Limit: problems whose dmlp_knn_local_workspace_bytes() exceeds
+ *    DMLP_STATIC_SCRATCH_BYTES are refused (-3, message in dmlp_last_error()).
+ *  - Every GPU that loads the library keeps the array reserved until exit.
+ *  - The first call on each device looks up the array's device address; make
+ *    that call at start-up, before any stream capture on that device.
+ *  - All calls share the one array, which keeps the previous call's contents;
+ *    the call re-initialises what it accumulates into.  Calls that overlap on
+ *    the same GPU (different streams or threads) race on it: serialise them. */
+#define DMLP_STATIC_SCRATCH_BYTES (64u << 20)
+int dmlp_knn_local_static(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels,
+                          int n, int a, int id_base, int kmax, double *out_dist, int *out_id, int *out_label,
+                          int *flags, int *num_flagged, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
