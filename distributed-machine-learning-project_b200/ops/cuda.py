@@ -106,8 +106,8 @@ def pack(src, rng, maxima=None, out=None):
 def topk_plan(q, n, a_pad, sms=None):
     arr = (_i * 8)()
     _check(_lib().dmlp_topk_plan(q, n, a_pad, sms or sm_count(), C.byref(arr)))
-    keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp"]
-    return dict(zip(keys, list(arr)[:7]))
+    keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp", "cluster"]
+    return dict(zip(keys, list(arr)[:8]))
 
 
 def dist_topk(qh, xh, xnorm2, cand=None, sms=None):
@@ -191,6 +191,40 @@ def synth_k(rows, row_base, min_k, max_k, seed, device="cuda"):
     out = torch.empty(rows, dtype=torch.int32, device=device)
     _check(_lib().dmlp_synth_k(_p(out), rows, row_base, min_k, max_k, seed, _stream()))
     return out
+
+
+class GatherArgs(C.Structure):
+    _fields_ = [("world", _i), ("rank", _i), ("slice_rows", _i), ("a", _i), ("epoch", C.c_uint32),
+                ("peer_base", _vp * 8), ("off_qh", _u64), ("off_q64", _u64), ("off_qn", _u64), ("off_qe", _u64),
+                ("off_k", _u64), ("off_pack_flags", _u64), ("rb_count", _vp), ("status", _vp),
+                ("timeout_seconds", _dbl)]
+
+
+class ScatterArgs(C.Structure):
+    _fields_ = [("world", _i), ("rank", _i), ("slice_rows", _i), ("peer_base", _vp * 8), ("off_dist", _u64),
+                ("off_id", _u64), ("off_label", _u64)]
+
+
+def dist_topk_gather(xh, xnorm2, cand, gather):
+    """K4: filter GEMM whose query operand is all-gathered from the peers inside the kernel."""
+    lib = _lib()
+    lib.dmlp_dist_topk_gather.argtypes = [_vp, _vp, _i, _i, _i, _vp, C.POINTER(GatherArgs), _vp]
+    n, a_pad = xh.shape
+    _check(lib.dmlp_dist_topk_gather(_p(xh), _p(xnorm2), n, a_pad, sm_count(), _p(cand), C.byref(gather), _stream()))
+    return cand
+
+
+def rerank_scatter(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, id_base, kmax, flags, nflag,
+                   scatter):
+    """K5: exact re-rank whose k-lists are stored straight into the owners' receive buffers."""
+    lib = _lib()
+    lib.dmlp_rerank_scatter.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
+                                        _vp, _vp, C.POINTER(ScatterArgs), _vp]
+    q, chunks, kp = cand.shape
+    n, a = x_attrs.shape
+    _check(lib.dmlp_rerank_scatter(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
+                                   _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax, _p(flags),
+                                   _p(nflag), C.byref(scatter), _stream()))
 
 
 def knn_local_workspace_bytes(q, n, a):

@@ -39,7 +39,7 @@ int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *ran
               float *norm2, float *errn, void *maxima, void *stream);
 
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
- * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, 0}.  The
+ * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
  * candidate buffer holds q * chunks * kp 64-bit keys. */
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]);
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
@@ -85,6 +85,64 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
                    int n, int a, int id_base, int kmax, const void *range, void *workspace,
                    size_t workspace_bytes, double *out_dist, int *out_id, int *out_label, int *flags,
                    int *num_flagged, void *stream);
+
+/* ---- symmetric peer memory + device-side signalling (replaces the reference's MPI
+ * layer, engine.cpp:33-35, 73-131, 147-209, 282-284) ---------------------------
+ * Unlike the kernel entry points above, alloc/open/close/free are set-up calls
+ * that do allocate and map memory; call them once, outside the hot path.
+ * A flag array is `world` 32-bit words inside a symmetric buffer: word s of rank
+ * d's array is written only by rank s. */
+int dmlp_symm_alloc(size_t bytes, void **ptr, unsigned char handle_out[64]);   /* cudaMalloc + zero + IPC export */
+int dmlp_symm_open(const unsigned char handle[64], void **ptr);                /* map a peer's buffer */
+int dmlp_symm_close(void *ptr);
+int dmlp_symm_free(void *ptr);
+/* peer_flag_ptrs: device array of `world` pointers, entry d = rank d's flag array
+ * as mapped here.  Stores `value` into word `my_rank` of every rank's array after
+ * a system-scope fence (so all earlier work on this stream is visible first). */
+int dmlp_symm_signal(void *peer_flag_ptrs, int world, int my_rank, uint32_t value, void *stream);
+/* Spins (on the device, in stream order) until every word of the local flag array
+ * has reached `value`; gives up after timeout_seconds and writes 1 + the index of
+ * the late rank to *status (device int, may be NULL). */
+int dmlp_symm_wait(const void *local_flags, int world, uint32_t value, double timeout_seconds, int *status,
+                   void *stream);
+
+/* ---- fused cross-GPU steps ------------------------------------------------------
+ * K4, all-gather -> GEMM (reference: the row/column MPI_Bcast of an operand shard,
+ * engine.cpp:129-131, 207-209, followed by the distance loop): every rank packs
+ * the `slice_rows` queries it owns into its symmetric buffer (at off_qh, rows
+ * [rank * slice_rows, ...)), signals pack_flags, and calls dmlp_dist_topk_gather.
+ * A communication warp in every GEMM CTA pulls the other ranks' packed rows
+ * through the peer mappings just ahead of the tiles that use them, then pulls the
+ * fp64 rows (off_q64), norms (off_qn, off_qe) and k (off_k) for the re-rank.
+ * rb_count: `world * slice_rows / 128` local counters, zeroed once at set-up;
+ * epoch: 1, 2, 3, ... per step.  slice_rows must be a multiple of 256. */
+typedef struct dmlp_gather_args {
+  int world, rank, slice_rows, a;
+  uint32_t epoch;
+  void *peer_base[8];
+  uint64_t off_qh, off_q64, off_qn, off_qe, off_k, off_pack_flags;
+  uint32_t *rb_count;
+  int *status;            /* device int: set non-zero if a peer never showed up */
+  double timeout_seconds;
+} dmlp_gather_args;
+int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, uint64_t *cand,
+                          const dmlp_gather_args *g, void *stream);
+
+/* K5, GEMM/top-k -> reduce-scatter of k-lists (reference: MPI_Gather of k-lists to
+ * row 0 + re-select, engine.cpp:283-308): dmlp_rerank with its outputs redirected
+ * into the owner's receive buffers [world][slice_rows][kmax] (off_dist, off_id,
+ * off_label inside the owner's symmetric buffer), written through NVLink from the
+ * kernel.  Follow with dmlp_symm_signal; the owner runs dmlp_symm_wait and
+ * dmlp_finalize over its receive buffers. */
+typedef struct dmlp_scatter_args {
+  int world, rank, slice_rows;
+  void *peer_base[8];
+  uint64_t off_dist, off_id, off_label;
+} dmlp_scatter_args;
+int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
+                        const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
+                        const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
+                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *stream);
 
 /* ---- the same pipeline for callers that cannot allocate -------------------------
  * (No counterpart in the reference: it has no GPU code and no scratch buffers.)

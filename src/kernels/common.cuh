@@ -122,6 +122,52 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
       : "memory");
 }
 
+// Multicast variant: the tile lands at the same shared-memory offset of every CTA
+// in `cta_mask`, and each of those CTAs' barriers (same offset) receives the bytes.
+__device__ __forceinline__ void tma_load_2d_mcast(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0,
+                                                  int c1, uint16_t cta_mask, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      ".L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5, %6;"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1),
+      "h"(cta_mask), "l"(policy)
+      : "memory");
+}
+// Pull a tile from HBM into L2 ahead of the load that will consume it.
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap *map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// L2 eviction-priority policies for TMA loads (createpolicy encodings).
+constexpr uint64_t kL2EvictNormal = 0x1000000000000000ULL;
+constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ULL;
+constexpr uint64_t kL2EvictLast = 0x14F0000000000000ULL;
+__device__ __forceinline__ void tma_load_2d_hint(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0,
+                                                 int c1, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1),
+      "l"(policy)
+      : "memory");
+}
+
 // ---------------------------------------------------------------------------
 // PTX: tcgen05 (5th-generation tensor cores, accumulators in tensor memory)
 // ---------------------------------------------------------------------------
@@ -156,6 +202,13 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
+}
+// Same, arriving on the barrier at this offset in every CTA of `cta_mask`.
+__device__ __forceinline__ void umma_commit_mcast(uint64_t *bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(smem_u32(bar)), "h"(cta_mask)
+      : "memory");
 }
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives lane
 // (base_lane + i), columns [col, col + 32).

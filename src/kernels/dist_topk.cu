@@ -21,6 +21,7 @@
 // sweep; each (query, chunk) pair emits its `kp` best (score, row) keys sorted
 // ascending.  Rows a chunk dropped all score >= the last key it kept, which is
 // what rerank.cu needs to certify the filter.
+#include <cstdlib>
 #include <limits>
 
 #include "common.cuh"
@@ -42,12 +43,6 @@ constexpr int CAP = 64;   // list capacity between compactions
 constexpr int THREADS = 192;
 constexpr int EPI_THREADS = 128;
 
-constexpr int OFF_A = 0;
-constexpr int OFF_B = OFF_A + STAGES * A_BYTES;
-constexpr int OFF_LIST = OFF_B + STAGES * B_BYTES;
-constexpr int OFF_XN = OFF_LIST + BM * CAP * 8;
-constexpr int OFF_BAR = OFF_XN + 2 * BN * 4;
-constexpr int SMEM_BYTES = OFF_BAR + 128 + 1024;  // + alignment slack
 
 struct Item {
   int m;
@@ -55,15 +50,17 @@ struct Item {
   int tile_begin, tile_end;
 };
 
-__device__ __forceinline__ bool get_item(const TopkPlan &p, int t, Item *it) {
-  const int per_group = p.group_m * p.chunks;
+// Work items are enumerated per cluster: item t names a cluster row (`cluster`
+// consecutive 128-query blocks, one per CTA of the cluster) and a chunk.
+__device__ __forceinline__ bool get_item(const TopkPlan &p, int t, int cta_rank, Item *it) {
+  const int per_group = p.group_mc * p.chunks;
   const int g = t / per_group;
   const int rem = t - g * per_group;
-  const int m0 = g * p.group_m;
-  const int gm = min(p.group_m, p.m_blocks - m0);
+  const int m0 = g * p.group_mc;
+  const int gm = min(p.group_mc, p.mc_blocks - m0);
   if (gm <= 0 || rem >= gm * p.chunks) return false;
   const int c = rem / gm;
-  it->m = m0 + (rem - c * gm);
+  it->m = ((m0 + (rem - c * gm) + p.rot) % p.mc_blocks) * p.cluster + cta_rank;  // may be a phantom block past m_blocks
   it->chunk = c;
   it->tile_begin = static_cast<int>(static_cast<long long>(c) * p.n_tiles / p.chunks);
   it->tile_end = static_cast<int>(static_cast<long long>(c + 1) * p.n_tiles / p.chunks);
@@ -120,12 +117,121 @@ __device__ __forceinline__ void compact_row(unsigned long long *row_keys, int ro
   __syncwarp();
 }
 
+// Smem layout.  `STG` pipeline stages of (query tile, data tile[ half]) precede the
+// per-row candidate lists, the staged data norms and the barriers.
+template <int STG, int B_STAGE_BYTES>
+struct Layout {
+  static constexpr int kOffA = 0;
+  static constexpr int kOffB = kOffA + STG * A_BYTES;
+  static constexpr int kOffList = kOffB + STG * B_STAGE_BYTES;
+  static constexpr int kOffXn = kOffList + BM * CAP * 8;
+  static constexpr int kOffBar = kOffXn + 2 * BN * 4;
+  static constexpr int kBytes = kOffBar + 256 + 1024;  // + alignment slack
+};
+using Layout1 = Layout<STAGES, B_BYTES>;            // one CTA per 128 x 256 tile
+constexpr int STAGES2 = 4;
+using Layout2 = Layout<STAGES2, B_BYTES / 2>;       // CTA pair per 256 x 256 tile
+
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+
+// Epilogue shared by both kernels: 4 warps, one query row per thread, 256
+// accumulator columns per tile.  `tempty_addr` is the barrier (cluster address)
+// on which each warp signals that the accumulator stage may be overwritten.
+template <bool REMOTE_EMPTY>
+__device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *smem, int off_list, int off_xn,
+                                              uint32_t tmem_base, uint64_t *tfull_bar, uint64_t *tempty_bar,
+                                              int cluster_id, int num_clusters, int cta_rank, int total_items,
+                                              const float *__restrict__ xnorm2,
+                                              unsigned long long *__restrict__ cand) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int quarter = warp & 3;              // tensor-memory lane quarter this warp may read
+  const int row_in_tile = quarter * 32 + lane;
+  unsigned long long *lists = reinterpret_cast<unsigned long long *>(smem + off_list);
+  unsigned long long *my_keys = lists + row_in_tile * CAP;
+  float *xn_all = reinterpret_cast<float *>(smem + off_xn);
+  const int e_tid = threadIdx.x - 64;
+  const float inf = std::numeric_limits<float>::infinity();
+  int cnt = 0;
+  float tau = inf;
+  uint32_t acc_it = 0;
+
+  for (int t = cluster_id; t < total_items; t += num_clusters) {
+    Item it;
+    if (!get_item(plan, t, cta_rank, &it)) continue;
+    for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
+      const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
+      float *xn = xn_all + acc * BN;
+      for (int i = e_tid; i < BN; i += EPI_THREADS) {
+        const int col = tile * BN + i;
+        xn[i] = col < plan.n ? __ldg(xnorm2 + col) : inf;
+      }
+      named_barrier_sync(1, EPI_THREADS);
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        // make room for up to 32 appends per row
+        __syncwarp();
+        unsigned need = __ballot_sync(0xFFFFFFFFu, cnt > CAP - 32);
+        while (need) {
+          const int r = __ffs(need) - 1;
+          need &= need - 1;
+          compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, nullptr);
+        }
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c0, v);
+        tmem_ld_wait();
+        float s[32];
+        float mn = inf;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          s[j] = fmaf(-2.0f, __uint_as_float(v[j]), xn[c0 + j]);
+          mn = fminf(mn, s[j]);
+        }
+        if (mn < tau) {
+          const int id0 = tile * BN + c0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (s[j] < tau) {
+              my_keys[(cnt + row_in_tile) & (CAP - 1)] = make_key(s[j], id0 + j);
+              ++cnt;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (REMOTE_EMPTY) mbar_arrive_remote(smem_u32(&tempty_bar[acc]) & 0xFEFFFFFFu);  // leader CTA's barrier
+        else mbar_arrive(&tempty_bar[acc]);
+      }
+    }
+    // flush this (row block, chunk): sorted kp keys per row
+    __syncwarp();
+    for (int r = 0; r < 32; ++r) {
+      const long long qrow = static_cast<long long>(it.m) * BM + quarter * 32 + r;
+      unsigned long long *out = qrow < plan.q_rows ? cand + (qrow * plan.chunks + it.chunk) * KP : nullptr;
+      compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, out);
+    }
+    cnt = 0;
+    tau = inf;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Variant 1: one CTA per 128 x 256 tile (tcgen05 cta_group::1); optional cluster
+// whose CTAs share each data tile through TMA multicast.
+// ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(THREADS, 1)
 dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
                  const float *__restrict__ xnorm2, const TopkPlan plan, unsigned long long *__restrict__ cand) {
+  using L = Layout1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + OFF_BAR);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kOffBar);
   uint64_t *full_bar = bars;                  // [STAGES]
   uint64_t *empty_bar = bars + STAGES;        // [STAGES]
   uint64_t *tfull_bar = bars + 2 * STAGES;    // [2]
@@ -134,6 +240,11 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int csize = plan.cluster;
+  const int cta_rank = csize > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int cluster_id = blockIdx.x / csize;
+  const int num_clusters = gridDim.x / csize;
+  const uint16_t cmask = static_cast<uint16_t>((1u << csize) - 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_q);
@@ -143,7 +254,7 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     if (lane == 0) {
       for (int s = 0; s < STAGES; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], 1);
+        mbar_init(&empty_bar[s], csize);  // every CTA of the cluster must release the stage
       }
       for (int s = 0; s < 2; ++s) {
         mbar_init(&tfull_bar[s], 1);
@@ -157,26 +268,37 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (csize > 1) cluster_sync_all();  // peers' barriers must exist before multicast traffic starts
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int per_group = plan.group_m * plan.chunks;
-  const int total_items = ((plan.m_blocks + plan.group_m - 1) / plan.group_m) * per_group;
+  const int per_group = plan.group_mc * plan.chunks;
+  const int total_items = ((plan.mc_blocks + plan.group_mc - 1) / plan.group_mc) * per_group;
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_items; t += gridDim.x) {
+      const uint64_t pol_q = plan.hint_q == 2 ? kL2EvictLast : (plan.hint_q == 1 ? kL2EvictFirst : kL2EvictNormal);
+      const uint64_t pol_x = plan.hint_x == 2 ? kL2EvictLast : (plan.hint_x == 1 ? kL2EvictFirst : kL2EvictNormal);
+      const int slice_rows = BN / csize, slice_bytes = slice_rows * BK * 2;
+      for (int t = cluster_id; t < total_items; t += num_clusters) {
         Item it;
-        if (!get_item(plan, t, &it)) continue;
+        if (!get_item(plan, t, cta_rank, &it)) continue;
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             mbar_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
-            tma_load_2d(smem + OFF_A + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM);
-            tma_load_2d(smem + OFF_B + stage * B_BYTES, &tm_x, &full_bar[stage], kb * BK, tile * BN);
+            // query tiles are re-read for every data tile of the sweep: keep them in L2
+            tma_load_2d_hint(smem + L::kOffA + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM, pol_q);
+            if (csize == 1) {
+              tma_load_2d_hint(smem + L::kOffB + stage * B_BYTES, &tm_x, &full_bar[stage], kb * BK, tile * BN, pol_x);
+            } else {
+              // this CTA fetches one slice of the data tile and multicasts it to the cluster
+              tma_load_2d_mcast(smem + L::kOffB + stage * B_BYTES + cta_rank * slice_bytes, &tm_x, &full_bar[stage],
+                                kb * BK, tile * BN + cta_rank * slice_rows, cmask, pol_x);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -189,9 +311,9 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_it = 0;
-      for (int t = blockIdx.x; t < total_items; t += gridDim.x) {
+      for (int t = cluster_id; t < total_items; t += num_clusters) {
         Item it;
-        if (!get_item(plan, t, &it)) continue;
+        if (!get_item(plan, t, cta_rank, &it)) continue;
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
           const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
           mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -200,12 +322,14 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            const uint64_t da = make_smem_desc_sw128(smem_u32(smem + OFF_A + stage * A_BYTES));
-            const uint64_t db = make_smem_desc_sw128(smem_u32(smem + OFF_B + stage * B_BYTES));
+            const uint64_t da = make_smem_desc_sw128(smem_u32(smem + L::kOffA + stage * A_BYTES));
+            const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * B_BYTES));
 #pragma unroll
             for (int kk = 0; kk < BK / 16; ++kk)
               umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
-            umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+            // frees the smem stage (in every CTA of the cluster) once these MMAs retire
+            if (csize == 1) umma_commit(&empty_bar[stage]);
+            else umma_commit_mcast(&empty_bar[stage], cmask);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           umma_commit(&tfull_bar[acc]);      // accumulator complete -> epilogue
@@ -213,85 +337,305 @@ dist_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       }
     }
   } else {
-    // -------------------------------- epilogue --------------------------------
-    const int quarter = warp & 3;              // tensor-memory lane quarter this warp may read
-    const int row_in_tile = quarter * 32 + lane;
-    unsigned long long *lists = reinterpret_cast<unsigned long long *>(smem + OFF_LIST);
-    unsigned long long *my_keys = lists + row_in_tile * CAP;
-    float *xn_all = reinterpret_cast<float *>(smem + OFF_XN);
-    const int e_tid = threadIdx.x - 64;
-    const float inf = std::numeric_limits<float>::infinity();
-    int cnt = 0;
-    float tau = inf;
-    uint32_t acc_it = 0;
-
-    for (int t = blockIdx.x; t < total_items; t += gridDim.x) {
-      Item it;
-      if (!get_item(plan, t, &it)) continue;
-      for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
-        const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
-        float *xn = xn_all + acc * BN;
-        for (int i = e_tid; i < BN; i += EPI_THREADS) {
-          const int col = tile * BN + i;
-          xn[i] = col < plan.n ? __ldg(xnorm2 + col) : inf;
-        }
-        named_barrier_sync(1, EPI_THREADS);
-        mbar_wait(&tfull_bar[acc], acc_phase);
-        tc_fence_after();
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
-          // make room for up to 32 appends per row
-          __syncwarp();
-          unsigned need = __ballot_sync(0xFFFFFFFFu, cnt > CAP - 32);
-          while (need) {
-            const int r = __ffs(need) - 1;
-            need &= need - 1;
-            compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, nullptr);
-          }
-          uint32_t v[32];
-          tmem_ld_32x32(t_row + c0, v);
-          tmem_ld_wait();
-          float s[32];
-          float mn = inf;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            s[j] = fmaf(-2.0f, __uint_as_float(v[j]), xn[c0 + j]);
-            mn = fminf(mn, s[j]);
-          }
-          if (mn < tau) {
-            const int id0 = tile * BN + c0;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (s[j] < tau) {
-                my_keys[(cnt + row_in_tile) & (CAP - 1)] = make_key(s[j], id0 + j);
-                ++cnt;
-              }
-            }
-          }
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      }
-      // flush this (row block, chunk): sorted kp keys per row
-      __syncwarp();
-      for (int r = 0; r < 32; ++r) {
-        const long long qrow = static_cast<long long>(it.m) * BM + quarter * 32 + r;
-        unsigned long long *out =
-            qrow < plan.q_rows ? cand + (qrow * plan.chunks + it.chunk) * KP : nullptr;
-        compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, out);
-      }
-      cnt = 0;
-      tau = inf;
-    }
+    epilogue_loop<false>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
+                         num_clusters, cta_rank, total_items, xnorm2, cand);
   }
 
   tc_fence_before();
   __syncthreads();
+  if (csize > 1) cluster_sync_all();  // no CTA may leave while peers can still signal it
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Variant 2: CTA pair per 256 x 256 tile (tcgen05 cta_group::2).  Each CTA of the
+// pair stages its own 128 query rows and one half (128 rows) of the data tile;
+// the leader CTA issues the MMAs for both, so each SM's shared memory moves
+// half as many operand bytes per flop -- what the 128 B/clk smem port needs for
+// the tensor pipe to run at full rate.  Accumulator rows live in each CTA's own
+// tensor memory, so the epilogue is the same as in variant 1.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_2d_pair(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0,
+                                                 int c1, uint64_t policy) {
+  // completion bytes are credited to the barrier at this offset in the leader CTA
+  const uint32_t leader_bar = smem_u32(bar) & 0xFEFFFFFFu;
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1),
+      "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
+constexpr int THREADS2 = THREADS + 32;  // + one communication warp
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Communication warp (K4): all-gather of the packed query rows, fused into the
+// GEMM.  Rows are taken in the order the tiles will need them; each finished row
+// bumps its block's counter, which the TMA producers poll before touching the
+// block.  Afterwards the fp64 rows, norms and k of the remote slices are pulled
+// for the re-rank kernel (no flags needed: it runs after this kernel).
+__device__ void gather_warp(const TopkPlan &plan, const GatherArgs &ga, int lane) {
+  const int G = gridDim.x, b = blockIdx.x;
+  unsigned ready_mask = 1u << ga.rank;
+  bool dead = false;
+  auto wait_peer = [&](int owner) {
+    if ((ready_mask >> owner) & 1u) return;
+    const unsigned *flag = reinterpret_cast<const unsigned *>(ga.peer_base[ga.rank] + ga.off_pack_flags) + owner;
+    const long long t0 = clock64();
+    while (static_cast<int>(ld_acquire_sys(flag) - ga.epoch) < 0) {
+      if (clock64() - t0 > ga.timeout_cycles) {  // watchdog: report and stop waiting
+        if (lane == 0 && ga.status) atomicExch(ga.status, 100 + owner);
+        dead = true;
+        break;
+      }
+      __nanosleep(100);
+    }
+    ready_mask |= 1u << owner;
+  };
+  const int a_pad = plan.a_pad;
+  const int vec_per_row = a_pad / 8;  // int4 = 8 halves
+  const long long total_rows = static_cast<long long>(plan.mc_blocks) * plan.cluster * BM;
+  for (long long seq = b; seq < total_rows; seq += G) {
+    const int o = static_cast<int>(seq / BM), i = static_cast<int>(seq - static_cast<long long>(o) * BM);
+    const int cr = o / plan.cluster, j = o - cr * plan.cluster;
+    const int m = ((cr + plan.rot) % plan.mc_blocks) * plan.cluster + j;
+    const long long grow = static_cast<long long>(m) * BM + i;
+    const int owner = static_cast<int>(grow / ga.slice_rows);
+    if (owner != ga.rank && owner < ga.world) {
+      wait_peer(owner);
+      if (!dead) {
+        const int4 *src = reinterpret_cast<const int4 *>(ga.peer_base[owner] + ga.off_qh) + grow * vec_per_row;
+        int4 *dst = reinterpret_cast<int4 *>(ga.peer_base[ga.rank] + ga.off_qh) + grow * vec_per_row;
+        for (int v0 = 0; v0 < vec_per_row; v0 += 32 * 8) {
+          int4 tmp[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < vec_per_row) tmp[u] = src[v];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < vec_per_row) dst[v] = tmp[u];
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      atomicAdd(ga.rb_count + m, 1u);
+    }
+  }
+  // fp64 rows + per-query scalars of the remote slices, for the re-rank kernel
+  const long long qp = static_cast<long long>(ga.world) * ga.slice_rows;
+  const bool vec_ok = (ga.a % 2) == 0;
+  for (long long grow = b; grow < qp; grow += G) {
+    const int owner = static_cast<int>(grow / ga.slice_rows);
+    if (owner == ga.rank) continue;
+    wait_peer(owner);
+    if (dead) break;
+    const double *src = reinterpret_cast<const double *>(ga.peer_base[owner] + ga.off_q64) + grow * ga.a;
+    double *dst = reinterpret_cast<double *>(ga.peer_base[ga.rank] + ga.off_q64) + grow * ga.a;
+    if (vec_ok) {
+      const int n2 = ga.a / 2;
+      const double2 *s2 = reinterpret_cast<const double2 *>(src);
+      double2 *d2 = reinterpret_cast<double2 *>(dst);
+      for (int v0 = 0; v0 < n2; v0 += 32 * 8) {
+        double2 tmp[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int v = v0 + u * 32 + lane;
+          if (v < n2) tmp[u] = s2[v];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int v = v0 + u * 32 + lane;
+          if (v < n2) d2[v] = tmp[u];
+        }
+      }
+    } else {
+      for (int v = lane; v < ga.a; v += 32) dst[v] = src[v];
+    }
+    if (lane == 0) {
+      reinterpret_cast<float *>(ga.peer_base[ga.rank] + ga.off_qn)[grow] =
+          reinterpret_cast<const float *>(ga.peer_base[owner] + ga.off_qn)[grow];
+      reinterpret_cast<float *>(ga.peer_base[ga.rank] + ga.off_qe)[grow] =
+          reinterpret_cast<const float *>(ga.peer_base[owner] + ga.off_qe)[grow];
+      reinterpret_cast<int *>(ga.peer_base[ga.rank] + ga.off_k)[grow] =
+          reinterpret_cast<const int *>(ga.peer_base[owner] + ga.off_k)[grow];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(THREADS2, 1)
+dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
+                      const float *__restrict__ xnorm2, const TopkPlan plan,
+                      unsigned long long *__restrict__ cand, const GatherArgs ga) {
+  using L = Layout2;
+  constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of the data tile
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kOffBar);
+  uint64_t *full_bar = bars;                    // [STAGES2]  (the leader's copy is the live one)
+  uint64_t *empty_bar = bars + STAGES2;         // [STAGES2]  per CTA, released by the leader's commits
+  uint64_t *tfull_bar = bars + 2 * STAGES2;     // [2]        per CTA
+  uint64_t *tempty_bar = bars + 2 * STAGES2 + 2;  // [2]      leader's copy collects both epilogues
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES2 + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int cta_rank = static_cast<int>(cluster_ctarank());  // 0 = leader
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_x);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES2; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      for (int s = 0; s < 2; ++s) {
+        mbar_init(&tfull_bar[s], 1);
+        mbar_init(&tempty_bar[s], 8);  // 4 epilogue warps in each CTA of the pair
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int per_group = plan.group_mc * plan.chunks;
+  const int total_items = ((plan.mc_blocks + plan.group_mc - 1) / plan.group_mc) * per_group;
+
+  if (warp == 0) {
+    // ---------------- TMA producer (both CTAs load their own operands) ----------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint64_t pol_q = plan.hint_q == 2 ? kL2EvictLast : (plan.hint_q == 1 ? kL2EvictFirst : kL2EvictNormal);
+      const uint64_t pol_x = plan.hint_x == 2 ? kL2EvictLast : (plan.hint_x == 1 ? kL2EvictFirst : kL2EvictNormal);
+      for (int t = cluster_id; t < total_items; t += num_clusters) {
+        Item it;
+        if (!get_item(plan, t, cta_rank, &it)) continue;
+        if (ga.world > 1) {
+          // the block's packed rows may still be on their way from their owner
+          const unsigned target = ga.epoch * BM;
+          const long long t0 = clock64();
+          while (static_cast<int>(ld_acquire_gpu(ga.rb_count + it.m) - target) < 0) {
+            if (clock64() - t0 > ga.timeout_cycles) {
+              if (ga.status) atomicExch(ga.status, 200);
+              break;
+            }
+            __nanosleep(64);
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
+        }
+        if (plan.prefetch > 0) {
+          // experiment: offset the pairs that sweep the same chunk by a fixed lag
+          const int pos = (it.m >> 1) % plan.group_mc;
+          for (int w = 0; w < pos; ++w) __nanosleep(plan.prefetch);
+        }
+        for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
+          for (int kb = 0; kb < plan.k_blocks; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + BH_BYTES));
+            tma_load_2d_pair(smem + L::kOffA + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM, pol_q);
+            tma_load_2d_pair(smem + L::kOffB + stage * BH_BYTES, &tm_x, &full_bar[stage], kb * BK,
+                             tile * BN + cta_rank * (BN / 2), pol_x);
+            if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer (leader CTA only) ----------------
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(2 * BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t acc_it = 0;
+      for (int t = cluster_id; t < total_items; t += num_clusters) {
+        Item it;
+        if (!get_item(plan, t, cta_rank, &it)) continue;
+        for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
+          const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
+          mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          for (int kb = 0; kb < plan.k_blocks; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t da = make_smem_desc_sw128(smem_u32(smem + L::kOffA + stage * A_BYTES));
+            const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BH_BYTES));
+#pragma unroll
+            for (int kk = 0; kk < BK / 16; ++kk)
+              umma_f16_pair(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+            umma_commit_pair(&empty_bar[stage]);  // frees this stage in both CTAs
+            if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+          }
+          umma_commit_pair(&tfull_bar[acc]);      // both CTAs' epilogues may read their rows
+        }
+      }
+    }
+  } else if (warp == 6) {
+    if (ga.world > 1) gather_warp(plan, ga, lane);
+  } else {
+    if (cta_rank == 0)
+      epilogue_loop<false>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
+                           num_clusters, cta_rank, total_items, xnorm2, cand);
+    else
+      epilogue_loop<true>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
+                          num_clusters, cta_rank, total_items, xnorm2, cand);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
   }
 }
 
@@ -337,33 +681,95 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   p.n_tiles = (n + BN - 1) / BN;
   p.k_blocks = a_pad / BK;
   if (num_sms < 1) num_sms = 1;
-  // Row blocks per wave: keep their query tiles (128 x a_pad fp16 each) within
-  // a 32 MB slice of L2 so only the data tiles stream from HBM.
+  long long budget_mb = 160;
+  int cluster = 4;
+  p.hint_q = 2;  // evict-last
+  p.hint_x = 0;
+  if (const char *e = getenv("DMLP_TOPK_L2_MB")) budget_mb = atoll(e) > 0 ? atoll(e) : budget_mb;
+  if (const char *e = getenv("DMLP_TOPK_HINT_Q")) p.hint_q = atoi(e);
+  if (const char *e = getenv("DMLP_TOPK_HINT_X")) p.hint_x = atoi(e);
+  if (const char *e = getenv("DMLP_TOPK_CLUSTER")) cluster = atoi(e);
+  p.pair = 1;  // CTA-pair MMA (cta_group::2) unless there is a single row block
+  if (const char *e = getenv("DMLP_TOPK_PAIR")) p.pair = atoi(e) != 0;
+  if (p.m_blocks < 2) p.pair = 0;
+  if (p.pair) cluster = 2;
+  p.prefetch = 0;
+  p.rot = 0;
+  if (const char *e = getenv("DMLP_TOPK_PREFETCH")) p.prefetch = atoi(e);
+  // Cluster: CTAs that sweep the same data tiles in lock step and share each
+  // tile through TMA multicast.  Never wider than the number of row blocks.
+  if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) cluster = 4;
+  while (cluster > 1 && cluster > p.m_blocks) cluster >>= 1;
+  p.cluster = cluster;
+  p.mc_blocks = (p.m_blocks + cluster - 1) / cluster;
+  // Clusters that fit the chip at once (GPC boundaries strand a few SMs: 148 SMs
+  // hold 74 pairs, 33 quads or 16 octets).
+  int nclusters = cluster == 1 ? num_sms : cluster == 2 ? num_sms / 2 : cluster == 4 ? (num_sms * 33) / 148
+                                                                                      : (num_sms * 16) / 148;
+  if (nclusters < 1) nclusters = 1;
+  // Split the clusters into `chunks` column ranges x `group_mc` cluster rows.  More
+  // cluster rows per chunk means more CTAs sweeping the same data tiles together
+  // (fewer HBM reads of the data shard: measured fastest at two chunks on the
+  // headline shape); the cap keeps the wave's query tiles within reach of L2.
+  // At least two chunks whenever possible: each contributes 32 keys per query,
+  // which is the head-room the certified filter needs above k.
   long long tile_bytes = static_cast<long long>(BM) * a_pad * 2;
-  long long fit = (32LL << 20) / (tile_bytes > 0 ? tile_bytes : 1);
-  int gm = static_cast<int>(fit < 1 ? 1 : (fit > num_sms ? num_sms : fit));
-  if (gm > p.m_blocks) gm = p.m_blocks > 0 ? p.m_blocks : 1;
-  p.group_m = gm;
-  int c = num_sms / gm;
-  if (c < 1) c = 1;
+  long long wave_bytes = tile_bytes * cluster * nclusters;
+  long long budget = budget_mb << 20;
+  int c = static_cast<int>((wave_bytes + budget - 1) / budget);
+  if (c < 2) c = 2;
+  if (const char *e = getenv("DMLP_TOPK_CHUNKS")) c = atoi(e) > 0 ? atoi(e) : c;
+  if (c > nclusters) c = nclusters;
+  int gmc = nclusters / c;
+  if (const char *e = getenv("DMLP_TOPK_GMC")) gmc = atoi(e) > 0 ? atoi(e) : gmc;
+  if (gmc > p.mc_blocks) {  // few queries: give the spare clusters to more chunks
+    gmc = p.mc_blocks > 0 ? p.mc_blocks : 1;
+    if (!getenv("DMLP_TOPK_CHUNKS")) c = nclusters / gmc;
+  }
   if (c > p.n_tiles) c = p.n_tiles > 0 ? p.n_tiles : 1;
+  if (c < 1) c = 1;
+  p.group_mc = gmc;
+  p.group_m = gmc * cluster;
   p.chunks = c;
-  long long items = static_cast<long long>((p.m_blocks + gm - 1) / gm) * gm * c;
-  p.grid = static_cast<int>(items < num_sms ? (items > 0 ? items : 1) : num_sms);
+  long long items = static_cast<long long>((p.mc_blocks + gmc - 1) / gmc) * gmc * c;
+  int use = static_cast<int>(items < nclusters ? (items > 0 ? items : 1) : nclusters);
+  p.grid = use * cluster;
   return p;
 }
 
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
-                     unsigned long long *cand, cudaStream_t s) {
+                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s) {
   if (plan.q_rows <= 0 || plan.n <= 0) return 0;
   DMLP_REQUIRE(plan.kp == KP, "dist_topk: this build keeps 32 keys per (query, chunk)");
   DMLP_REQUIRE(plan.a_pad % BK == 0 && plan.a_pad > 0, "dist_topk: a_pad must be a positive multiple of 64");
   CUtensorMap tm_q, tm_x;
   if (int rc = make_fp16_tile_map(&tm_q, qh, plan.q_rows, plan.a_pad, BM)) return rc;
-  if (int rc = make_fp16_tile_map(&tm_x, xh, plan.n, plan.a_pad, BN)) return rc;
-  DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  dist_topk_kernel<<<plan.grid, THREADS, SMEM_BYTES, s>>>(tm_q, tm_x, xnorm2, plan, cand);
-  DMLP_CUDA_OK(cudaGetLastError());
+  if (int rc = make_fp16_tile_map(&tm_x, xh, plan.n, plan.a_pad, plan.pair ? BN / 2 : BN / plan.cluster)) return rc;
+  const int smem_bytes = plan.pair ? Layout2::kBytes : Layout1::kBytes;
+  if (plan.pair)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  else
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(plan.grid);
+  cfg.blockDim = dim3(plan.pair ? THREADS2 : THREADS);
+  cfg.dynamicSmemBytes = smem_bytes;
+  GatherArgs ga;
+  if (gather != nullptr) ga = *gather;
+  DMLP_REQUIRE(ga.world == 1 || plan.pair, "dist_topk: the fused operand gather needs the CTA-pair kernel");
+  DMLP_REQUIRE(ga.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = plan.cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (plan.pair)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel, tm_q, tm_x, xnorm2, plan, cand, ga));
+  else
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_kernel, tm_q, tm_x, xnorm2, plan, cand));
   return 0;
 }
 

@@ -51,10 +51,17 @@ struct TopkPlan {
   int kp;          ///< candidates kept per (query, chunk)
   int m_blocks;    ///< ceil(q_rows / 128)
   int n_tiles;     ///< ceil(n / 256)
-  int group_m;     ///< row blocks that share one wave
+  int group_m;     ///< row blocks that share one wave (= group_mc * cluster)
   int chunks;      ///< column chunks per query (lists per query)
   int k_blocks;    ///< ceil(a_pad / 64)
-  int grid;        ///< persistent CTAs
+  int grid;        ///< persistent CTAs (= clusters * cluster)
+  int pair;        ///< 1: CTA-pair MMA (cta_group::2, cluster of 2); 0: one CTA per tile
+  int cluster;     ///< CTAs per cluster; they sweep the same data tiles via TMA multicast
+  int mc_blocks;   ///< ceil(m_blocks / cluster): row-block groups handled by one cluster
+  int group_mc;    ///< cluster rows per wave
+  int prefetch;    ///< experiment knob (producer start lag in ns); 0 = off
+  int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
+  int hint_q, hint_x;  ///< L2 eviction hints for query / data tiles: 0 normal, 1 first, 2 last
 };
 TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms);
 
@@ -64,9 +71,36 @@ int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t
 int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
                 float *norm2, float *errn, PackStats *maxima, cudaStream_t s);
 
+/// Cross-GPU operand gather fused into the filter GEMM (K4).  Every rank owns
+/// `slice_rows` query rows and has packed them into its own symmetric buffer;
+/// a communication warp in each GEMM CTA pulls the other ranks' packed rows over
+/// NVLink into the local copy just ahead of the tiles that consume them, then
+/// pulls the fp64 rows, norms and k for the re-rank kernel that follows.
+constexpr int kMaxPeers = 8;
+struct GatherArgs {
+  int world = 1, rank = 0;
+  int slice_rows = 0;          ///< padded rows per owner (multiple of 256)
+  int a = 0;                   ///< fp64 row length
+  unsigned epoch = 0;
+  unsigned char *peer_base[kMaxPeers] = {};  ///< symmetric buffers as mapped here (own included)
+  unsigned long long off_qh = 0, off_q64 = 0, off_qn = 0, off_qe = 0, off_k = 0, off_pack_flags = 0;
+  unsigned *rb_count = nullptr;  ///< local, one counter per 128-row block, monotonically increasing
+  int *status = nullptr;
+  long long timeout_cycles = 0;
+};
+
+/// Where the exact k-lists go (K5): straight into the owner rank's receive
+/// buffer [world][slice_rows][kmax], through the peer mapping.
+struct ScatterArgs {
+  int world = 1, rank = 0;
+  int slice_rows = 0;
+  unsigned char *peer_base[kMaxPeers] = {};
+  unsigned long long off_dist = 0, off_id = 0, off_label = 0;
+};
+
 // dist_topk.cu  (cand: [q_rows][chunks][kp] keys, ascending per list)
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
-                     unsigned long long *cand, cudaStream_t s);
+                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s);
 
 // rerank.cu
 struct RerankArgs {
@@ -88,6 +122,7 @@ struct RerankArgs {
   int *out_label;                  // [q][kmax]
   int *flags;                      // [q] 0 = certified, else reason bits
   int *num_flagged;                // device counter
+  ScatterArgs scatter;             // world > 1: lists go to the owners' receive buffers
 };
 int launch_rerank(const RerankArgs &args, cudaStream_t s);
 

@@ -190,8 +190,19 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
   }
   __syncthreads();
 
-  // rank by (distance asc, id desc) and emit the first kq
-  const long long obase = static_cast<long long>(q) * a.kmax;
+  // rank by (distance asc, id desc) and emit the first kq -- locally, or (K5) straight
+  // into the receive buffer of the rank that owns this query, over NVLink
+  long long obase = static_cast<long long>(q) * a.kmax;
+  double *o_dist = a.out_dist;
+  int *o_id = a.out_id, *o_label = a.out_label;
+  if (a.scatter.world > 1) {
+    const int owner = q / a.scatter.slice_rows;
+    const int ql = q - owner * a.scatter.slice_rows;
+    obase = (static_cast<long long>(a.scatter.rank) * a.scatter.slice_rows + ql) * a.kmax;
+    o_dist = reinterpret_cast<double *>(a.scatter.peer_base[owner] + a.scatter.off_dist);
+    o_id = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_id);
+    o_label = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_label);
+  }
   if (tid < w) {
     const double d = s_dist[tid];
     const int id = s_id[tid];
@@ -201,15 +212,15 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
       rank += (dj < d || (dj == d && s_id[j] > id)) ? 1 : 0;
     }
     if (rank < kq) {
-      a.out_dist[obase + rank] = d;
-      a.out_id[obase + rank] = a.id_base + id;
-      a.out_label[obase + rank] = a.x_labels[id];
+      o_dist[obase + rank] = d;
+      o_id[obase + rank] = a.id_base + id;
+      o_label[obase + rank] = a.x_labels[id];
     }
   }
   for (int i = (w < kq ? w : kq) + tid; i < a.kmax; i += RR_THREADS) {
-    a.out_dist[obase + i] = 1e18;
-    a.out_id[obase + i] = -1;
-    a.out_label[obase + i] = -1;
+    o_dist[obase + i] = 1e18;
+    o_id[obase + i] = -1;
+    o_label[obase + i] = -1;
   }
   if (tid == 0) {
     a.flags[q] = s_flag;

@@ -64,7 +64,7 @@ int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *ran
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]) {
   TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
   plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.chunks;
-  plan_out[4] = p.k_blocks; plan_out[5] = p.grid; plan_out[6] = p.kp; plan_out[7] = 0;
+  plan_out[4] = p.k_blocks; plan_out[5] = p.grid; plan_out[6] = p.kp; plan_out[7] = p.cluster;
   return 0;
 }
 
@@ -74,7 +74,7 @@ int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2,
     if (int rc = current_sm_count(&num_sms)) return rc;
   TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
   return launch_dist_topk(static_cast<const __half *>(q_fp16), static_cast<const __half *>(x_fp16), x_norm2, p,
-                          reinterpret_cast<unsigned long long *>(cand), st(stream));
+                          reinterpret_cast<unsigned long long *>(cand), nullptr, st(stream));
 }
 
 int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
@@ -91,6 +91,52 @@ int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs,
   r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
   r.out_dist = out_dist; r.out_id = out_id; r.out_label = out_label;
   r.flags = flags; r.num_flagged = num_flagged;
+  return launch_rerank(r, st(stream));
+}
+
+int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, uint64_t *cand,
+                          const dmlp_gather_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr && g->world >= 1 && g->world <= kMaxPeers, "dist_topk_gather: world must be in [1, 8]");
+  DMLP_REQUIRE(g->slice_rows > 0 && g->slice_rows % 256 == 0, "dist_topk_gather: slice_rows must be a multiple of 256");
+  if (num_sms <= 0)
+    if (int rc = current_sm_count(&num_sms)) return rc;
+  const int q = g->world * g->slice_rows;
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+  DMLP_REQUIRE(p.pair == 1, "dist_topk_gather: needs the CTA-pair kernel");
+  // start the sweep at this rank's own slice: its rows are ready without any transfer,
+  // and every GPU pulls from a different peer first
+  p.rot = static_cast<int>((static_cast<long long>(g->rank) * g->slice_rows / 128 / p.cluster) % p.mc_blocks);
+  GatherArgs ga;
+  ga.world = g->world; ga.rank = g->rank; ga.slice_rows = g->slice_rows; ga.a = g->a; ga.epoch = g->epoch;
+  for (int i = 0; i < g->world; ++i) ga.peer_base[i] = static_cast<unsigned char *>(g->peer_base[i]);
+  ga.off_qh = g->off_qh; ga.off_q64 = g->off_q64; ga.off_qn = g->off_qn; ga.off_qe = g->off_qe; ga.off_k = g->off_k;
+  ga.off_pack_flags = g->off_pack_flags;
+  ga.rb_count = g->rb_count; ga.status = g->status;
+  ga.timeout_cycles = static_cast<long long>((g->timeout_seconds > 0 ? g->timeout_seconds : 20.0) * 1.5e9);
+  const __half *qh = reinterpret_cast<const __half *>(ga.peer_base[ga.rank] + ga.off_qh);
+  return launch_dist_topk(qh, static_cast<const __half *>(x_fp16), x_norm2, p,
+                          reinterpret_cast<unsigned long long *>(cand), &ga, st(stream));
+}
+
+int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
+                        const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
+                        const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
+                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *stream) {
+  DMLP_REQUIRE(sc != nullptr && sc->world >= 2 && sc->world <= kMaxPeers, "rerank_scatter: world must be in [2, 8]");
+  DMLP_REQUIRE(q == sc->world * sc->slice_rows, "rerank_scatter: q must equal world * slice_rows");
+  RerankArgs r;
+  r.cand = reinterpret_cast<const unsigned long long *>(cand);
+  r.chunks = chunks; r.kp = kp;
+  r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
+  r.q_norm2 = q_norm2; r.q_errn = q_errn;
+  r.range = static_cast<const PackStats *>(range);
+  r.x_maxima = static_cast<const PackStats *>(x_maxima);
+  r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
+  r.out_dist = nullptr; r.out_id = nullptr; r.out_label = nullptr;
+  r.flags = flags; r.num_flagged = num_flagged;
+  r.scatter.world = sc->world; r.scatter.rank = sc->rank; r.scatter.slice_rows = sc->slice_rows;
+  for (int i = 0; i < sc->world; ++i) r.scatter.peer_base[i] = static_cast<unsigned char *>(sc->peer_base[i]);
+  r.scatter.off_dist = sc->off_dist; r.scatter.off_id = sc->off_id; r.scatter.off_label = sc->off_label;
   return launch_rerank(r, st(stream));
 }
 
@@ -189,7 +235,7 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   if (int rc = launch_pack(x_attrs, n, a, L.a_pad, rng, xh, xn, xe, stats, s)) return rc;
   if (int rc = launch_pack(q_attrs, q, a, L.a_pad, rng, qh, qn, qe, q_stats, s)) return rc;
   TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms);
-  if (int rc = launch_dist_topk(qh, xh, xn, p, cand, s)) return rc;
+  if (int rc = launch_dist_topk(qh, xh, xn, p, cand, nullptr, s)) return rc;
   if (num_flagged) DMLP_CUDA_OK(cudaMemsetAsync(num_flagged, 0, sizeof(int), s));
   RerankArgs r;
   r.cand = cand; r.chunks = p.chunks; r.kp = 32;

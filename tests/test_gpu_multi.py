@@ -1,0 +1,71 @@
+"""Multi-GPU paths (need >= 2 GPUs): fused peer-memory engine and the NCCL+cuBLAS baseline
+must both reproduce the CPU oracle.  Spawns one process per GPU with torch.distributed.run."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+WORKER = r'''
+import os, sys, json
+sys.path.insert(0, os.environ["DMLP_ROOT"])
+import numpy as np, torch, torch.distributed as dist
+from dmlp_b200.parallel import DistributedKNN
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=dev)
+impl, n, q, a, kmin, kmax = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6])
+eng = DistributedKNN(device=dev, impl=impl)
+eng.synth_problem(n_total=n, q_total=q, a=a, lo=-100.0, hi=100.0, min_k=kmin, max_k=kmax, num_labels=7, seed=5)
+for step in range(3):                      # several steps: epochs, flag reuse, buffer reuse
+    checked = eng.verify_against_oracle(10 ** 9)
+assert eng.check_watchdog() == 0
+eng.stage_host_inputs()
+lab, chk = eng.run_from_host()
+ref_lab, ref_chk = eng.run_resident()
+torch.cuda.synchronize()
+assert (chk.numpy() == ref_chk.cpu().numpy()).all()
+print(json.dumps({"rank": rank, "checked": checked, "flagged": eng.last_flagged, "peer_fused": bool(getattr(eng, "peer_fused", False))}))
+eng.close()
+dist.destroy_process_group()
+'''
+
+
+def _run(tmp_path, repo_root, world, *args):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, DMLP_ROOT=repo_root)
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", str(script), *map(str, args)],
+                         capture_output=True, text=True, env=env, timeout=240)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return res.stdout
+
+
+def _world():
+    n = torch.cuda.device_count()
+    return 8 if n >= 8 else 4 if n >= 4 else 2 if n >= 2 else 0
+
+
+@pytest.mark.parametrize("impl", ["fused", "nccl_cublas"])
+@pytest.mark.parametrize("shape", [(6000, 1000, 96, 1, 12), (3001, 515, 33, 2, 20), (20000, 700, 256, 16, 16)])
+def test_distributed_matches_oracle(tmp_path, repo_root, impl, shape):
+    world = _world()
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    out = _run(tmp_path, repo_root, world, impl, *shape)
+    assert out.count('"checked"') == world
+    if impl == "fused":
+        assert '"peer_fused": true' in out
+
+
+def test_distributed_large_k_takes_exact_path(tmp_path, repo_root):
+    world = _world()
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 30, 60)
+    assert out.count('"checked"') == world
