@@ -30,7 +30,9 @@ def _lib():
         lib.dmlp_topk_plan.argtypes = [_i, _i, _i, _i, C.POINTER(_i * 8)]
         lib.dmlp_dist_topk.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]
         lib.dmlp_rerank.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
-                                    _vp, _vp, _vp, _vp, _vp, _vp]
+                                    _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]
+        lib.dmlp_rerank_workspace_bytes.argtypes = [_i]
+        lib.dmlp_rerank_workspace_bytes.restype = _sz
         lib.dmlp_exact_workspace_bytes.argtypes = [_i, _i]
         lib.dmlp_exact_workspace_bytes.restype = _sz
         lib.dmlp_exact.argtypes = [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]
@@ -121,6 +123,17 @@ def dist_topk(qh, xh, xnorm2, cand=None, sms=None):
     return cand
 
 
+_rerank_ws = {}
+
+
+def rerank_workspace(q, device):
+    """Cached scratch (survivor pair list) for the re-rank kernels."""
+    key = (str(device), q)
+    if key not in _rerank_ws:
+        _rerank_ws[key] = torch.empty(int(_lib().dmlp_rerank_workspace_bytes(q)), dtype=torch.uint8, device=device)
+    return _rerank_ws[key]
+
+
 def rerank(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, id_base, kmax, out=None):
     q, chunks, kp = cand.shape
     n, a = x_attrs.shape
@@ -132,9 +145,10 @@ def rerank(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, 
                torch.empty(q, dtype=torch.int32, device=dev),
                torch.zeros(1, dtype=torch.int32, device=dev))
     od, oi, ol, flags, nflag = out
+    ws = rerank_workspace(q, dev)
     _check(_lib().dmlp_rerank(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
                               _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax,
-                              _p(od), _p(oi), _p(ol), _p(flags), _p(nflag), _stream()))
+                              _p(od), _p(oi), _p(ol), _p(flags), _p(nflag), _p(ws), ws.numel(), _stream()))
     return od, oi, ol, flags, nflag
 
 
@@ -219,12 +233,13 @@ def rerank_scatter(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_
     """K5: exact re-rank whose k-lists are stored straight into the owners' receive buffers."""
     lib = _lib()
     lib.dmlp_rerank_scatter.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
-                                        _vp, _vp, C.POINTER(ScatterArgs), _vp]
+                                        _vp, _vp, C.POINTER(ScatterArgs), _vp, _sz, _vp]
     q, chunks, kp = cand.shape
     n, a = x_attrs.shape
+    ws = rerank_workspace(q, cand.device)
     _check(lib.dmlp_rerank_scatter(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
                                    _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax, _p(flags),
-                                   _p(nflag), C.byref(scatter), _stream()))
+                                   _p(nflag), C.byref(scatter), _p(ws), ws.numel(), _stream()))
 
 
 def knn_local_workspace_bytes(q, n, a):

@@ -52,7 +52,7 @@ def run_baseline(eng):
     nflag.zero_()
     K.rerank(cand, q_all, eng.x, eng.labels, k_all, eng.qn, eng.qe_, eng.stats, eng.stats, eng.id_base, eng.kmax,
              out=eng.lists)
-    eng.launch_count += 1
+    eng.launch_count += 3
     flagged = int(nflag.item())
     if flagged:
         rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)

@@ -201,7 +201,7 @@ class DistributedKNN:
         self.nflag.zero_()
         K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
                          self.stats, self.id_base, self.kmax, self.flags, self.nflag, self.scatter)   # K5
-        self.launch_count += 5
+        self.launch_count += 7   # pack x2, dist_topk, rerank x3, signal
         flagged = int(self.nflag.item())
         if flagged:
             self._repair_flagged()
@@ -252,7 +252,7 @@ class DistributedKNN:
             nflag.zero_()
             K.rerank(self.cand, q_all, self.x, self.labels, k_all, self.qn, self.qe_, self.stats, self.stats,
                      self.id_base, self.kmax, out=self.lists)
-            self.launch_count += 4
+            self.launch_count += 6   # pack x2, dist_topk, rerank x3
             flagged = int(nflag.item())
             if flagged:
                 rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)

@@ -48,11 +48,19 @@ int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2,
 /* ---- K2 exact_rerank (reference: engine.cpp:12-18 semantics) ------------------
  * Writes, per query, kmax slots of (dist, id, label): the exact local top-k in
  * (distance asc, id desc) order, padded with (1e18, -1, -1).  flags[q] != 0 marks
- * a query the filter could not certify; *num_flagged counts them. */
+ * a query the filter could not certify; *num_flagged counts them.  Scratch (the
+ * survivor pair list) comes from the caller: dmlp_rerank_workspace_bytes(q) bytes,
+ * 256-byte aligned. */
+size_t dmlp_rerank_workspace_bytes(int q);
 int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                 const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
                 const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax,
-                double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *stream);
+                double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *workspace,
+                size_t workspace_bytes, void *stream);
+
+/* Diagnostics: subsequent dmlp_rerank* launches also record, per query, how many
+ * survivors they recomputed in fp64 (device int[q]); NULL turns it off. */
+void dmlp_debug_rerank_w(int *w_out);
 
 /* ---- exact fp64 brute force (reference: engine.cpp:233-257 as written) --------
  * Processes `count` queries: rows query_rows[0..count) or, with NULL, rows
@@ -142,7 +150,8 @@ typedef struct dmlp_scatter_args {
 int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                         const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
                         const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
-                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *stream);
+                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *workspace,
+                        size_t workspace_bytes, void *stream);
 
 /* ---- the same pipeline for callers that cannot allocate -------------------------
  * (No counterpart in the reference: it has no GPU code and no scratch buffers.)

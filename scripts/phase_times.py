@@ -49,8 +49,18 @@ for rep in range(args.reps + 2):
     cand = timed("dist_topk", lambda: K.dist_topk(qh, xh, xn))
     od, oi, ol, flags, nflag = timed("rerank", lambda: K.rerank(cand, qq, x, lab, k, qn, qe, st, st, 0, args.kmax))
     timed("finalize", lambda: K.finalize(od[None], oi[None], ol[None], k))
+import ctypes
+wbuf = torch.zeros(Q, dtype=torch.int32, device="cuda")
+K._lib().dmlp_debug_rerank_w.argtypes = [ctypes.c_void_p]
+K._lib().dmlp_debug_rerank_w(ctypes.c_void_p(wbuf.data_ptr()))
+K.rerank(cand, qq, x, lab, k, qn, qe, st, st, 0, args.kmax)
+torch.cuda.synchronize()
+K._lib().dmlp_debug_rerank_w(None)
+wf = wbuf.float()
+wstats = {"mean": wf.mean().item(), "p50": wf.median().item(), "p99": wf.kthvalue(int(0.99 * Q)).values.item(),
+          "max": wf.max().item(), "k_mean": k.float().mean().item()}
 plan = K.topk_plan(Q, N, xh.shape[1])
 med = {n: statistics.median(v) for n, v in times.items()}
 flops = 2.0 * Q * N * K.pad64(A)
 print(json.dumps({"shape": [Q, N, A], "plan": plan, "ms": med, "total_ms": sum(med.values()),
-                  "dist_topk_tflops": flops / (med["dist_topk"] * 1e-3) / 1e12, "flagged": int(nflag.item())}))
+                  "dist_topk_tflops": flops / (med["dist_topk"] * 1e-3) / 1e12, "flagged": int(nflag.item()), "survivors": wstats}))

@@ -123,8 +123,13 @@ struct RerankArgs {
   int *flags;                      // [q] 0 = certified, else reason bits
   int *num_flagged;                // device counter
   ScatterArgs scatter;             // world > 1: lists go to the owners' receive buffers
+  int *w_out = nullptr;            // optional [q]: survivors recomputed per query (diagnostics)
+  void *workspace = nullptr;       // >= rerank_workspace_bytes(q), 256-byte aligned
+  size_t workspace_bytes = 0;
 };
+size_t rerank_workspace_bytes(int q);
 int launch_rerank(const RerankArgs &args, cudaStream_t s);
+void set_rerank_debug_w(int *w_out);  // diagnostics: next launches record survivors per query here
 
 // finalize.cu: merge `sources` sorted lists per query, vote, checksum
 struct FinalizeArgs {

@@ -4,18 +4,26 @@
 // The reference ranks by squared distances accumulated in fp64, strictly in
 // index order, without FMA (reference: engine.cpp:12-18); its reported order is
 // ascending distance with ties to the larger id (engine.cpp:334-338).  The filter
-// GEMM only yields approximate scores, so for each query this kernel
-//   1. merges the per-chunk key lists and finds the k-th smallest score,
-//   2. derives a score threshold T such that every point of the exact top-k must
-//      have score <= T, from the measured rounding-error norms of the packed
-//      rows (pack.cu) and a bound on the fp32 tensor-core accumulation,
-//   3. proves completeness: every chunk whose list is full must have cut off
-//      above T (dropped rows score >= the cut-off); otherwise the query is
-//      flagged and the caller re-runs it on the exact path (exact.cu),
-//   4. recomputes the survivors in fp64 with the reference's rounding sequence
-//      (__dsub_rn/__dmul_rn/__dadd_rn, one sequential chain per candidate),
-//      checks each against its predicted error, ranks them and writes the k
-//      best as (distance, id, label).
+// GEMM only yields approximate scores, so three kernels run per call:
+//
+//   select  (one CTA per query) merges the per-chunk key lists, finds the k-th
+//           smallest score and derives a threshold T such that every point of the
+//           exact top-k must score <= T -- from the measured rounding-error norms
+//           of the packed rows (pack.cu) and a bound on the fp32 tensor-core
+//           accumulation.  It proves completeness (every full chunk list must have
+//           cut off above T: dropped rows score >= the cut-off) or flags the query,
+//           and appends the survivors to a dense (query, row) pair list.
+//   exact   (one warp per query, one lane per survivor) recomputes the distance in
+//           fp64 with the reference's rounding sequence (__dsub_rn/__dmul_rn/
+//           __dadd_rn, one sequential chain per lane).  Rows are streamed in
+//           coalesced 256-byte segments through a per-warp cp.async ring; there
+//           is no block-wide barrier, so a dozen independent warps per SM keep
+//           both the memory system and the dependent fp64 chains busy.
+//   emit    (one warp per query) checks every recomputed pair against its predicted
+//           error, ranks by (distance asc, id desc) and writes the k best as
+//           (distance, id, label) -- locally, or (K5) straight into the receive
+//           buffer of the rank that owns the query.
+// Flagged queries are re-run by the caller on the exact path (exact.cu).
 #include <limits>
 
 #include "common.cuh"
@@ -27,33 +35,49 @@ namespace k {
 namespace {
 
 constexpr int RR_THREADS = 128;
-constexpr int WMAX = 64;       // survivors recomputed per query
-constexpr int CH = 32;         // columns staged per step
-constexpr int RSTRIDE = CH + 2;  // doubles; keeps rows 16-byte aligned
+constexpr int WMAX = 64;        // survivors recomputed per query, at most
+constexpr int PAIRS_PER_Q = 32; // pair-list capacity per query on average
 
 enum : int { kFlagCutoff = 1, kFlagOverflow = 2, kFlagModel = 4 };
 
-template <int BYTES>
-__device__ __forceinline__ void cp_async(void *dst, const void *src, bool valid) {
-  const int sz = valid ? BYTES : 0;  // src-size 0 zero-fills the destination
-  if (BYTES == 16)
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
-  else
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+struct QMeta {
+  double delta, E, qn2, s2;
+};
 
-template <int VEC>  // doubles per cp.async: 2 (16 B) or 1 (8 B)
-__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, int lpad) {
+struct Scratch {
+  unsigned *counter;
+  int *q_base, *q_w;
+  QMeta *meta;
+  int *pair_q, *pair_id;
+  float *pair_score;
+  double *pair_dist;
+  long long capacity;
+};
+
+size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+
+Scratch carve(void *ws, int q) {
+  Scratch s;
+  unsigned char *p = static_cast<unsigned char *>(ws);
+  const long long cap = static_cast<long long>(q) * PAIRS_PER_Q + WMAX;
+  s.capacity = cap;
+  s.counter = reinterpret_cast<unsigned *>(p); p += 256;
+  s.q_base = reinterpret_cast<int *>(p); p += up256(sizeof(int) * q);
+  s.q_w = reinterpret_cast<int *>(p); p += up256(sizeof(int) * q);
+  s.meta = reinterpret_cast<QMeta *>(p); p += up256(sizeof(QMeta) * q);
+  s.pair_q = reinterpret_cast<int *>(p); p += up256(sizeof(int) * cap);
+  s.pair_id = reinterpret_cast<int *>(p); p += up256(sizeof(int) * cap);
+  s.pair_score = reinterpret_cast<float *>(p); p += up256(sizeof(float) * cap);
+  s.pair_dist = reinterpret_cast<double *>(p); p += up256(sizeof(double) * cap);
+  return s;
+}
+
+// ------------------------------------------------------------------ select
+__global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankArgs a, const Scratch sc, int lpad) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   unsigned long long *keys = reinterpret_cast<unsigned long long *>(rr_smem);
-  double *xbuf = reinterpret_cast<double *>(rr_smem + static_cast<size_t>(lpad) * 8);  // [2][WMAX+1][RSTRIDE]
-  __shared__ double s_dist[WMAX];
-  __shared__ int s_id[WMAX];
-  __shared__ int s_nvalid, s_w, s_flag;
-  __shared__ double s_T, s_delta, s_E, s_qn2, s_s2;
+  __shared__ int s_nvalid, s_w, s_flag, s_base;
+  __shared__ double s_T;
 
   const int tid = threadIdx.x;
   const int q = blockIdx.x;
@@ -106,8 +130,10 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
       const double root = delta + sqrt(2.0 * delta * delta + E + U);
       T = root * root * (1.0 + 1e-6) - qn2;
     }
-    s_T = T; s_delta = delta; s_E = E; s_qn2 = qn2;
-    s_s2 = sp.scale * sp.scale;
+    s_T = T;
+    QMeta m;
+    m.delta = delta; m.E = E; m.qn2 = qn2; m.s2 = sp.scale * sp.scale;
+    sc.meta[q] = m;
   }
   __syncthreads();
   const double T = s_T;
@@ -124,74 +150,146 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
     if (last != kKeyInvalid && !(static_cast<double>(key_score(last)) > T)) atomicOr(&s_flag, kFlagCutoff);
   }
   __syncthreads();
-  int w = s_w;
-  if (w > WMAX) {
-    if (tid == 0) atomicOr(&s_flag, kFlagOverflow);
-    w = WMAX;
-  }
-
-  // ---- exact fp64 distances for the w survivors -----------------------------
-  const double *qrow = a.q_attrs + static_cast<long long>(q) * a.a;
-  const int my_id = tid < w ? key_id(keys[tid]) : 0;
-  const int nsteps = (a.a + CH - 1) / CH;
-  constexpr int SEG = CH / VEC;  // copies per row per step
-  auto issue = [&](int step, int buf) {
-    const int col0 = step * CH;
-    double *dst_base = xbuf + static_cast<size_t>(buf) * (WMAX + 1) * RSTRIDE;
-    for (int sidx = tid; sidx < (w + 1) * SEG; sidx += RR_THREADS) {
-      const int row = sidx / SEG, off = (sidx - row * SEG) * VEC;
-      const double *src_row = row == 0 ? qrow : a.x_attrs + static_cast<long long>(key_id(keys[row - 1])) * a.a;
-      const int col = col0 + off;
-      const bool valid = col + VEC <= a.a;
-      const double *src = src_row + (valid ? col : 0);
-      double *dst = dst_base + row * RSTRIDE + off;
-      if (VEC == 2 && !valid && col < a.a) {
-        // odd tail: one real element, then zero
-        dst[0] = src_row[col];
-        dst[1] = 0.0;
-      } else {
-        cp_async<VEC * 8>(dst, src, valid);
-      }
+  if (tid == 0) {
+    int w = s_w;
+    if (w > WMAX) { s_flag |= kFlagOverflow; w = WMAX; }
+    long long base = 0;
+    if (w > 0) {
+      base = atomicAdd(sc.counter, static_cast<unsigned>(w));
+      if (base + w > sc.capacity) { s_flag |= kFlagOverflow; w = 0; base = 0; }  // pair list full
     }
-    cp_async_commit();
-  };
+    s_w = w;
+    s_base = static_cast<int>(base);
+    sc.q_base[q] = static_cast<int>(base);
+    sc.q_w[q] = w;
+    a.flags[q] = s_flag;
+    if (a.w_out != nullptr) a.w_out[q] = w;
+  }
+  __syncthreads();
+  const int w = s_w, base = s_base;
+  for (int i = tid; i < w; i += RR_THREADS) {
+    sc.pair_q[base + i] = q;
+    sc.pair_id[base + i] = key_id(keys[i]);
+    sc.pair_score[base + i] = key_score(keys[i]);
+  }
+}
 
-  double acc = 0.0;
-  if (w > 0) {
-    issue(0, 0);
-    for (int step = 0; step < nsteps; ++step) {
-      const int buf = step & 1;
-      if (step + 1 < nsteps) {
-        issue(step + 1, buf ^ 1);
-        cp_async_wait<1>();
-      } else {
-        cp_async_wait<0>();
+// ------------------------------------------------------------------- exact
+// One warp per query.  Lane r owns survivor r and runs its sequential chain; the
+// warp cooperatively streams 32-column chunks of the survivors' rows (and of the
+// query row) through a private two-stage cp.async ring, so every global access is
+// a coalesced 256-byte row segment and no block-wide barrier is needed.
+constexpr int XC = 32;             // columns per chunk
+constexpr int XSTR = XC + 2;       // row stride in doubles (16-byte aligned rows)
+constexpr int XROWS = 33;          // 32 survivors + the query row
+constexpr int XSTAGE = XROWS * XSTR;
+constexpr int X_WARPS = 4;
+constexpr int X_SMEM = X_WARPS * 2 * XSTAGE * 8;
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async_zfill(void *dst, const void *src, bool valid) {
+  const int sz = valid ? BYTES : 0;  // src-size 0 zero-fills the destination
+  if (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+
+template <bool VEC2>
+__global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_kernel(const RerankArgs a, const Scratch sc) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * X_WARPS + warp;
+  if (q >= a.q) return;
+  const int w = sc.q_w[q];
+  if (w == 0) return;
+  const int base = sc.q_base[q];
+  double *ring = reinterpret_cast<double *>(rr_smem) + static_cast<size_t>(warp) * 2 * XSTAGE;
+  const double *qrow = a.q_attrs + static_cast<long long>(q) * a.a;
+  const int nchunks = (a.a + XC - 1) / XC;
+
+  for (int g0 = 0; g0 < w; g0 += 32) {
+    const int cnt = (w - g0) < 32 ? (w - g0) : 32;
+    const int my_id = lane < cnt ? sc.pair_id[base + g0 + lane] : 0;
+    // row r of the stage: r < cnt -> survivor r, r == cnt -> the query row
+    auto issue = [&](int chunk) {
+      if (chunk < nchunks) {
+        double *stage = ring + (chunk & 1) * XSTAGE;
+        const int col0 = chunk * XC;
+        if (VEC2) {
+          // 16 lanes x 16 B cover one 32-column row segment; two rows per instruction
+          const int half = lane >> 4, seg = lane & 15;
+          const int col = col0 + seg * 2;
+          const bool in = col + 2 <= a.a;
+          for (int r0 = 0; r0 <= cnt; r0 += 2) {
+            const int r = r0 + half;
+            const int rid = __shfl_sync(0xFFFFFFFFu, my_id, r < cnt ? r : 0);
+            if (r <= cnt) {
+              const double *src = (r == cnt ? qrow : a.x_attrs + static_cast<long long>(rid) * a.a) + (in ? col : 0);
+              cp_async_zfill<16>(stage + r * XSTR + seg * 2, src, in);
+            }
+          }
+        } else {
+          const int col = col0 + lane;
+          const bool in = col < a.a;
+          for (int r = 0; r <= cnt; ++r) {
+            const int rid = __shfl_sync(0xFFFFFFFFu, my_id, r < cnt ? r : 0);
+            const double *src = (r == cnt ? qrow : a.x_attrs + static_cast<long long>(rid) * a.a) + (in ? col : 0);
+            cp_async_zfill<8>(stage + r * XSTR + lane, src, in);
+          }
+        }
       }
-      __syncthreads();
-      if (tid < w) {
-        const double *qs = xbuf + static_cast<size_t>(buf) * (WMAX + 1) * RSTRIDE;
-        const double *xs = qs + (tid + 1) * RSTRIDE;
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    double acc = 0.0;
+    issue(0);
+    for (int chunk = 0; chunk < nchunks; ++chunk) {
+      issue(chunk + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
+      if (lane < cnt) {
+        const double *stage = ring + (chunk & 1) * XSTAGE;
+        const double *qs = stage + cnt * XSTR;
+        const double *xs = stage + lane * XSTR;
 #pragma unroll 8
-        for (int i = 0; i < CH; ++i) {
+        for (int i = 0; i < XC; ++i) {
           const double d = __dsub_rn(qs[i], xs[i]);
           acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
         }
       }
-      __syncthreads();
+      __syncwarp();
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (lane < cnt) sc.pair_dist[base + g0 + lane] = acc;
+    __syncwarp();
   }
-  if (tid < w) {
-    s_dist[tid] = acc;
-    s_id[tid] = my_id;
-    // a-posteriori check of the error model on every recomputed pair
-    const double dhat = fmax(s_qn2 + static_cast<double>(key_score(keys[tid])), 0.0);
-    const double bound = (2.0 * sqrt(dhat) * s_delta + s_delta * s_delta + s_E) * (1.0 + 1e-6) + 1e-9 * dhat;
-    if (fabs(acc * s_s2 - dhat) > bound) atomicOr(&s_flag, kFlagModel);
-  }
-  __syncthreads();
+}
 
-  // rank by (distance asc, id desc) and emit the first kq -- locally, or (K5) straight
-  // into the receive buffer of the rank that owns this query, over NVLink
+// -------------------------------------------------------------------- emit
+__global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc) {
+  __shared__ double s_dist[RR_THREADS / 32][WMAX];
+  __shared__ int s_id[RR_THREADS / 32][WMAX];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * (RR_THREADS / 32) + warp;
+  if (q >= a.q) return;
+  int kq = a.k[q];
+  kq = kq < 0 ? 0 : (kq > a.kmax ? a.kmax : kq);
+  const int w = sc.q_w[q], base = sc.q_base[q];
+  const QMeta m = sc.meta[q];
+  int bad = 0;
+  for (int i = lane; i < w; i += 32) {
+    const double d = sc.pair_dist[base + i];
+    s_dist[warp][i] = d;
+    s_id[warp][i] = sc.pair_id[base + i];
+    // a-posteriori check of the error model on every recomputed pair
+    const double dhat = fmax(m.qn2 + static_cast<double>(sc.pair_score[base + i]), 0.0);
+    const double bound = (2.0 * sqrt(dhat) * m.delta + m.delta * m.delta + m.E) * (1.0 + 1e-6) + 1e-9 * dhat;
+    if (fabs(d * m.s2 - dhat) > bound) bad = 1;
+  }
+  bad = __any_sync(0xFFFFFFFFu, bad);
+  __syncwarp();
+
   long long obase = static_cast<long long>(q) * a.kmax;
   double *o_dist = a.out_dist;
   int *o_id = a.out_id, *o_label = a.out_label;
@@ -203,13 +301,13 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
     o_id = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_id);
     o_label = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_label);
   }
-  if (tid < w) {
-    const double d = s_dist[tid];
-    const int id = s_id[tid];
+  for (int i = lane; i < w; i += 32) {
+    const double d = s_dist[warp][i];
+    const int id = s_id[warp][i];
     int rank = 0;
     for (int j = 0; j < w; ++j) {
-      const double dj = s_dist[j];
-      rank += (dj < d || (dj == d && s_id[j] > id)) ? 1 : 0;
+      const double dj = s_dist[warp][j];
+      rank += (dj < d || (dj == d && s_id[warp][j] > id)) ? 1 : 0;
     }
     if (rank < kq) {
       o_dist[obase + rank] = d;
@@ -217,36 +315,61 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(const RerankArgs a, 
       o_label[obase + rank] = a.x_labels[id];
     }
   }
-  for (int i = (w < kq ? w : kq) + tid; i < a.kmax; i += RR_THREADS) {
+  for (int i = (w < kq ? w : kq) + lane; i < a.kmax; i += 32) {
     o_dist[obase + i] = 1e18;
     o_id[obase + i] = -1;
     o_label[obase + i] = -1;
   }
-  if (tid == 0) {
-    a.flags[q] = s_flag;
-    if (s_flag != 0 && a.num_flagged != nullptr) atomicAdd(a.num_flagged, 1);
+  if (lane == 0) {
+    const int f = a.flags[q] | (bad ? kFlagModel : 0);
+    a.flags[q] = f;
+    if (f != 0 && a.num_flagged != nullptr) atomicAdd(a.num_flagged, 1);
   }
 }
 
+int *g_debug_w = nullptr;
+
 }  // namespace
 
-int launch_rerank(const RerankArgs &args, cudaStream_t s) {
+void set_rerank_debug_w(int *w_out) { g_debug_w = w_out; }
+
+size_t rerank_workspace_bytes(int q) {
+  if (q < 1) q = 1;
+  const size_t cap = static_cast<size_t>(q) * PAIRS_PER_Q + WMAX;
+  return 256 + 2 * up256(sizeof(int) * q) + up256(sizeof(QMeta) * q) + 2 * up256(sizeof(int) * cap) +
+         up256(sizeof(float) * cap) + up256(sizeof(double) * cap);
+}
+
+int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
+  RerankArgs args = args_in;
+  if (args.w_out == nullptr) args.w_out = g_debug_w;
   if (args.q <= 0) return 0;
   const int L = args.chunks * args.kp;
   DMLP_REQUIRE(L > 0 && L <= 8192, "rerank: chunks * kp must be in (0, 8192]");
   DMLP_REQUIRE(args.kmax > 0, "rerank: kmax must be positive");
+  DMLP_REQUIRE(args.workspace != nullptr && args.workspace_bytes >= rerank_workspace_bytes(args.q),
+               "rerank: workspace missing or smaller than rerank_workspace_bytes(q)");
+  DMLP_REQUIRE((reinterpret_cast<uintptr_t>(args.workspace) & 255) == 0, "rerank: workspace must be 256-byte aligned");
+  const Scratch sc = carve(args.workspace, args.q);
+  DMLP_CUDA_OK(cudaMemsetAsync(sc.counter, 0, sizeof(unsigned), s));
   int lpad = 64;
   while (lpad < L) lpad <<= 1;
-  const size_t smem = static_cast<size_t>(lpad) * 8 + sizeof(double) * 2 * (WMAX + 1) * RSTRIDE;
+  const size_t smem = static_cast<size_t>(lpad) * 8;
+  DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  rerank_select_kernel<<<args.q, RR_THREADS, smem, s>>>(args, sc, lpad);
+  DMLP_CUDA_OK(cudaGetLastError());
+  const unsigned blocks = static_cast<unsigned>((args.q + X_WARPS - 1) / X_WARPS);
   const bool vec2 = (args.a % 2 == 0) && (reinterpret_cast<uintptr_t>(args.q_attrs) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(args.x_attrs) % 16 == 0);
   if (vec2) {
-    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    rerank_kernel<2><<<args.q, RR_THREADS, smem, s>>>(args, lpad);
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, X_SMEM));
+    rerank_exact_kernel<true><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);
   } else {
-    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    rerank_kernel<1><<<args.q, RR_THREADS, smem, s>>>(args, lpad);
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, X_SMEM));
+    rerank_exact_kernel<false><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);
   }
+  DMLP_CUDA_OK(cudaGetLastError());
+  rerank_emit_kernel<<<(args.q + RR_THREADS / 32 - 1) / (RR_THREADS / 32), RR_THREADS, 0, s>>>(args, sc);
   DMLP_CUDA_OK(cudaGetLastError());
   return 0;
 }

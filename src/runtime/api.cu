@@ -80,8 +80,10 @@ int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2,
 int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                 const int *x_labels, const int *k, const float *q_norm2, const float *q_errn, const void *range,
                 const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax, double *out_dist,
-                int *out_id, int *out_label, int *flags, int *num_flagged, void *stream) {
+                int *out_id, int *out_label, int *flags, int *num_flagged, void *workspace, size_t workspace_bytes,
+                void *stream) {
   RerankArgs r;
+  r.workspace = workspace; r.workspace_bytes = workspace_bytes;
   r.cand = reinterpret_cast<const unsigned long long *>(cand);
   r.chunks = chunks; r.kp = kp;
   r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
@@ -121,7 +123,8 @@ int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a
 int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                         const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
                         const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
-                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *stream) {
+                        int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *workspace,
+                        size_t workspace_bytes, void *stream) {
   DMLP_REQUIRE(sc != nullptr && sc->world >= 2 && sc->world <= kMaxPeers, "rerank_scatter: world must be in [2, 8]");
   DMLP_REQUIRE(q == sc->world * sc->slice_rows, "rerank_scatter: q must equal world * slice_rows");
   RerankArgs r;
@@ -134,11 +137,16 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
   r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
   r.out_dist = nullptr; r.out_id = nullptr; r.out_label = nullptr;
   r.flags = flags; r.num_flagged = num_flagged;
+  r.workspace = workspace; r.workspace_bytes = workspace_bytes;
   r.scatter.world = sc->world; r.scatter.rank = sc->rank; r.scatter.slice_rows = sc->slice_rows;
   for (int i = 0; i < sc->world; ++i) r.scatter.peer_base[i] = static_cast<unsigned char *>(sc->peer_base[i]);
   r.scatter.off_dist = sc->off_dist; r.scatter.off_id = sc->off_id; r.scatter.off_label = sc->off_label;
   return launch_rerank(r, st(stream));
 }
+
+void dmlp_debug_rerank_w(int *w_out) { set_rerank_debug_w(w_out); }
+
+size_t dmlp_rerank_workspace_bytes(int q) { return rerank_workspace_bytes(q); }
 
 size_t dmlp_exact_workspace_bytes(int n, int batch) { return exact_workspace_bytes(n, batch); }
 
@@ -178,7 +186,7 @@ int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k,
 // ---- whole local pipeline ------------------------------------------------------
 namespace {
 struct LocalLayout {
-  size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, total;
+  size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, rerank, rerank_bytes, total;
   int a_pad, chunks;
 };
 LocalLayout local_layout(int q, int n, int a, int num_sms) {
@@ -197,6 +205,8 @@ LocalLayout local_layout(int q, int n, int a, int num_sms) {
   L.qn = take(size_t(q) * 4);
   L.qe = take(size_t(q) * 4);
   L.cand = take(size_t(q) * p.chunks * 32 * 8);
+  L.rerank_bytes = rerank_workspace_bytes(q);
+  L.rerank = take(L.rerank_bytes);
   L.total = off;
   return L;
 }
@@ -243,6 +253,7 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   r.q_norm2 = qn; r.q_errn = qe; r.range = rng; r.x_maxima = stats;
   r.q = q; r.n = n; r.a = a; r.a_pad = L.a_pad; r.id_base = id_base; r.kmax = kmax;
   r.out_dist = out_dist; r.out_id = out_id; r.out_label = out_label; r.flags = flags; r.num_flagged = num_flagged;
+  r.workspace = w + L.rerank; r.workspace_bytes = L.rerank_bytes;
   return launch_rerank(r, s);
 }
 
