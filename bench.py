@@ -4,8 +4,12 @@
 Metric and config follow BASELINE.json: "samples/sec" = queries per second of the
 whole job (reference: `Time taken` around Engine::KNN, common.cpp:119-131), on the
 synthetic problem of the named shape -- num_attrs ("hidden") 8192, num_queries
-("batch") 65536 -- weak-scaled in num_data (65536 datapoints per GPU), generated
-with the reference generator's distribution (generate_input.py:13-21).
+("batch") 65536 per GPU against a fixed dataset of 65536 points -- generated with
+the reference generator's distribution (generate_input.py:13-21).  Weak scaling
+keeps the per-GPU batch fixed: N GPUs classify N x 65536 queries per step.  The
+default grid is 1 x N (queries sharded, dataset replicated: every rank loads 1/N
+of the dataset and the rest arrives over NVLink); --grid RxC selects any other
+layout, e.g. Nx1 for pure data sharding with the fused list reduction.
 
   value   device-timed: inputs already resident in HBM as fp64; one step = the
           full job (range stats, fp16 pack, tcgen05 filter GEMM + fused top-k,
@@ -35,8 +39,9 @@ def parse_args():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl_cublas"])
     p.add_argument("--num-attrs", type=int, default=8192)
-    p.add_argument("--num-queries", type=int, default=65536)
-    p.add_argument("--data-per-gpu", type=int, default=65536)
+    p.add_argument("--num-queries", type=int, default=65536, help="queries per GPU (weak scaling axis)")
+    p.add_argument("--num-data", type=int, default=65536, help="datapoints in total (fixed)")
+    p.add_argument("--grid", default="", help="RxC (data shards x query shards); default 1xN")
     p.add_argument("--min-k", type=int, default=4)
     p.add_argument("--max-k", type=int, default=16)
     p.add_argument("--labels", type=int, default=10)
@@ -81,9 +86,10 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     from dmlp_b200.parallel import DistributedKNN
-    eng = DistributedKNN(device=dev, impl="fused" if args.impl == "ours" else "nccl_cublas")
-    A, Q, Nloc = args.num_attrs, args.num_queries, args.data_per_gpu
-    N = Nloc * world
+    grid = tuple(int(v) for v in args.grid.lower().split("x")) if args.grid else (1, world)
+    eng = DistributedKNN(device=dev, impl="fused" if args.impl == "ours" else "nccl_cublas", grid=grid)
+    A, N = args.num_attrs, args.num_data
+    Q = args.num_queries * world
     eng.synth_problem(n_total=N, q_total=Q, a=A, lo=-100.0, hi=100.0, min_k=args.min_k, max_k=args.max_k,
                       num_labels=args.labels, seed=args.seed)
 
@@ -158,11 +164,12 @@ def main():
             "dtype": "fp16 tensor-core filter (fp32 accumulate) + exact fp64 re-rank; results bit-identical to fp64",
             "data": "synthetic (generate_input.py distribution, uniform [-100,100] 6 decimals), on-device generator",
             "impl": args.impl,
-            "config": {"model": "knn synthetic hidden(num_attrs)=%d batch(num_queries)=%d" % (A, Q),
-                       "global_batch": Q, "seq_len": A, "num_data_total": N, "num_data_per_gpu": Nloc,
-                       "k": [args.min_k, args.max_k], "parallelism": "data-shard x%d (R=%d,C=1)" % (world, world),
+            "config": {"model": "knn synthetic hidden(num_attrs)=%d batch(num_queries)=%d per GPU" % (A, args.num_queries),
+                       "global_batch": Q, "seq_len": A, "num_data_total": N, "queries_per_gpu": args.num_queries,
+                       "k": [args.min_k, args.max_k],
+                       "parallelism": "grid R=%d (data shards) x C=%d (query shards)" % (eng.R, eng.C),
                        "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed"
-                             % ((Nloc + Q) * A * 8 / 1e9)},
+                             % ((N / eng.R + Q / eng.C) * A * 8 / 1e9)},
             "filter_gemm_tflops_per_gpu": flops / world / 1e12,
             "flagged_queries": flagged,
             "gpu_launches": launches,

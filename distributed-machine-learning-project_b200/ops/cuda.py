@@ -219,6 +219,18 @@ class ScatterArgs(C.Structure):
                 ("off_id", _u64), ("off_label", _u64)]
 
 
+class PeerGatherArgs(C.Structure):
+    _fields_ = [("world", _i), ("rank", _i), ("epoch", C.c_uint32), ("peer_base", _vp * 8), ("off_flags", _u64),
+                ("part_off", _u64 * 8), ("part_len", _u64 * 8), ("status", _vp), ("timeout_seconds", _dbl)]
+
+
+def peer_gather(args):
+    """Pull every other rank's part of a symmetric region over NVLink (in-kernel all-gather)."""
+    lib = _lib()
+    lib.dmlp_peer_gather.argtypes = [C.POINTER(PeerGatherArgs), _vp]
+    _check(lib.dmlp_peer_gather(C.byref(args), _stream()))
+
+
 def dist_topk_gather(xh, xnorm2, cand, gather):
     """K4: filter GEMM whose query operand is all-gathered from the peers inside the kernel."""
     lib = _lib()

@@ -1,26 +1,31 @@
 """Distributed k-NN engine: one process per GPU (torch.distributed, NCCL for plumbing).
 
-Layout (the reference's grid with C = 1, engine.cpp:40-57): rank r holds data shard
-r and *owns* query slice r.  Every rank scores all queries against its shard, then
-the per-query k-lists are reduced onto the slice owner (a reduce-scatter of
-k-lists over the data axis, reference: engine.cpp:283-308), which votes and
-checksums.
+Grid (the reference's process grid, engine.cpp:40-57): R rows x C columns,
+rank = r * C + c.  Row r holds data shard r, column c holds query shard c.
 
-impl = "fused"        hand-written sm_100a kernels.  Cross-GPU data moves through
-                      peer-mapped symmetric buffers from inside the kernels: the
-                      filter GEMM all-gathers its query operand while it runs (K4),
-                      the re-rank stores its k-lists straight into the owner's
-                      receive buffer (K5), flags replace barriers.  NCCL carries
-                      one 16-byte all-reduce (value range) per step.
-impl = "nccl_cublas"  baseline variant: NCCL all-gather of operands, cuBLAS
-                      GEMM (torch.matmul), torch.topk, NCCL exchange of lists.
+  * along a row (same data shard, C ranks): every rank loads 1/C of the shard and
+    the parts are all-gathered over NVLink by a pull kernel (the reference's row
+    MPI_Bcast of the data shard, engine.cpp:129-131);
+  * along a column (same queries, R ranks): every rank owns 1/R of the column's
+    queries; the filter GEMM all-gathers the packed queries from inside the kernel
+    (K4) and the re-rank stores each query's k-list straight into its owner's
+    receive buffer (K5, the reduce-scatter of k-lists of engine.cpp:283-308).
+
+R x 1 is pure data sharding, 1 x C pure query sharding with a replicated dataset
+(the data-parallel layout: every GPU sees the whole dataset, the batch is split).
+
+impl = "fused"        the above, hand-written sm_100a kernels, peer-mapped symmetric
+                      buffers, flags instead of barriers.  NCCL carries one 16-byte
+                      all-reduce per step, and only when R > 1.
+impl = "nccl_cublas"  baseline variant: NCCL all-gathers, cuBLAS GEMM (torch.mm),
+                      torch.topk, NCCL all-to-all of the lists.
 """
 import numpy as np
 import torch
 import torch.distributed as dist
 
 from ..ops import cuda as K
-from .grid import even_slice
+from .grid import Grid, even_slice
 from .symm import Layout, SymmetricBuffer
 
 
@@ -29,90 +34,163 @@ def _round_up(v, m):
 
 
 class DistributedKNN:
-    def __init__(self, device=None, impl="fused", group=None):
+    def __init__(self, device=None, impl="fused", grid=None):
         self.device = torch.device(device if device is not None else "cuda")
         self.impl = impl
-        self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        if grid is None:
+            grid = (self.world, 1)
+        self.grid = Grid.for_world(self.world, *grid)
+        self.R, self.C = self.grid.rows, self.grid.cols
+        self.r, self.c = self.grid.coords(self.rank)
+        self.col_group = self.row_group = None
+        if self.world > 1:
+            # every rank must create every group, in the same order
+            for c in range(self.C):
+                g = dist.new_group(self.grid.column_ranks(c))
+                if c == self.c:
+                    self.col_group = g
+            for r in range(self.R):
+                g = dist.new_group(self.grid.row_ranks(r))
+                if r == self.r:
+                    self.row_group = g
         self.launch_count = 0
         self.last_flagged = 0
         self.epoch = 0
         self.host = None
-        self.sym = None
+        self.sym = self.row_sym = None
 
     # ------------------------------------------------------------------ problem
-    def set_local_problem(self, x, labels, id_base, q_slice, k_slice, q_total, kmax):
-        """Install this rank's resident inputs: its data shard (fp64 [n, a]) with the
-        global id of row 0, and the query slice it owns (rows of the even partition)."""
+    def partition(self, n_total, q_total):
+        """(data part, data shard, query slice, query shard) as global [begin, end) ranges."""
+        sb, se, _ = even_slice(n_total, self.R, self.r)          # data shard of this row
+        pb, pe, _ = even_slice(se - sb, self.C, self.c)          # the part of it this rank loads
+        cb, ce, _ = even_slice(q_total, self.C, self.c)          # query shard of this column
+        ob, oe, _ = even_slice(ce - cb, self.R, self.r)          # the slice of it this rank owns
+        return (sb + pb, sb + pe), (sb, se), (cb + ob, cb + oe), (cb, ce)
+
+    def set_local_problem(self, x_part, labels_part, q_slice, k_slice, n_total, q_total, kmax):
+        """Install this rank's resident inputs: the part of its data shard it loaded and
+        the query slice it owns (see partition())."""
         dev = self.device
-        self.x = x.to(dev, torch.float64).contiguous()
-        self.labels = labels.to(dev, torch.int32).contiguous()
-        self.id_base = int(id_base)
-        self.q_total = int(q_total)
-        self.qb, self.qe, self.q_even = even_slice(self.q_total, self.world, self.rank)
-        self.nq = self.qe - self.qb
-        assert q_slice.shape[0] == self.nq
-        self.a = int(self.x.shape[1])
+        (pb, pe), (sb, se), (ob, oe), (cb, ce) = self.partition(n_total, q_total)
+        assert x_part.shape[0] == pe - pb and q_slice.shape[0] == oe - ob
+        self.n_total, self.q_total = int(n_total), int(q_total)
+        self.part_rows, self.shard_rows = (pb - sb, pe - sb), se - sb
+        self.id_base = sb
+        self.q_col = ce - cb                      # queries of this column
+        self.q_even = even_slice(self.q_col, self.R, self.r)[2]
+        self.nq = oe - ob
+        self.a = int(x_part.shape[1])
         self.kmax = int(kmax)
-        self._alloc(q_slice.to(dev, torch.float64), k_slice.to(dev, torch.int32))
+        self._alloc(x_part.to(dev, torch.float64), labels_part.to(dev, torch.int32),
+                    q_slice.to(dev, torch.float64), k_slice.to(dev, torch.int32))
 
     def synth_problem(self, n_total, q_total, a, lo, hi, min_k, max_k, num_labels, seed):
         """Generate this rank's part of the synthetic problem on the device (K8)."""
         with torch.cuda.device(self.device):
-            nb, ne, _ = even_slice(n_total, self.world, self.rank)
-            qb, qe, _ = even_slice(q_total, self.world, self.rank)
-            x = K.synth_attrs(ne - nb, a, nb, lo, hi, seed, 0, self.device)
-            labels = K.synth_labels(ne - nb, nb, num_labels, seed, self.device)
-            qs = K.synth_attrs(qe - qb, a, qb, lo, hi, seed, 2, self.device)
+            (pb, pe), _, (ob, oe), _ = self.partition(n_total, q_total)
+            x = K.synth_attrs(pe - pb, a, pb, lo, hi, seed, 0, self.device)
+            labels = K.synth_labels(pe - pb, pb, num_labels, seed, self.device)
+            qs = K.synth_attrs(oe - ob, a, ob, lo, hi, seed, 2, self.device)
             kmax_eff = min(max_k, n_total)
-            ks = K.synth_k(qe - qb, qb, min(min_k, kmax_eff), kmax_eff, seed, self.device)
-            self.set_local_problem(x, labels, nb, qs, ks, q_total, max(1, kmax_eff))
+            ks = K.synth_k(oe - ob, ob, min(min_k, kmax_eff), kmax_eff, seed, self.device)
+            self.set_local_problem(x, labels, qs, ks, n_total, q_total, max(1, kmax_eff))
 
-    def _alloc(self, q_slice, k_slice):
-        dev, W = self.device, self.world
-        n, a, km = self.x.shape[0], self.a, self.kmax
-        self.a_pad = K.pad64(a)
+    # --------------------------------------------------------------- allocation
+    def _alloc(self, x_part, labels_part, q_slice, k_slice):
+        dev, R, C = self.device, self.R, self.C
+        n, km = self.shard_rows, self.kmax
+        self.a_pad = K.pad64(self.a)
         self.fused_ok = km <= K.FUSED_MAX_K and n > 0
-        self.peer_fused = W > 1 and self.impl == "fused" and self.fused_ok
+        self.peer_fused = R > 1 and self.impl == "fused" and self.fused_ok
+        self.peer_rows = C > 1 and self.impl == "fused"
         with torch.cuda.device(dev):
+            self.status = torch.zeros(1, dtype=torch.int32, device=dev)
             self.stats = K.new_stats(dev)
             self.q_stats = K.new_stats(dev)
+            self._alloc_shard(x_part, labels_part)
             self.xh = torch.empty((n, self.a_pad), dtype=torch.float16, device=dev)
             self.xn = torch.empty(n, dtype=torch.float32, device=dev)
             self.xe = torch.empty(n, dtype=torch.float32, device=dev)
             if self.peer_fused:
                 self._alloc_symmetric(q_slice, k_slice)
-                return
-            # single GPU, or the NCCL-plumbed paths: every slice padded to q_even rows
-            self.qs = self.q_even
-            self.qp = self.qs * W
-            self.q_slice, self.k_slice = q_slice.contiguous(), k_slice.contiguous()
-            if W > 1:
-                self.q_all = torch.zeros((self.qp, a), dtype=torch.float64, device=dev)
-                self.k_all = torch.zeros(self.qp, dtype=torch.int32, device=dev)
-                self.q_pad = torch.zeros((self.qs, a), dtype=torch.float64, device=dev)
-                self.k_pad = torch.zeros(self.qs, dtype=torch.int32, device=dev)
-                self.recv = (torch.empty((W, self.qs, km), dtype=torch.float64, device=dev),
-                             torch.empty((W, self.qs, km), dtype=torch.int32, device=dev),
-                             torch.empty((W, self.qs, km), dtype=torch.int32, device=dev))
-            self.qh = torch.zeros((self.qp, self.a_pad), dtype=torch.float16, device=dev)
-            self.qn = torch.zeros(self.qp, dtype=torch.float32, device=dev)
-            self.qe_ = torch.zeros(self.qp, dtype=torch.float32, device=dev)
-            plan = K.topk_plan(self.qp, max(n, 1), self.a_pad)
-            self.cand = torch.empty((self.qp, plan["chunks"], plan["kp"]), dtype=torch.int64, device=dev)
-            self.lists = (torch.empty((self.qp, km), dtype=torch.float64, device=dev),
-                          torch.empty((self.qp, km), dtype=torch.int32, device=dev),
-                          torch.empty((self.qp, km), dtype=torch.int32, device=dev),
-                          torch.empty(self.qp, dtype=torch.int32, device=dev),
-                          torch.zeros(1, dtype=torch.int32, device=dev))
+            else:
+                self._alloc_plain(q_slice, k_slice)
+            torch.cuda.synchronize(dev)
+        if self.world > 1:
+            dist.barrier()
+
+    def _alloc_shard(self, x_part, labels_part):
+        """The data shard of this row: local when C == 1, otherwise a row-symmetric buffer
+        in which every rank of the row fills its own part and pulls the others'."""
+        dev, C, n, a = self.device, self.C, self.shard_rows, self.a
+        b, e = self.part_rows
+        if C == 1:
+            self.x, self.labels = x_part.contiguous(), labels_part.contiguous()
+            self.x_part, self.labels_part = self.x, self.labels
+            return
+        if self.peer_rows:
+            lay = Layout()
+            lay.add("part_flags", 128)
+            lay.add("x64", n * a * 8)
+            lay.add("labels", n * 4)
+            self.row_sym = sym = SymmetricBuffer(lay, dev, self.row_group)
+            self.x = sym.view("x64", torch.float64, (n, a))
+            self.labels = sym.view("labels", torch.int32)
+            self.part_table = sym.pointer_table("part_flags")
+            self._row_gather_args = []
+            for name, row_bytes in (("x64", a * 8), ("labels", 4)):
+                g = K.PeerGatherArgs()
+                g.world, g.rank = C, self.c
+                for p in range(C):
+                    g.peer_base[p] = sym.peer_ptrs[p]
+                    pb, pe, _ = even_slice(n, C, p)
+                    g.part_off[p] = lay.off[name] + pb * row_bytes
+                    g.part_len[p] = (pe - pb) * row_bytes
+                g.off_flags = lay.off["part_flags"]
+                g.status, g.timeout_seconds = self.status.data_ptr(), 20.0
+                self._row_gather_args.append(g)
+        else:
+            self.x = torch.empty((n, a), dtype=torch.float64, device=dev)
+            self.labels = torch.empty(n, dtype=torch.int32, device=dev)
+            self._row_sizes = [even_slice(n, C, p)[1] - even_slice(n, C, p)[0] for p in range(C)]
+        self.x_part, self.labels_part = self.x[b:e], self.labels[b:e]
+        self.x_part.copy_(x_part)
+        self.labels_part.copy_(labels_part)
+
+    def _alloc_plain(self, q_slice, k_slice):
+        """Column buffers for a single-rank column or for the NCCL-plumbed paths."""
+        dev, R, a, km, n = self.device, self.R, self.a, self.kmax, self.shard_rows
+        self.qs = self.q_even
+        self.qp = self.qs * R
+        self.q_slice, self.k_slice = q_slice.contiguous(), k_slice.contiguous()
+        if R > 1:
+            self.q_all = torch.zeros((self.qp, a), dtype=torch.float64, device=dev)
+            self.k_all = torch.zeros(self.qp, dtype=torch.int32, device=dev)
+            self.q_pad = torch.zeros((self.qs, a), dtype=torch.float64, device=dev)
+            self.k_pad = torch.zeros(self.qs, dtype=torch.int32, device=dev)
+            self.recv = (torch.empty((R, self.qs, km), dtype=torch.float64, device=dev),
+                         torch.empty((R, self.qs, km), dtype=torch.int32, device=dev),
+                         torch.empty((R, self.qs, km), dtype=torch.int32, device=dev))
+        self.qh = torch.zeros((self.qp, self.a_pad), dtype=torch.float16, device=dev)
+        self.qn = torch.zeros(self.qp, dtype=torch.float32, device=dev)
+        self.qe_ = torch.zeros(self.qp, dtype=torch.float32, device=dev)
+        plan = K.topk_plan(self.qp, max(n, 1), self.a_pad)
+        self.cand = torch.empty((self.qp, plan["chunks"], plan["kp"]), dtype=torch.int64, device=dev)
+        self.lists = (torch.empty((self.qp, km), dtype=torch.float64, device=dev),
+                      torch.empty((self.qp, km), dtype=torch.int32, device=dev),
+                      torch.empty((self.qp, km), dtype=torch.int32, device=dev),
+                      torch.empty(self.qp, dtype=torch.int32, device=dev),
+                      torch.zeros(1, dtype=torch.int32, device=dev))
 
     def _alloc_symmetric(self, q_slice, k_slice):
-        """Symmetric buffer: packed and fp64 queries of every slice, norms, k, the
+        """Column-symmetric buffer: packed and fp64 queries of every slice, norms, k, the
         receive area for k-lists, and the flag words."""
-        dev, W, a, km = self.device, self.world, self.a, self.kmax
+        dev, R, a, km = self.device, self.R, self.a, self.kmax
         self.qs = _round_up(self.q_even, 256)   # slice stride in the padded query index space
-        self.qp = self.qs * W
+        self.qp = self.qs * R
         lay = Layout()
         lay.add("pack_flags", 128)
         lay.add("list_flags", 128)
@@ -121,11 +199,11 @@ class DistributedKNN:
         lay.add("qn", self.qp * 4)
         lay.add("qe", self.qp * 4)
         lay.add("k", self.qp * 4)
-        lay.add("recv_dist", W * self.qs * km * 8)
-        lay.add("recv_id", W * self.qs * km * 4)
-        lay.add("recv_label", W * self.qs * km * 4)
-        self.sym = sym = SymmetricBuffer(lay, dev, self.group)
-        r0 = self.rank * self.qs
+        lay.add("recv_dist", R * self.qs * km * 8)
+        lay.add("recv_id", R * self.qs * km * 4)
+        lay.add("recv_label", R * self.qs * km * 4)
+        self.sym = sym = SymmetricBuffer(lay, dev, self.col_group)
+        r0 = self.r * self.qs
         self.q_all = sym.view("q64", torch.float64, (self.qp, a))
         self.k_all = sym.view("k", torch.int32)
         self.qh = sym.view("qh", torch.float16, (self.qp, self.a_pad))
@@ -136,21 +214,19 @@ class DistributedKNN:
         self.k_slice = self.k_all[r0:r0 + self.nq]
         self.q_slice.copy_(q_slice)
         self.k_slice.copy_(k_slice)
-        self.recv = (sym.view("recv_dist", torch.float64, (W, self.qs, km)),
-                     sym.view("recv_id", torch.int32, (W, self.qs, km)),
-                     sym.view("recv_label", torch.int32, (W, self.qs, km)))
+        self.recv = (sym.view("recv_dist", torch.float64, (R, self.qs, km)),
+                     sym.view("recv_id", torch.int32, (R, self.qs, km)),
+                     sym.view("recv_label", torch.int32, (R, self.qs, km)))
         self.pack_table = sym.pointer_table("pack_flags")
         self.list_table = sym.pointer_table("list_flags")
         self.rb_count = torch.zeros(self.qp // 128, dtype=torch.int32, device=dev)
-        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
-        n = self.x.shape[0]
-        plan = K.topk_plan(self.qp, max(n, 1), self.a_pad)
+        plan = K.topk_plan(self.qp, max(self.shard_rows, 1), self.a_pad)
         self.cand = torch.empty((self.qp, plan["chunks"], plan["kp"]), dtype=torch.int64, device=dev)
         self.flags = torch.empty(self.qp, dtype=torch.int32, device=dev)
         self.nflag = torch.zeros(1, dtype=torch.int32, device=dev)
         g = K.GatherArgs()
-        g.world, g.rank, g.slice_rows, g.a = W, self.rank, self.qs, a
-        for r in range(W):
+        g.world, g.rank, g.slice_rows, g.a = R, self.r, self.qs, a
+        for r in range(R):
             g.peer_base[r] = sym.peer_ptrs[r]
         g.off_qh, g.off_q64 = lay.off["qh"], lay.off["q64"]
         g.off_qn, g.off_qe, g.off_k = lay.off["qn"], lay.off["qe"], lay.off["k"]
@@ -158,19 +234,19 @@ class DistributedKNN:
         g.rb_count, g.status, g.timeout_seconds = self.rb_count.data_ptr(), self.status.data_ptr(), 20.0
         self.gather = g
         s = K.ScatterArgs()
-        s.world, s.rank, s.slice_rows = W, self.rank, self.qs
-        for r in range(W):
+        s.world, s.rank, s.slice_rows = R, self.r, self.qs
+        for r in range(R):
             s.peer_base[r] = sym.peer_ptrs[r]
         s.off_dist, s.off_id, s.off_label = lay.off["recv_dist"], lay.off["recv_id"], lay.off["recv_label"]
         self.scatter = s
-        torch.cuda.synchronize(dev)
-        dist.barrier(group=self.group)
 
     # --------------------------------------------------------------------- steps
     def run_resident(self):
         """One full job with inputs resident on the device.  Returns (label, checksum)
         for the query slice this rank owns (device tensors)."""
         with torch.cuda.device(self.device):
+            self.epoch += 1
+            self._gather_shard()
             if self.impl == "nccl_cublas":
                 from .baseline import run_baseline
                 return run_baseline(self)
@@ -178,19 +254,40 @@ class DistributedKNN:
                 return self._run_peer_fused()
             return self._run_local_or_nccl()
 
+    def _gather_shard(self):
+        """Row all-gather: after this, self.x / self.labels hold the whole data shard."""
+        if self.C == 1:
+            return
+        if self.peer_rows:
+            self.row_sym.signal(self.part_table, self.epoch)     # "my part is in place"
+            for g in self._row_gather_args:
+                g.epoch = self.epoch
+                K.peer_gather(g)
+            self.launch_count += 3
+        elif len(set(self._row_sizes)) == 1:
+            dist.all_gather_into_tensor(self.x, self.x_part.contiguous(), group=self.row_group)
+            dist.all_gather_into_tensor(self.labels, self.labels_part.contiguous(), group=self.row_group)
+        else:
+            for full, part in ((self.x, self.x_part), (self.labels, self.labels_part)):
+                outs, b = [], 0
+                for sz in self._row_sizes:
+                    outs.append(full[b:b + sz])
+                    b += sz
+                dist.all_gather(outs, part.contiguous(), group=self.row_group)
+
     def _range_stats(self):
-        """Value range over every rank's data and queries -> common centring / scaling."""
+        """Value range of the data shard and queries -> common centring / scaling for
+        the ranks that exchange packed rows (one column)."""
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_update(self.x, self.stats)
         K.stats_update(self.q_slice, self.stats)
         self.launch_count += 4
-        if self.world > 1:
-            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.group)
+        if self.R > 1:
+            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.col_group)
 
     def _run_peer_fused(self):
-        W, r0 = self.world, self.rank * self.qs
-        self.epoch += 1
+        r0 = self.r * self.qs
         self._range_stats()
         K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
         K.pack(self.q_slice, self.stats, self.q_stats,
@@ -201,7 +298,7 @@ class DistributedKNN:
         self.nflag.zero_()
         K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
                          self.stats, self.id_base, self.kmax, self.flags, self.nflag, self.scatter)   # K5
-        self.launch_count += 7   # pack x2, dist_topk, rerank x3, signal
+        self.launch_count += 7   # pack x2, signal, dist_topk, rerank x3
         flagged = int(self.nflag.item())
         if flagged:
             self._repair_flagged()
@@ -228,17 +325,17 @@ class DistributedKNN:
             ql = sel - o * self.qs
             for name, dtype, src in (("recv_dist", torch.float64, tmp[0]), ("recv_id", torch.int32, tmp[1]),
                                      ("recv_label", torch.int32, tmp[2])):
-                dst = self.sym.view(name, dtype, (self.world, self.qs, km), rank=o)
-                dst[self.rank, ql] = src[sel]
+                dst = self.sym.view(name, dtype, (self.R, self.qs, km), rank=o)
+                dst[self.r, ql] = src[sel]
 
-    # -- single GPU, and multi-GPU with NCCL plumbing (large k, or impl without peer memory)
+    # -- single-rank columns, and columns plumbed with NCCL (large k, or the baseline)
     def _gather_queries_nccl(self):
-        if self.world == 1:
+        if self.R == 1:
             return self.q_slice, self.k_slice
         self.q_pad[: self.nq].copy_(self.q_slice)
         self.k_pad[: self.nq].copy_(self.k_slice)
-        dist.all_gather_into_tensor(self.q_all, self.q_pad, group=self.group)
-        dist.all_gather_into_tensor(self.k_all, self.k_pad, group=self.group)
+        dist.all_gather_into_tensor(self.q_all, self.q_pad, group=self.col_group)
+        dist.all_gather_into_tensor(self.k_all, self.k_pad, group=self.col_group)
         return self.q_all, self.k_all
 
     def _run_local_or_nccl(self):
@@ -266,15 +363,19 @@ class DistributedKNN:
 
     def _reduce_and_finalize_nccl(self, od, oi, ol):
         """k-lists of every data shard -> owner of the query slice -> merge, vote, checksum."""
-        W, qs, km = self.world, self.qs, self.kmax
-        if W == 1:
-            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-            self.launch_count += 1
+        R, qs, km = self.R, self.qs, self.kmax
+        if R == 1:
+            if km <= 1024:
+                label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+                self.launch_count += 1
+            else:
+                from ..models.knn import _finalize_host_merge
+                label, checksum = _finalize_host_merge((od[None], oi[None], ol[None]), self.k_slice, self.device)
             return label, checksum
         for src, dst in zip((od, oi, ol), self.recv):
-            dist.all_to_all_single(dst.view(W * qs, km), src.view(W * qs, km), group=self.group)
-        mine = self.k_all[self.rank * qs:(self.rank + 1) * qs]
-        if W * km <= 1024:
+            dist.all_to_all_single(dst.view(R * qs, km), src.view(R * qs, km), group=self.col_group)
+        mine = self.k_all[self.r * qs:(self.r + 1) * qs]
+        if R * km <= 1024:
             label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2], mine)
             self.launch_count += 1
         else:
@@ -286,7 +387,7 @@ class DistributedKNN:
     def stage_host_inputs(self):
         """Copy this rank's inputs into pinned host memory (the loader's output)."""
         self.host = {
-            "x": self.x.cpu().pin_memory(), "labels": self.labels.cpu().pin_memory(),
+            "x": self.x_part.cpu().pin_memory(), "labels": self.labels_part.cpu().pin_memory(),
             "q": self.q_slice.cpu().pin_memory(), "k": self.k_slice.cpu().pin_memory(),
         }
         self.host_out = (torch.empty(self.nq, dtype=torch.int32).pin_memory(),
@@ -297,8 +398,8 @@ class DistributedKNN:
     def run_from_host(self):
         """Public end-to-end call: pinned host inputs -> device -> job -> host results."""
         h = self.host
-        self.x.copy_(h["x"], non_blocking=True)
-        self.labels.copy_(h["labels"], non_blocking=True)
+        self.x_part.copy_(h["x"], non_blocking=True)
+        self.labels_part.copy_(h["labels"], non_blocking=True)
         self.q_slice.copy_(h["q"], non_blocking=True)
         self.k_slice.copy_(h["k"], non_blocking=True)
         label, checksum = self.run_resident()
@@ -309,29 +410,31 @@ class DistributedKNN:
 
     def check_watchdog(self):
         """Non-zero means a peer signal timed out somewhere."""
-        return int(self.status.item()) if self.sym is not None else 0
+        return int(self.status.item())
 
     def close(self):
-        if self.sym is not None:
-            self.sym.close()
-            self.sym = None
+        for s in (self.sym, self.row_sym):
+            if s is not None:
+                s.close()
+        self.sym = self.row_sym = None
 
     # -------------------------------------------------------------- verification
     def verify_against_oracle(self, count):
-        """Re-derive the first `count` owned queries on the CPU oracle (needs the
-        whole dataset on the host: only sensible for small problems)."""
+        """Re-derive the first `count` owned queries on the CPU oracle (gathers the whole
+        dataset on the host: only sensible for small problems)."""
         from ..ops import cpu
         label, checksum = self.run_resident()
+        torch.cuda.synchronize(self.device)
         if self.world > 1:
-            parts = [None] * self.world     # shards may differ in size: exchange as objects
-            dist.all_gather_object(parts, (self.x.cpu().numpy(), self.labels.cpu().numpy()), group=self.group)
-            x = torch.from_numpy(np.concatenate([p[0] for p in parts]))
-            lab = torch.from_numpy(np.concatenate([p[1] for p in parts]))
+            parts = [None] * self.world     # parts differ in size: exchange as objects
+            dist.all_gather_object(parts, (self.x_part.cpu().numpy(), self.labels_part.cpu().numpy()))
+            # global row order = shard by shard, part by part = rank order r * C + c
+            x = np.concatenate([p[0] for p in parts])
+            lab = np.concatenate([p[1] for p in parts])
         else:
-            x, lab = self.x, self.labels
+            x, lab = self.x.cpu().numpy(), self.labels.cpu().numpy()
         c = min(count, self.nq)
-        want_label, want, *_ = cpu.knn(x.cpu().numpy(), lab.cpu().numpy(), self.q_slice[:c].cpu().numpy(),
-                                       self.k_slice[:c].cpu().numpy())
+        want_label, want, *_ = cpu.knn(x, lab, self.q_slice[:c].cpu().numpy(), self.k_slice[:c].cpu().numpy())
         got = checksum[:c].cpu().numpy().view(np.uint64)
         if not (got == want).all():
             raise AssertionError(f"rank {self.rank}: {(got != want).sum()} of {c} checksums differ from the oracle")

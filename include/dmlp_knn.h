@@ -114,6 +114,22 @@ int dmlp_symm_signal(void *peer_flag_ptrs, int world, int my_rank, uint32_t valu
 int dmlp_symm_wait(const void *local_flags, int world, uint32_t value, double timeout_seconds, int *status,
                    void *stream);
 
+/* All-gather of per-rank parts of one region of the symmetric buffers (reference:
+ * the row MPI_Bcast that replicates a data shard, engine.cpp:129-131): rank p's
+ * part lives at part_off[p] (length part_len[p]) in every rank's buffer; after
+ * each rank has signalled word `rank` of the flag array at off_flags with `epoch`,
+ * this kernel pulls every other rank's part over NVLink into the local buffer. */
+typedef struct dmlp_peer_gather_args {
+  int world, rank;
+  uint32_t epoch;
+  void *peer_base[8];
+  uint64_t off_flags;
+  uint64_t part_off[8], part_len[8];
+  int *status;
+  double timeout_seconds;
+} dmlp_peer_gather_args;
+int dmlp_peer_gather(const dmlp_peer_gather_args *g, void *stream);
+
 /* ---- fused cross-GPU steps ------------------------------------------------------
  * K4, all-gather -> GEMM (reference: the row/column MPI_Bcast of an operand shard,
  * engine.cpp:129-131, 207-209, followed by the distance loop): every rank packs

@@ -19,7 +19,8 @@ torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
 dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
 dist.init_process_group("nccl", device_id=dev)
 impl, n, q, a, kmin, kmax = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6])
-eng = DistributedKNN(device=dev, impl=impl)
+grid = tuple(int(v) for v in sys.argv[7].split("x"))
+eng = DistributedKNN(device=dev, impl=impl, grid=grid)
 eng.synth_problem(n_total=n, q_total=q, a=a, lo=-100.0, hi=100.0, min_k=kmin, max_k=kmax, num_labels=7, seed=5)
 for step in range(3):                      # several steps: epochs, flag reuse, buffer reuse
     checked = eng.verify_against_oracle(10 ** 9)
@@ -51,21 +52,30 @@ def _world():
     return 8 if n >= 8 else 4 if n >= 4 else 2 if n >= 2 else 0
 
 
+def _grids(world):
+    """Data-sharded, query-sharded and (from 4 GPUs) a proper 2-D grid."""
+    g = [(world, 1), (1, world)]
+    if world >= 4:
+        g.append((2, world // 2))
+    return g
+
+
 @pytest.mark.parametrize("impl", ["fused", "nccl_cublas"])
 @pytest.mark.parametrize("shape", [(6000, 1000, 96, 1, 12), (3001, 515, 33, 2, 20), (20000, 700, 256, 16, 16)])
 def test_distributed_matches_oracle(tmp_path, repo_root, impl, shape):
     world = _world()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
-    out = _run(tmp_path, repo_root, world, impl, *shape)
-    assert out.count('"checked"') == world
-    if impl == "fused":
-        assert '"peer_fused": true' in out
+    for R, C in _grids(world):
+        out = _run(tmp_path, repo_root, world, impl, *shape, f"{R}x{C}")
+        assert out.count('"checked"') == world, (R, C)
+        if impl == "fused" and R > 1:
+            assert '"peer_fused": true' in out
 
 
 def test_distributed_large_k_takes_exact_path(tmp_path, repo_root):
     world = _world()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
-    out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 30, 60)
+    out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 30, 60, f"{world}x1")
     assert out.count('"checked"') == world
