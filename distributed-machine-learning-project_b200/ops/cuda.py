@@ -92,6 +92,30 @@ def stats_update(src, st):
     _check(_lib().dmlp_stats_update(_p(src), src.numel(), _p(st), _stream()))
 
 
+def stats_set(st, lo, hi):
+    """Install a host-computed value range into a stats block."""
+    lib = _lib()
+    lib.dmlp_stats_set.argtypes = [_vp, _dbl, _dbl, _vp]
+    _check(lib.dmlp_stats_set(_p(st), float(lo), float(hi), _stream()))
+
+
+def encode_decimal6(src):
+    """fp64 tensor -> (int32 tensor, ok): the decimal6 wire form, ok=False if any value does not round-trip."""
+    lib = _lib()
+    lib.dmlp_encode_decimal6.argtypes = [_vp, _vp, _i64, _vp, _vp]
+    dst = torch.empty(src.shape, dtype=torch.int32, device=src.device)
+    bad = torch.zeros(1, dtype=torch.int32, device=src.device)
+    _check(lib.dmlp_encode_decimal6(_p(src), _p(dst), src.numel(), _p(bad), _stream()))
+    return dst, int(bad.item()) == 0
+
+
+def expand_decimal6(src, dst):
+    lib = _lib()
+    lib.dmlp_expand_decimal6.argtypes = [_vp, _vp, _i64, _vp]
+    _check(lib.dmlp_expand_decimal6(_p(src), _p(dst), src.numel(), _stream()))
+    return dst
+
+
 def pack(src, rng, maxima=None, out=None):
     """fp64 [rows, a] -> (fp16 [rows, a_pad], norm2 [rows], errn [rows])."""
     rows, a = src.shape

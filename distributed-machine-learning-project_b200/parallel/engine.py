@@ -134,12 +134,14 @@ class DistributedKNN:
         if self.peer_rows:
             lay = Layout()
             lay.add("part_flags", 128)
+            lay.add("done_flags", 128)
             lay.add("x64", n * a * 8)
             lay.add("labels", n * 4)
             self.row_sym = sym = SymmetricBuffer(lay, dev, self.row_group)
             self.x = sym.view("x64", torch.float64, (n, a))
             self.labels = sym.view("labels", torch.int32)
             self.part_table = sym.pointer_table("part_flags")
+            self.done_table = sym.pointer_table("done_flags")
             self._row_gather_args = []
             for name, row_bytes in (("x64", a * 8), ("labels", 4)):
                 g = K.PeerGatherArgs()
@@ -263,7 +265,8 @@ class DistributedKNN:
             for g in self._row_gather_args:
                 g.epoch = self.epoch
                 K.peer_gather(g)
-            self.launch_count += 3
+            self.row_sym.signal(self.done_table, self.epoch)     # "I have finished reading your parts"
+            self.launch_count += 4
         elif len(set(self._row_sizes)) == 1:
             dist.all_gather_into_tensor(self.x, self.x_part.contiguous(), group=self.row_group)
             dist.all_gather_into_tensor(self.labels, self.labels_part.contiguous(), group=self.row_group)
@@ -384,29 +387,157 @@ class DistributedKNN:
         return label[:self.nq], checksum[:self.nq]
 
     # ---------------------------------------------------------------- end to end
-    def stage_host_inputs(self):
-        """Copy this rank's inputs into pinned host memory (the loader's output)."""
-        self.host = {
-            "x": self.x_part.cpu().pin_memory(), "labels": self.labels_part.cpu().pin_memory(),
-            "q": self.q_slice.cpu().pin_memory(), "k": self.k_slice.cpu().pin_memory(),
-        }
-        self.host_out = (torch.empty(self.nq, dtype=torch.int32).pin_memory(),
-                         torch.empty(self.nq, dtype=torch.int64).pin_memory())
-        self.h2d_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host.values())
-        self.d2h_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host_out)
+    E2E_CHUNK_ROWS = 18944   # 74 cluster rows of 256 queries: whole waves of the filter GEMM
+
+    def stage_host_inputs(self, wire="auto"):
+        """The loader's output: this rank's inputs in pinned host memory, plus the value
+        range (so no device pass over the data is needed before packing can start).
+
+        wire = "fp64" keeps doubles on the wire; "decimal6" sends the six-decimal values of
+        the text grammar as 32-bit integers (half the PCIe bytes, expanded bit-exactly on
+        the device); "auto" picks decimal6 when every value on every rank round-trips."""
+        dev = self.device
+        with torch.cuda.device(dev):
+            use_dec = False
+            if wire in ("auto", "decimal6"):
+                xi, ok_x = K.encode_decimal6(self.x_part)
+                qi, ok_q = K.encode_decimal6(self.q_slice)
+                ok = torch.tensor([1 if (ok_x and ok_q) else 0], dtype=torch.int32, device=dev)
+                if self.world > 1:
+                    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                use_dec = bool(ok.item())
+                if wire == "decimal6" and not use_dec:
+                    raise ValueError("inputs are not representable in the decimal6 wire format")
+            lo = min(self.x_part.min().item() if self.x_part.numel() else 0.0,
+                     self.q_slice.min().item() if self.q_slice.numel() else 0.0)
+            hi = max(self.x_part.max().item() if self.x_part.numel() else 0.0,
+                     self.q_slice.max().item() if self.q_slice.numel() else 0.0)
+            rng = torch.tensor([-lo, hi], dtype=torch.float64, device=dev)
+            if self.world > 1:
+                dist.all_reduce(rng, op=dist.ReduceOp.MAX)
+            self.host_range = (-rng[0].item(), rng[1].item())
+            self.wire = "decimal6" if use_dec else "fp64"
+            self.host = {
+                "x": (xi if use_dec else self.x_part).cpu().pin_memory(),
+                "labels": self.labels_part.cpu().pin_memory(),
+                "q": (qi if use_dec else self.q_slice).cpu().pin_memory(),
+                "k": self.k_slice.cpu().pin_memory(),
+            }
+            self.host_out = (torch.empty(self.nq, dtype=torch.int32).pin_memory(),
+                             torch.empty(self.nq, dtype=torch.int64).pin_memory())
+            self.h2d_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host.values())
+            self.d2h_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host_out)
+            self.streamed = self.R == 1 and self.fused_ok and self.impl == "fused"
+            self.copy_stream = torch.cuda.Stream(device=dev)
+            rows = min(self.E2E_CHUNK_ROWS, max(self.nq, 1))
+            self.chunk_rows = rows
+            if use_dec:
+                self.x_wire = torch.empty(self.x_part.shape, dtype=torch.int32, device=dev)
+                self.q_wire = [torch.empty((rows, self.a), dtype=torch.int32, device=dev) for _ in range(2)]
+            self._cand_by_rows = {}
+            torch.cuda.synchronize(dev)
 
     def run_from_host(self):
-        """Public end-to-end call: pinned host inputs -> device -> job -> host results."""
+        """Public end-to-end call: pinned host inputs -> device -> job -> host results.
+        With a single-rank column the copy of the next query chunk overlaps the
+        kernels of the current one (two streams)."""
+        with torch.cuda.device(self.device):
+            if getattr(self, "streamed", False):
+                label, checksum = self._run_streamed()
+            else:
+                label, checksum = self._run_copy_then_compute()
+            self.host_out[0].copy_(label, non_blocking=True)
+            self.host_out[1].copy_(checksum, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return self.host_out
+
+    def _wait_part_readers(self):
+        """Before this rank's part of the data shard is overwritten: every rank of the row
+        must have finished pulling the previous step's copy."""
+        if self.peer_rows and self.epoch > 0:
+            self.row_sym.wait("done_flags", self.epoch, self.status)
+
+    def _run_copy_then_compute(self):
         h = self.host
-        self.x_part.copy_(h["x"], non_blocking=True)
+        self._wait_part_readers()
+        if self.wire == "decimal6":
+            self.x_wire.copy_(h["x"], non_blocking=True)
+            K.expand_decimal6(self.x_wire, self.x_part)
+            for b in range(0, self.nq, self.chunk_rows):
+                e = min(b + self.chunk_rows, self.nq)
+                self.q_wire[0][: e - b].copy_(h["q"][b:e], non_blocking=True)
+                K.expand_decimal6(self.q_wire[0][: e - b], self.q_slice[b:e])
+        else:
+            self.x_part.copy_(h["x"], non_blocking=True)
+            self.q_slice.copy_(h["q"], non_blocking=True)
         self.labels_part.copy_(h["labels"], non_blocking=True)
-        self.q_slice.copy_(h["q"], non_blocking=True)
         self.k_slice.copy_(h["k"], non_blocking=True)
-        label, checksum = self.run_resident()
-        self.host_out[0].copy_(label, non_blocking=True)
-        self.host_out[1].copy_(checksum, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return self.host_out
+        return self.run_resident()
+
+    def _run_streamed(self):
+        h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream
+        dec = self.wire == "decimal6"
+        nq, rows = self.nq, self.chunk_rows
+        chunks = [(b, min(b + rows, nq)) for b in range(0, nq, rows)]
+        cs.wait_stream(main)                      # previous step's readers of the buffers are done
+        e_x = torch.cuda.Event()
+        e_q = [torch.cuda.Event() for _ in chunks]
+        e_free = [None, None]
+        with torch.cuda.stream(cs):
+            self._wait_part_readers()
+            (self.x_wire if dec else self.x_part).copy_(h["x"], non_blocking=True)
+            self.labels_part.copy_(h["labels"], non_blocking=True)
+            self.k_slice.copy_(h["k"], non_blocking=True)
+            e_x.record(cs)
+        # data shard: expand, all-gather along the row, pack
+        self.epoch += 1
+        main.wait_event(e_x)
+        if dec:
+            K.expand_decimal6(self.x_wire, self.x_part)
+        self._gather_shard()
+        K.stats_reset(self.stats)
+        K.stats_reset(self.q_stats)
+        K.stats_set(self.stats, *self.host_range)
+        K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+        od, oi, ol, flags, nflag = self.lists
+        nflag.zero_()
+        self.launch_count += 4 + (1 if dec else 0)
+        for i, (b, e) in enumerate(chunks):
+            with torch.cuda.stream(cs):
+                if dec:
+                    if e_free[i & 1] is not None:
+                        cs.wait_event(e_free[i & 1])          # the expand of chunk i-2 has drained this buffer
+                    self.q_wire[i & 1][: e - b].copy_(h["q"][b:e], non_blocking=True)
+                else:
+                    self.q_slice[b:e].copy_(h["q"][b:e], non_blocking=True)
+                e_q[i].record(cs)
+            main.wait_event(e_q[i])
+            if dec:
+                K.expand_decimal6(self.q_wire[i & 1][: e - b], self.q_slice[b:e])
+                e_free[i & 1] = torch.cuda.Event()
+                e_free[i & 1].record(main)
+            qh, qn, qe = self.qh[b:e], self.qn[b:e], self.qe_[b:e]
+            K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(qh, qn, qe))
+            key = e - b
+            if key not in self._cand_by_rows:
+                plan = K.topk_plan(key, max(self.shard_rows, 1), self.a_pad)
+                self._cand_by_rows[key] = torch.empty((key, plan["chunks"], plan["kp"]), dtype=torch.int64,
+                                                      device=self.device)
+            cand = self._cand_by_rows[key]
+            K.dist_topk(qh, self.xh, self.xn, cand=cand)
+            K.rerank(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], qn, qe, self.stats, self.stats,
+                     self.id_base, self.kmax, out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
+            self.launch_count += 5 + (1 if dec else 0)
+        label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+        self.launch_count += 1
+        flagged = int(nflag.item())
+        if flagged:
+            rows_f = torch.nonzero(flags[:nq], as_tuple=False).flatten().to(torch.int32)
+            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows_f, out=(od, oi, ol))
+            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+            self.launch_count += 4
+        self.last_flagged = flagged
+        return label, checksum
 
     def check_watchdog(self):
         """Non-zero means a peer signal timed out somewhere."""

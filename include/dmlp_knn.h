@@ -38,6 +38,18 @@ int dmlp_stats_update(const double *src, int64_t count, void *stats, void *strea
 int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16,
               float *norm2, float *errn, void *maxima, void *stream);
 
+/* Install a value range computed elsewhere (e.g. by the loader on the host) instead
+ * of running dmlp_stats_update over the data.  The row maxima are left untouched. */
+int dmlp_stats_set(void *stats, double lo, double hi, void *stream);
+
+/* "decimal6" wire format for the host->device copy (reference: the text grammar's
+ * "%.6f" values, generate_input.py:15,20): a value that equals i / 1e6 for a 32-bit
+ * integer i travels as i.  encode checks the round trip for every element (sets
+ * *bad to 1 otherwise) and is meant for load time; expand reproduces the doubles
+ * bit-for-bit on the device. */
+int dmlp_encode_decimal6(const double *src, int *dst, int64_t count, int *bad, void *stream);
+int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *stream);
+
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
  * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
  * candidate buffer holds q * chunks * kp 64-bit keys. */

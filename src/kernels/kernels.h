@@ -98,6 +98,9 @@ struct ScatterArgs {
   unsigned long long off_dist = 0, off_id = 0, off_label = 0;
 };
 
+int launch_expand_decimal6(const int *src, double *dst, long long count, cudaStream_t s);
+int launch_encode_decimal6(const double *src, int *dst, long long count, int *bad, cudaStream_t s);
+
 // dist_topk.cu  (cand: [q_rows][chunks][kp] keys, ascending per list)
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
                      unsigned long long *cand, const GatherArgs *gather, cudaStream_t s);

@@ -117,6 +117,55 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
   }
 }
 
+// Wire format "decimal6": the text grammar carries six decimals, so a value whose
+// scaled integer fits 32 bits travels as that integer (half the PCIe bytes of an
+// fp64) and is expanded here.  (double)i / 1e6 with IEEE division is correctly
+// rounded, i.e. exactly the double a text parser produces for that decimal.
+__global__ void __launch_bounds__(256) expand_decimal6_kernel(const int *__restrict__ src, double *__restrict__ dst,
+                                                              long long count) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride)
+    dst[i] = __ddiv_rn(static_cast<double>(src[i]), 1e6);
+}
+
+// Checks that every value survives the decimal6 round trip and emits the integers.
+__global__ void __launch_bounds__(256) encode_decimal6_kernel(const double *__restrict__ src, int *__restrict__ dst,
+                                                              long long count, int *bad) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  int local_bad = 0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
+    const double v = src[i];
+    const double scaled = rint(__dmul_rn(v, 1e6));
+    int iv = 0;
+    if (fabs(scaled) < 2147483647.0) {
+      iv = static_cast<int>(scaled);
+      if (__ddiv_rn(static_cast<double>(iv), 1e6) != v) local_bad = 1;
+    } else {
+      local_bad = 1;
+    }
+    dst[i] = iv;
+  }
+  if (local_bad) atomicExch(bad, 1);
+}
+
+int launch_expand_decimal6(const int *src, double *dst, long long count, cudaStream_t s) {
+  if (count <= 0) return 0;
+  long long blocks = (count + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  expand_decimal6_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, dst, count);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_encode_decimal6(const double *src, int *dst, long long count, int *bad, cudaStream_t s) {
+  if (count <= 0) return 0;
+  long long blocks = (count + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  encode_decimal6_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, dst, count, bad);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int launch_stats_reset(PackStats *st, cudaStream_t s) {
   stats_reset_kernel<<<1, 32, 0, s>>>(st);
   DMLP_CUDA_OK(cudaGetLastError());

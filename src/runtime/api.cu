@@ -61,6 +61,20 @@ int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *ran
                      norm2, errn, static_cast<PackStats *>(maxima), st(stream));
 }
 
+int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *stream) {
+  return launch_expand_decimal6(src, dst, count, st(stream));
+}
+
+int dmlp_encode_decimal6(const double *src, int *dst, int64_t count, int *bad, void *stream) {
+  return launch_encode_decimal6(src, dst, count, bad, st(stream));
+}
+
+int dmlp_stats_set(void *stats, double lo, double hi, void *stream) {
+  const double v[2] = {-lo, hi};
+  DMLP_CUDA_OK(cudaMemcpyAsync(stats, v, sizeof v, cudaMemcpyHostToDevice, st(stream)));
+  return 0;
+}
+
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]) {
   TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
   plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.chunks;

@@ -168,3 +168,34 @@ def test_model_api_all_paths(K):
     big_k = np.full(300, 64, np.int32)
     _, want_sum, *_ = cpu.knn(data, labels, queries, big_k)
     assert (knn(data, labels, queries, big_k).checksums_u64() == want_sum).all()
+
+
+def test_decimal6_wire_round_trip(K):
+    data, *_ = cpu.synth(500, 1, 33, -100.0, 100.0, 1, 1, 2, seed=8)
+    x = _dev(data)
+    enc, ok = K.encode_decimal6(x)
+    assert ok
+    out = K.expand_decimal6(enc, torch.empty_like(x))
+    assert torch.equal(out, x)                                  # bit-exact doubles back
+    assert (enc.cpu().numpy() == np.rint(data * 1e6).astype(np.int64)).all()
+    bad = x.clone()
+    bad[3, 3] = 0.1234567                                       # seven decimals: not representable
+    assert not K.encode_decimal6(bad)[1]
+    big = x.clone()
+    big[0, 0] = 5000.0                                          # 5e9 does not fit 32 bits
+    assert not K.encode_decimal6(big)[1]
+
+
+def test_streamed_end_to_end_single_gpu(K):
+    from dmlp_b200.parallel import DistributedKNN
+    eng = DistributedKNN(device=torch.device("cuda", 0))
+    eng.synth_problem(n_total=9000, q_total=40000, a=64, lo=-100.0, hi=100.0, min_k=1, max_k=12, num_labels=5, seed=3)
+    _, ref = eng.run_resident()
+    ref = ref.cpu().numpy().copy()
+    for wire in ("auto", "fp64"):
+        eng.stage_host_inputs(wire=wire)
+        assert eng.streamed and eng.wire == ("decimal6" if wire == "auto" else "fp64")
+        for _ in range(2):
+            _, chk = eng.run_from_host()
+            assert (chk.numpy() == ref).all(), wire
+    assert eng.verify_against_oracle(200) == 200

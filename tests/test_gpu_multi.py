@@ -25,11 +25,14 @@ eng.synth_problem(n_total=n, q_total=q, a=a, lo=-100.0, hi=100.0, min_k=kmin, ma
 for step in range(3):                      # several steps: epochs, flag reuse, buffer reuse
     checked = eng.verify_against_oracle(10 ** 9)
 assert eng.check_watchdog() == 0
-eng.stage_host_inputs()
-lab, chk = eng.run_from_host()
 ref_lab, ref_chk = eng.run_resident()
-torch.cuda.synchronize()
-assert (chk.numpy() == ref_chk.cpu().numpy()).all()
+ref_chk = ref_chk.cpu().numpy().copy()
+for wire in ("auto", "fp64"):
+    eng.stage_host_inputs(wire=wire)
+    for step in range(3):                  # buffers are overwritten every step: reader/writer flags
+        lab, chk = eng.run_from_host()
+        assert (chk.numpy() == ref_chk).all(), (wire, step)
+assert eng.check_watchdog() == 0
 print(json.dumps({"rank": rank, "checked": checked, "flagged": eng.last_flagged, "peer_fused": bool(getattr(eng, "peer_fused", False))}))
 eng.close()
 dist.destroy_process_group()
