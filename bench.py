@@ -48,6 +48,7 @@ def parse_args():
     p.add_argument("--seed", type=int, default=42)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--verify", type=int, default=0, help="check this many queries against the CPU oracle")
+    p.add_argument("--ref-queries", type=int, default=8, help="queries timed by --impl reference")
     return p.parse_args()
 
 

@@ -1,0 +1,93 @@
+#!/usr/bin/env bash
+# Benchmark harness with the reference's command line (reference: run_bench.sh:3-27):
+#   ./run_bench.sh {1|2|3|4|all}
+# For each configuration it builds, runs the baseline once (cached in
+# outputs/test_N.{out,err}), runs ./engine into outputs/tmp.{out,err}, compares the
+# `Time taken` lines and -- unlike the reference, which leaves that to the reader
+# -- diffs the sorted result lines.
+#
+# What differs from the reference, and why:
+#   * no Slurm / mpirun: one process drives every visible GPU (DMLP_NGPU, DMLP_GRID);
+#   * baseline: benchmarks/bench_N need OpenMPI 4, which this image lacks, so the
+#     baseline is the unmodified reference engine.cpp built against a one-rank MPI
+#     stand-in (baseline/_ref_build/engine_ref, valid for constant k), else this
+#     repository's CPU oracle (DMLP_BACKEND=cpu ./engine);
+#   * inputs: inputs.zip is not shipped; missing inputs/inputN.in are generated
+#     with tools/generate_input.py at the sizes below (override with INPUT_ARGS_N).
+set -u
+cd "$(dirname "$0")"
+
+usage() {
+  cat <<USAGE
+Usage: $0 <CONFIG>
+
+  1    bench_1-style job: 1-D data shards, one gather      (input1)
+  2    bench_2-style job: data shards + list reduction      (input2)
+  3    bench_3-style job: same input as 2, 2-D device grid  (input2)
+  4    bench_4-style job: replicated data, queries sharded  (input3)
+  all  the four above in sequence
+USAGE
+  exit 1
+}
+[ "$#" -eq 1 ] || usage
+case "$1" in 1|2|3|4|all) ;; *) echo "Error: invalid CONFIG '$1'"; usage ;; esac
+
+INPUT_ARGS_1=${INPUT_ARGS_1:-"--num_data 20000 --num_queries 2000 --num_attrs 32 --min -100 --max 100 --minK 8 --maxK 8 --num_labels 10"}
+INPUT_ARGS_2=${INPUT_ARGS_2:-"--num_data 50000 --num_queries 4000 --num_attrs 64 --min -100 --max 100 --minK 16 --maxK 16 --num_labels 10"}
+INPUT_ARGS_3=${INPUT_ARGS_3:-"--num_data 30000 --num_queries 8000 --num_attrs 128 --min 0 --max 10 --minK 5 --maxK 5 --num_labels 4"}
+
+ngpu=$(nvidia-smi -L 2>/dev/null | wc -l)
+grid_for() {  # layout per configuration on the GPUs that are visible
+  local g=${ngpu:-0}; [ "$g" -lt 1 ] && g=1
+  case "$1" in
+    1|2) echo "${g}x1" ;;
+    3)   if [ "$g" -ge 4 ]; then echo "2x$((g / 2))"; else echo "${g}x1"; fi ;;
+    4)   echo "1x${g}" ;;
+  esac
+}
+input_for() { case "$1" in 1) echo 1 ;; 2|3) echo 2 ;; 4) echo 3 ;; esac; }
+
+time_of() { grep -oE 'Time taken:\s*[0-9]+' "$1" | grep -oE '[0-9]+' | head -1; }
+
+compare_times() {
+  local b e
+  b=$(time_of "$1"); e=$(time_of "$2")
+  if [ -z "$b" ] || [ -z "$e" ]; then echo "Error: no 'Time taken' line in $1 or $2"; return; fi
+  echo
+  echo "=== Performance Comparison ==="
+  echo "Benchmark time: ${b} ms"
+  echo "Engine time:    ${e} ms"
+  if [ "$b" -gt 0 ]; then
+    awk -v b="$b" -v e="$e" 'BEGIN { d = e - b; p = d / b * 100;
+      if (d > 0) printf "Difference:     +%d ms (%.2f%% slower)\n", d, p;
+      else if (d < 0) printf "Difference:     -%d ms (%.2f%% faster)\n", -d, -p;
+      else print "Difference:     0 ms (No difference)" }'
+  fi
+  echo "=============================="
+}
+
+compare_outputs() {
+  if diff <(sort "$1") <(sort "$2") > /dev/null; then echo "Results:        identical ($(wc -l < "$2") queries)"
+  else echo "Results:        DIFFER (sort $1 | diff - <(sort $2))"; fi
+}
+
+make -j8 all tools > /dev/null || { echo "build failed"; exit 1; }
+python3 -c "import bench_reference as b; b.ensure_reference()" > /dev/null 2>&1
+mkdir -p outputs inputs
+
+run_config() {
+  local n=$1 inp="inputs/input$(input_for "$1").in" args_var="INPUT_ARGS_$(input_for "$1")"
+  if [ ! -f "$inp" ]; then
+    echo "Generating $inp (${!args_var})"
+    python3 tools/generate_input.py ${!args_var} --seed 42 --output "$inp" > /dev/null
+  fi
+  if [ -f "outputs/test_$n.err" ]; then echo "Output found in cache. Skipping..."
+  elif [ -x baseline/_ref_build/engine_ref ]; then baseline/_ref_build/engine_ref < "$inp" 2> "outputs/test_$n.err" > "outputs/test_$n.out"
+  else DMLP_BACKEND=cpu ./engine < "$inp" 2> "outputs/test_$n.err" > "outputs/test_$n.out"; fi
+  DMLP_GRID=${DMLP_GRID:-$(grid_for "$n")} ./engine < "$inp" 2> outputs/tmp.err > outputs/tmp.out || cat outputs/tmp.err
+  compare_times "outputs/test_$n.err" outputs/tmp.err
+  compare_outputs "outputs/test_$n.out" outputs/tmp.out
+}
+
+if [ "$1" = "all" ]; then for c in 1 2 3 4; do echo "--- CONFIG $c ---"; run_config "$c"; done
+else run_config "$1"; fi

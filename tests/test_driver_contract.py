@@ -70,3 +70,25 @@ def test_bad_input_fails_cleanly(engine_bins, tmp_path):
     bad.write_text("1 1 1\n0 1.0\nX 1 1.0\n")
     res = _run(engine_bins[0], bad)
     assert res.returncode != 0 and "wrongly formatted" in res.stderr
+
+
+def test_run_bench_harness_flow(repo_root, tmp_path):
+    """run_bench.sh keeps the reference CLI: usage on bad args, baseline cache, time compare, output diff."""
+    sh = os.path.join(repo_root, "run_bench.sh")
+    res = subprocess.run([sh], capture_output=True, text=True)
+    assert res.returncode == 1 and "Usage" in res.stdout
+    res = subprocess.run([sh, "7"], capture_output=True, text=True)
+    assert res.returncode == 1 and "invalid CONFIG" in res.stdout
+    for stale in ("outputs/test_1.err", "outputs/test_1.out", "inputs/input1.in"):
+        p = os.path.join(repo_root, stale)
+        if os.path.exists(p):
+            os.remove(p)
+    env = dict(os.environ, DMLP_BACKEND="cpu", DMLP_STRATEGY="gather", DMLP_RANKS="2",
+               INPUT_ARGS_1="--num_data 300 --num_queries 40 --num_attrs 5 --min 0 --max 10 --minK 3 --maxK 3 --num_labels 3")
+    res = subprocess.run([sh, "1"], capture_output=True, text=True, env=env)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "=== Performance Comparison ===" in res.stdout and "Results:        identical (40 queries)" in res.stdout
+    res = subprocess.run([sh, "1"], capture_output=True, text=True, env=env)
+    assert "Output found in cache. Skipping..." in res.stdout
+    for stale in ("outputs/test_1.err", "outputs/test_1.out", "inputs/input1.in"):
+        os.remove(os.path.join(repo_root, stale))
