@@ -24,6 +24,9 @@ def _lib():
         lib.dmlp_result_checksum.argtypes = [C.c_int, _i, C.c_int64]
         lib.dmlp_result_checksum.restype = C.c_uint64
         lib.dmlp_merge_topk.argtypes = [_d, _i, _d, _i, C.c_int, _d, _i]
+        lib.dmlp_cpu_local_lists.argtypes = [_d, _i, C.c_int64, C.c_int, _d, _i, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                             _d, _i, _i]
+        lib.dmlp_cpu_finalize_lists.argtypes = [_d, _i, _i, C.c_int, C.c_int64, C.c_int, _i, _i, _u]
         lib.dmlp_parse_header.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int64),
                                           C.POINTER(C.c_int64), C.POINTER(C.c_int)]
         lib.dmlp_parse_text.argtypes = [C.c_char_p, C.c_size_t, C.c_int, _d, _i, _d, _i]
@@ -61,6 +64,35 @@ def knn(data, labels, queries, k, strategy="serial", ranks=1, rows=0, cols=0, th
                                strategy.encode(), ranks, rows, cols, threads,
                                out_label, out_sum, out_ids, out_dist))
     return out_label, out_sum, out_ids, out_dist, off
+
+
+def local_lists(data, labels, id_base, queries, k, kmax, threads=0):
+    """Per-shard exact k-lists ([q, kmax] dist / id / label, sentinel padded, global ids)."""
+    data = np.ascontiguousarray(data, dtype=np.float64)
+    queries = np.ascontiguousarray(queries, dtype=np.float64)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    k = np.ascontiguousarray(k, dtype=np.int32)
+    q, a = queries.shape
+    od = np.empty((q, kmax), np.float64)
+    oi = np.empty((q, kmax), np.int32)
+    ol = np.empty((q, kmax), np.int32)
+    _check(_lib().dmlp_cpu_local_lists(data.reshape(-1), labels, data.shape[0], id_base, queries.reshape(-1), k, q, a,
+                                       kmax, threads, od.reshape(-1), oi.reshape(-1), ol.reshape(-1)))
+    return od, oi, ol
+
+
+def finalize_lists(dist, ids, labels, k):
+    """Merge [sources, q, kmax] lists with the merge operator, vote, checksum."""
+    dist = np.ascontiguousarray(dist, dtype=np.float64)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    k = np.ascontiguousarray(k, dtype=np.int32)
+    sources, q, kmax = dist.shape
+    out_label = np.empty(q, np.int32)
+    out_sum = np.empty(q, np.uint64)
+    _check(_lib().dmlp_cpu_finalize_lists(dist.reshape(-1), ids.reshape(-1), labels.reshape(-1), sources, q, kmax, k,
+                                          out_label, out_sum))
+    return out_label, out_sum
 
 
 def exact_sqdist(a, b):

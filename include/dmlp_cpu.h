@@ -32,6 +32,16 @@ uint64_t dmlp_result_checksum(int label, const int *ids, int64_t k);
 void dmlp_merge_topk(const double *xd, const int *xi, const double *yd, const int *yi, int k,
                      double *od, int *oi);
 
+/* The two halves of the distributed job, for multi-process CPU runs (gloo): per-shard
+ * sorted, sentinel-padded k-lists with global ids (engine.cpp:233-257), and the
+ * owner-side merge + vote + checksum over `sources` such lists (engine.cpp:289-347).
+ * Lists are [q][kmax] with stride kmax. */
+int dmlp_cpu_local_lists(const double *data_attrs, const int *data_labels, int64_t n, int id_base,
+                         const double *query_attrs, const int *query_k, int64_t q, int a, int kmax, int threads,
+                         double *out_dist, int *out_id, int *out_label);
+int dmlp_cpu_finalize_lists(const double *dist, const int *id, const int *label, int sources, int64_t q, int kmax,
+                            const int *query_k, int *out_label, uint64_t *out_checksum);
+
 /* Text parser (common.cpp:93-117 grammar).  Two steps: read the header, then
  * fill caller-owned arrays. */
 int dmlp_parse_header(const char *text, size_t len, int64_t *n, int64_t *q, int *a);

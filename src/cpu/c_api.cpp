@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <exception>
 #include <stdexcept>
+#include <thread>
 #include <vector>
 #include <string>
 
@@ -70,6 +71,55 @@ void dmlp_merge_topk(const double *xd, const int *xi, const double *yd, const in
   for (int i = 0; i < k; ++i) { x[i] = {xd[i], xi[i], 0}; y[i] = {yd[i], yi[i], 0}; }
   dmlp::merge_topk(x.data(), y.data(), k, o.data());
   for (int i = 0; i < k; ++i) { od[i] = o[i].dist; oi[i] = o[i].id; }
+}
+
+int dmlp_cpu_local_lists(const double *data_attrs, const int *data_labels, int64_t n, int id_base,
+                         const double *query_attrs, const int *query_k, int64_t q, int a, int kmax, int threads,
+                         double *out_dist, int *out_id, int *out_label) {
+  return guarded([&] {
+    dmlp::DatasetView d; d.n = n; d.a = a; d.attrs = data_attrs; d.labels = data_labels; d.id_base = id_base;
+    if (threads <= 0) threads = int(std::thread::hardware_concurrency());
+    if (threads < 1) threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+      pool.emplace_back([&, t] {
+        std::vector<dmlp::Neighbor> tmp(static_cast<size_t>(kmax > 0 ? kmax : 1));
+        for (int64_t i = q * t / threads; i < q * (t + 1) / threads; ++i) {
+          int k = query_k[i] < 0 ? 0 : (query_k[i] > kmax ? kmax : query_k[i]);
+          dmlp::local_topk(d, query_attrs + i * a, k, tmp.data());
+          for (int j = 0; j < kmax; ++j) {
+            const bool real = j < k;
+            out_dist[i * kmax + j] = real ? tmp[size_t(j)].dist : dmlp::kSentinelDist;
+            out_id[i * kmax + j] = real ? tmp[size_t(j)].id : dmlp::kSentinelId;
+            out_label[i * kmax + j] = real ? tmp[size_t(j)].label : -1;
+          }
+        }
+      });
+    for (auto &th : pool) th.join();
+  });
+}
+
+int dmlp_cpu_finalize_lists(const double *dist, const int *id, const int *label, int sources, int64_t q, int kmax,
+                            const int *query_k, int *out_label, uint64_t *out_checksum) {
+  return guarded([&] {
+    std::vector<dmlp::Neighbor> acc, next, cur;
+    for (int64_t i = 0; i < q; ++i) {
+      int k = query_k[i] < 0 ? 0 : (query_k[i] > kmax ? kmax : query_k[i]);
+      const size_t kk = static_cast<size_t>(k);
+      acc.assign(kk, dmlp::Neighbor{dmlp::kSentinelDist, dmlp::kSentinelId, -1});
+      next.resize(kk); cur.resize(kk);
+      for (int s = 0; s < sources; ++s) {
+        const int64_t base = (int64_t(s) * q + i) * kmax;
+        for (int j = 0; j < k; ++j) cur[size_t(j)] = dmlp::Neighbor{dist[base + j], id[base + j], label[base + j]};
+        dmlp::merge_topk(acc.data(), cur.data(), k, next.data());   // the reduction operator, applied source by source
+        acc.swap(next);
+      }
+      dmlp::ResultSet rs;
+      dmlp::finalize_query(acc.data(), k, &rs);
+      out_label[i] = rs.label[0];
+      out_checksum[i] = rs.checksum[0];
+    }
+  });
 }
 
 int dmlp_parse_header(const char *text, size_t len, int64_t *n, int64_t *q, int *a) {
