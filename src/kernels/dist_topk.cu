@@ -48,6 +48,7 @@ struct Item {
   int m;
   int chunk;
   int tile_begin, tile_end;
+  int group, group_rows;  // which wave-group this item belongs to and how many cluster rows it has
 };
 
 // Work items are enumerated per cluster: item t names a cluster row (`cluster`
@@ -60,6 +61,8 @@ __device__ __forceinline__ bool get_item(const TopkPlan &p, int t, int cta_rank,
   const int gm = min(p.group_mc, p.mc_blocks - m0);
   if (gm <= 0 || rem >= gm * p.chunks) return false;
   const int c = rem / gm;
+  it->group = g;
+  it->group_rows = gm;
   it->m = ((m0 + (rem - c * gm) + p.rot) % p.mc_blocks) * p.cluster + cta_rank;  // may be a phantom block past m_blocks
   it->chunk = c;
   it->tile_begin = static_cast<int>(static_cast<long long>(c) * p.n_tiles / p.chunks);
@@ -559,6 +562,7 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       for (int t = cluster_id; t < total_items; t += num_clusters) {
         Item it;
         if (!get_item(plan, t, cta_rank, &it)) continue;
+        unsigned sync_epoch = 0;
         if (ga.world > 1) {
           // the block's packed rows may still be on their way from their owner
           const unsigned target = ga.epoch * BM;
@@ -579,6 +583,20 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         }
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
+            if (plan.sync && cta_rank == 0 && it.group_rows > 1 && (kb % plan.sync) == 0) {
+              // Re-align the pairs that sweep this chunk.  They read the same data tiles; L2
+              // only holds a few k-blocks of every stream, so once the pairs drift apart each
+              // one re-fetches the tile from HBM.  One counter per (group, chunk): arrive,
+              // then wait until all of the group's pairs have reached this point of the sweep.
+              unsigned *cnt = plan.sync_cnt + (it.group * plan.chunks + it.chunk);
+              atomicAdd(cnt, 1u);
+              ++sync_epoch;
+              const unsigned target = static_cast<unsigned>(it.group_rows) * sync_epoch;
+              const long long t0 = clock64();
+              while (static_cast<int>(ld_acquire_gpu(cnt) - target) < 0) {
+                if (clock64() - t0 > 2000000000LL) break;  // never hang on a lost peer
+              }
+            }
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + BH_BYTES));
             tma_load_2d_pair(smem + L::kOffA + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM, pol_q);
@@ -695,6 +713,10 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   if (p.pair) cluster = 2;
   p.prefetch = 0;
   p.rot = 0;
+  p.sync = p.k_blocks;   // re-align once per data tile; DMLP_TOPK_SYNC=<k-blocks between alignments>, 0 = off
+  p.sync_cnt = nullptr;
+  if (const char *e = getenv("DMLP_TOPK_SYNC")) p.sync = atoi(e);
+  if (p.sync < 0) p.sync = 0;
   if (const char *e = getenv("DMLP_TOPK_PREFETCH")) p.prefetch = atoi(e);
   // Cluster: CTAs that sweep the same data tiles in lock step and share each
   // tile through TMA multicast.  Never wider than the number of row blocks.
@@ -733,13 +755,37 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   p.chunks = c;
   long long items = static_cast<long long>((p.mc_blocks + gmc - 1) / gmc) * gmc * c;
   int use = static_cast<int>(items < nclusters ? (items > 0 ? items : 1) : nclusters);
+  // one wave = one whole group (gmc x c clusters), so that clusters sharing a chunk run side by side
+  if (p.pair && static_cast<long long>(gmc) * c <= use) use = gmc * c;
   p.grid = use * cluster;
   return p;
 }
 
-int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
+namespace {
+constexpr int kSyncCounters = 16384;
+__device__ unsigned g_sync_counters[kSyncCounters];
+}  // namespace
+
+int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan_in,
                      unsigned long long *cand, const GatherArgs *gather, cudaStream_t s) {
+  TopkPlan plan = plan_in;
   if (plan.q_rows <= 0 || plan.n <= 0) return 0;
+  {
+    // per-launch tile-alignment counters (internal scratch, one set per device)
+    const int groups = (plan.mc_blocks + plan.group_mc - 1) / plan.group_mc;
+    const long long need = static_cast<long long>(groups) * plan.chunks;
+    // the alignment wait needs every cluster of a group on the chip at once: only when the
+    // grid is a single wave of whole groups
+    const bool whole_wave = plan.pair && plan.group_mc * plan.chunks * plan.cluster == plan.grid;
+    if (plan.sync && whole_wave && need <= kSyncCounters) {
+      void *p = nullptr;
+      DMLP_CUDA_OK(cudaGetSymbolAddress(&p, g_sync_counters));
+      DMLP_CUDA_OK(cudaMemsetAsync(p, 0, sizeof(unsigned) * need, s));
+      plan.sync_cnt = static_cast<unsigned *>(p);
+    } else {
+      plan.sync = 0;
+    }
+  }
   DMLP_REQUIRE(plan.kp == KP, "dist_topk: this build keeps 32 keys per (query, chunk)");
   DMLP_REQUIRE(plan.a_pad % BK == 0 && plan.a_pad > 0, "dist_topk: a_pad must be a positive multiple of 64");
   CUtensorMap tm_q, tm_x;
