@@ -55,25 +55,33 @@ def _world():
     return 8 if n >= 8 else 4 if n >= 4 else 2 if n >= 2 else 0
 
 
-def _grids(world):
-    """Data-sharded, query-sharded and (from 4 GPUs) a proper 2-D grid."""
-    g = [(world, 1), (1, world)]
-    if world >= 4:
-        g.append((2, world // 2))
-    return g
+S0, S1, S2 = (6000, 1000, 96, 1, 12), (3001, 515, 33, 2, 20), (20000, 700, 256, 16, 16)
+CASES = [("fused", S0, "rows"), ("fused", S0, "cols"), ("fused", S1, "rows"), ("fused", S1, "cols"),
+         ("fused", S2, "rows"), ("nccl_cublas", S0, "rows"), ("nccl_cublas", S1, "cols"),
+         ("fused", S1, "2d"), ("nccl_cublas", S0, "2d")]
 
 
-@pytest.mark.parametrize("impl", ["fused", "nccl_cublas"])
-@pytest.mark.parametrize("shape", [(6000, 1000, 96, 1, 12), (3001, 515, 33, 2, 20), (20000, 700, 256, 16, 16)])
-def test_distributed_matches_oracle(tmp_path, repo_root, impl, shape):
+def _grid(kind, world):
+    """rows: pure data sharding (R x 1); cols: pure query sharding (1 x C); 2d: needs >= 4 GPUs."""
+    if kind == "rows":
+        return world, 1
+    if kind == "cols":
+        return 1, world
+    return (2, world // 2) if world >= 4 else None
+
+
+@pytest.mark.parametrize("impl,shape,kind", CASES)
+def test_distributed_matches_oracle(tmp_path, repo_root, impl, shape, kind):
     world = _world()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
-    for R, C in _grids(world):
-        out = _run(tmp_path, repo_root, world, impl, *shape, f"{R}x{C}")
-        assert out.count('"checked"') == world, (R, C)
-        if impl == "fused" and R > 1:
-            assert '"peer_fused": true' in out
+    grid = _grid(kind, world)
+    if grid is None:
+        pytest.skip("a 2-D grid needs at least 4 GPUs")
+    out = _run(tmp_path, repo_root, world, impl, *shape, f"{grid[0]}x{grid[1]}")
+    assert out.count('"checked"') == world
+    if impl == "fused" and grid[0] > 1:
+        assert '"peer_fused": true' in out
 
 
 def test_distributed_large_k_takes_exact_path(tmp_path, repo_root):
