@@ -35,13 +35,15 @@ if ROOT not in sys.path:
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl_cublas"])
     p.add_argument("--num-attrs", type=int, default=8192)
     p.add_argument("--num-queries", type=int, default=65536, help="queries per GPU (weak scaling axis)")
     p.add_argument("--num-data", type=int, default=65536, help="datapoints in total (fixed)")
-    p.add_argument("--grid", default="", help="RxC (data shards x query shards); default 1xN")
+    p.add_argument("--grid", default="", help="RxC (data shards x query shards); default 1xN (Nx1 with --scale data)")
+    p.add_argument("--scale", default="queries", choices=["queries", "data"],
+                   help="weak-scaling axis: queries per GPU fixed (default), or datapoints per GPU fixed")
     p.add_argument("--min-k", type=int, default=4)
     p.add_argument("--max-k", type=int, default=16)
     p.add_argument("--labels", type=int, default=10)
@@ -87,10 +89,12 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     from dmlp_b200.parallel import DistributedKNN
-    grid = tuple(int(v) for v in args.grid.lower().split("x")) if args.grid else (1, world)
+    by_data = args.scale == "data"
+    grid = tuple(int(v) for v in args.grid.lower().split("x")) if args.grid else ((world, 1) if by_data else (1, world))
     eng = DistributedKNN(device=dev, impl="fused" if args.impl == "ours" else "nccl_cublas", grid=grid)
-    A, N = args.num_attrs, args.num_data
-    Q = args.num_queries * world
+    A = args.num_attrs
+    N = args.num_data * (world if by_data else 1)
+    Q = args.num_queries * (1 if by_data else world)
     eng.synth_problem(n_total=N, q_total=Q, a=A, lo=-100.0, hi=100.0, min_k=args.min_k, max_k=args.max_k,
                       num_labels=args.labels, seed=args.seed)
 
@@ -166,7 +170,8 @@ def main():
             "data": "synthetic (generate_input.py distribution, uniform [-100,100] 6 decimals), on-device generator",
             "impl": args.impl,
             "config": {"model": "knn synthetic hidden(num_attrs)=%d batch(num_queries)=%d per GPU" % (A, args.num_queries),
-                       "global_batch": Q, "seq_len": A, "num_data_total": N, "queries_per_gpu": args.num_queries,
+                       "global_batch": Q, "seq_len": A, "num_data_total": N, "queries_per_gpu": Q // world,
+                       "weak_scaling_axis": args.scale,
                        "k": [args.min_k, args.max_k],
                        "parallelism": "grid R=%d (data shards) x C=%d (query shards)" % (eng.R, eng.C),
                        "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed"

@@ -1,4 +1,5 @@
 """Device-side timing and clock sampling (the reference has one wall clock)."""
+import os
 import statistics
 import subprocess
 import threading
@@ -11,54 +12,76 @@ _QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
 
 
 class ClockSampler:
-    """Samples nvidia-smi every `period_ms` in the background while a timed region runs."""
+    """Samples SM clocks and throttle reasons of one GPU in a background thread while a
+    timed region runs.  Uses NVML in-process (first sample within milliseconds, so short
+    regions are covered); falls back to polling nvidia-smi."""
 
-    def __init__(self, gpu_index=0, period_ms=200):
-        self.gpu_index, self.period_ms = gpu_index, period_ms
-        self.samples, self._proc, self._thread = [], None, None
+    _REASONS = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+
+    def __init__(self, gpu_index=0, period_ms=50):
+        self.gpu_index, self.period = gpu_index, period_ms / 1e3
+        self.sm, self.reasons, self.sm_max = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if self.gpu_index < len(ids) and ids[self.gpu_index].isdigit():
+                return int(ids[self.gpu_index])
+        return self.gpu_index
+
+    def _run_nvml(self):
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index())
+        self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop.is_set():
+            self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+            mask = int(get_reasons(h))
+            for name, bit in self._REASONS.items():
+                if mask & bit:
+                    self.reasons.add(name)
+            self._stop.wait(self.period)
+
+    def _run_smi(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={_QUERY}", "--format=csv,noheader,nounits", "-i",
+                                      str(self._physical_index())], capture_output=True, text=True, timeout=10).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                self.sm.append(float(parts[0]))
+                self.sm_max = float(parts[1])
+                for name, val in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"],
+                                     parts[3:7]):
+                    if val.lower().startswith("active"):
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(max(self.period, 0.2))
+
+    def _run(self):
+        try:
+            self._run_nvml()
+        except Exception:
+            self._run_smi()
 
     def __enter__(self):
-        try:
-            self._proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={_QUERY}", "--format=csv,noheader,nounits", "-i", str(self.gpu_index),
-                 "-lms", str(self.period_ms)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            self._proc = None
-            return self
-
-        def pump():
-            for line in self._proc.stdout:
-                parts = [p.strip() for p in line.split(",")]
-                if len(parts) >= 7:
-                    self.samples.append(parts)
-        self._thread = threading.Thread(target=pump, daemon=True)
+        self._thread = threading.Thread(target=self._run, daemon=True)
         self._thread.start()
         return self
 
     def __exit__(self, *exc):
-        if self._proc is not None:
-            self._proc.terminate()
-            try:
-                self._proc.wait(timeout=5)
-            except subprocess.TimeoutExpired:
-                self._proc.kill()
-            self._thread.join(timeout=5)
+        self._stop.set()
+        self._thread.join(timeout=15)
         return False
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            try:
-                sm.append(float(s[0]))
-                mx.append(float(s[1]))
-            except ValueError:
-                continue
-            for name, val in zip(names, s[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
 def time_steps(step_fn, steps, warmup, barrier=None):
