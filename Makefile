@@ -65,3 +65,21 @@ clean:
 	rm -rf $(B) engine engine.debug $(LIBDIR)/*.so tools/dmlp-gen outputs/tmp.*
 
 -include $(shell find $(B) -name '*.d' 2>/dev/null)
+
+# ---- sanitizers (the reference has none) --------------------------------------
+# Host: CPU-only driver under ASan + UBSan, run over every CPU strategy on a generated input.
+.PHONY: asan sanitize-gpu
+ASAN_CXX ?= /usr/bin/g++
+ASAN_FLAGS = -O1 -g -std=c++17 -ffp-contract=off -pthread -Iinclude -fsanitize=address,undefined -fno-omit-frame-pointer
+engine.asan: $(HOST_CPP) src/driver/main.cpp src/engine/gpu_stub.cpp
+	$(ASAN_CXX) $(ASAN_FLAGS) $^ -o $@
+asan: engine.asan
+	python3 tools/generate_input.py --num_data 600 --num_queries 50 --num_attrs 7 --min -5 --max 5 --minK 1 --maxK 9 \
+	    --num_labels 4 --output /tmp/dmlp_asan.in > /dev/null
+	for s in serial grid gather tree farm kdtree; do \
+	  DMLP_BACKEND=cpu DMLP_STRATEGY=$$s DMLP_RANKS=6 ./engine.asan < /tmp/dmlp_asan.in | sort | md5sum || exit 1; done
+	DMLP_BACKEND=cpu DMLP_STRATEGY=grid DMLP_GRID=4x2 ./engine.asan --aos < /tmp/dmlp_asan.in | sort | md5sum
+# Device: every kernel on small shapes under compute-sanitizer (one tool per run: TOOL=memcheck|racecheck|synccheck).
+TOOL ?= memcheck
+sanitize-gpu: libs
+	compute-sanitizer --tool $(TOOL) --error-exitcode 9 python3 scripts/sanitize_case.py

@@ -24,7 +24,10 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
+import os
+
 from ..ops import cuda as K
+from ..utils.timing import PhaseTracer
 from .grid import Grid, even_slice
 from .symm import Layout, SymmetricBuffer
 
@@ -60,6 +63,7 @@ class DistributedKNN:
         self.epoch = 0
         self.host = None
         self.sym = self.row_sym = None
+        self.tracer = PhaseTracer(os.environ.get("DMLP_TRACE", "0") not in ("", "0"))
 
     # ------------------------------------------------------------------ problem
     def partition(self, n_total, q_total):
@@ -248,7 +252,9 @@ class DistributedKNN:
         for the query slice this rank owns (device tensors)."""
         with torch.cuda.device(self.device):
             self.epoch += 1
-            self._gather_shard()
+            self.tracer.begin_step()
+            with self.tracer.phase("row_gather"):
+                self._gather_shard()
             if self.impl == "nccl_cublas":
                 from .baseline import run_baseline
                 return run_baseline(self)
@@ -290,25 +296,31 @@ class DistributedKNN:
             dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.col_group)
 
     def _run_peer_fused(self):
-        r0 = self.r * self.qs
-        self._range_stats()
-        K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
-        K.pack(self.q_slice, self.stats, self.q_stats,
-               out=(self.qh[r0:r0 + self.nq], self.qn[r0:r0 + self.nq], self.qe_[r0:r0 + self.nq]))
-        self.sym.signal(self.pack_table, self.epoch)          # "my packed slice is ready"
+        r0, tr = self.r * self.qs, self.tracer
+        with tr.phase("stats"):
+            self._range_stats()
+        with tr.phase("pack"):
+            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+            K.pack(self.q_slice, self.stats, self.q_stats,
+                   out=(self.qh[r0:r0 + self.nq], self.qn[r0:r0 + self.nq], self.qe_[r0:r0 + self.nq]))
+            self.sym.signal(self.pack_table, self.epoch)          # "my packed slice is ready"
         self.gather.epoch = self.epoch
-        K.dist_topk_gather(self.xh, self.xn, self.cand, self.gather)   # K4
+        with tr.phase("dist_topk+allgather"):
+            K.dist_topk_gather(self.xh, self.xn, self.cand, self.gather)   # K4
         self.nflag.zero_()
-        K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
-                         self.stats, self.id_base, self.kmax, self.flags, self.nflag, self.scatter)   # K5
+        with tr.phase("rerank+scatter"):
+            K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
+                             self.stats, self.id_base, self.kmax, self.flags, self.nflag, self.scatter)   # K5
         self.launch_count += 7   # pack x2, signal, dist_topk, rerank x3
         flagged = int(self.nflag.item())
         if flagged:
             self._repair_flagged()
         self.last_flagged = flagged
-        self.sym.signal(self.list_table, self.epoch)          # "my k-lists have landed everywhere"
-        self.sym.wait("list_flags", self.epoch, self.status)
-        label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2], self.k_all[r0:r0 + self.qs])
+        with tr.phase("wait_lists+finalize"):
+            self.sym.signal(self.list_table, self.epoch)          # "my k-lists have landed everywhere"
+            self.sym.wait("list_flags", self.epoch, self.status)
+            label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2],
+                                               self.k_all[r0:r0 + self.qs])
         self.launch_count += 3
         return label[:self.nq], checksum[:self.nq]
 
@@ -342,16 +354,22 @@ class DistributedKNN:
         return self.q_all, self.k_all
 
     def _run_local_or_nccl(self):
-        q_all, k_all = self._gather_queries_nccl()
-        self._range_stats()
+        tr = self.tracer
+        with tr.phase("query_gather"):
+            q_all, k_all = self._gather_queries_nccl()
+        with tr.phase("stats"):
+            self._range_stats()
         od, oi, ol, flags, nflag = self.lists
         if self.fused_ok:
-            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
-            K.pack(q_all, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
-            K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand)
+            with tr.phase("pack"):
+                K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+                K.pack(q_all, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
+            with tr.phase("dist_topk"):
+                K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand)
             nflag.zero_()
-            K.rerank(self.cand, q_all, self.x, self.labels, k_all, self.qn, self.qe_, self.stats, self.stats,
-                     self.id_base, self.kmax, out=self.lists)
+            with tr.phase("rerank"):
+                K.rerank(self.cand, q_all, self.x, self.labels, k_all, self.qn, self.qe_, self.stats, self.stats,
+                         self.id_base, self.kmax, out=self.lists)
             self.launch_count += 6   # pack x2, dist_topk, rerank x3
             flagged = int(nflag.item())
             if flagged:
@@ -362,7 +380,8 @@ class DistributedKNN:
         else:
             K.exact(q_all, self.x, self.labels, k_all, self.kmax, self.id_base, out=(od, oi, ol))
             self.launch_count += 3
-        return self._reduce_and_finalize_nccl(od, oi, ol)
+        with tr.phase("reduce+finalize"):
+            return self._reduce_and_finalize_nccl(od, oi, ol)
 
     def _reduce_and_finalize_nccl(self, od, oi, ol):
         """k-lists of every data shard -> owner of the query slice -> merge, vote, checksum."""

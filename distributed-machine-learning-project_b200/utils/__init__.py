@@ -1,2 +1,2 @@
-"""Utilities: timing / clocks, input format helpers."""
-from .timing import ClockSampler, time_steps  # noqa: F401
+"""Utilities: timing / clocks / tracing."""
+from .timing import ClockSampler, PhaseTracer, time_steps  # noqa: F401

@@ -102,3 +102,48 @@ def time_steps(step_fn, steps, warmup, barrier=None):
     if barrier:
         barrier()
     return start.elapsed_time(stop) / 1e3  # seconds
+
+
+class PhaseTracer:
+    """Per-phase device timing + NVTX ranges (the reference has one wall clock).
+
+    with tracer.phase("pack"): ...   NVTX range always; CUDA events only when enabled.
+    report() -> {phase: milliseconds} of the last step (synchronises)."""
+
+    def __init__(self, enabled=False):
+        self.enabled = enabled
+        self._events = []
+
+    class _Phase:
+        def __init__(self, tracer, name):
+            self.t, self.name = tracer, name
+
+        def __enter__(self):
+            torch.cuda.nvtx.range_push(self.name)
+            if self.t.enabled:
+                self.e0 = torch.cuda.Event(enable_timing=True)
+                self.e0.record()
+            return self
+
+        def __exit__(self, *exc):
+            if self.t.enabled:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                self.t._events.append((self.name, self.e0, e1))
+            torch.cuda.nvtx.range_pop()
+            return False
+
+    def phase(self, name):
+        return PhaseTracer._Phase(self, name)
+
+    def begin_step(self):
+        self._events = []
+
+    def report(self):
+        if not self.enabled:
+            return {}
+        torch.cuda.synchronize()
+        out = {}
+        for name, e0, e1 in self._events:
+            out[name] = out.get(name, 0.0) + e0.elapsed_time(e1)
+        return out

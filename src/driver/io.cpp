@@ -1,7 +1,9 @@
 // Text loader, synthetic generator and text writer.  See include/dmlp/io.h.
 #include "dmlp/io.h"
 
+#include <algorithm>
 #include <charconv>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <stdexcept>
@@ -196,31 +198,70 @@ void synth_problem(const SynthSpec &s, Problem *out) {
   for (auto &th : pool) th.join();
 }
 
+namespace {
+
+// " %.6f" for one value.  Values that are exact six-decimal numbers (everything the
+// generators produce) are printed with integer arithmetic; anything else goes through
+// snprintf so the text is always what printf("%.6f") would give.
+inline void append_fixed6(std::string &out, double v) {
+  const double scaled = v * 1e6;
+  if (std::fabs(scaled) < 9e15) {
+    long long i = std::llround(scaled);
+    if (static_cast<double>(i) / 1e6 == v) {
+      char buf[32];
+      int pos = 32;
+      const bool neg = i < 0;
+      unsigned long long u = neg ? static_cast<unsigned long long>(-i) : static_cast<unsigned long long>(i);
+      for (int d = 0; d < 6; ++d) { buf[--pos] = char('0' + u % 10); u /= 10; }
+      buf[--pos] = '.';
+      do { buf[--pos] = char('0' + u % 10); u /= 10; } while (u != 0);
+      if (neg && i != 0) buf[--pos] = '-';
+      buf[--pos] = ' ';
+      out.append(buf + pos, size_t(32 - pos));
+      return;
+    }
+  }
+  char tmp[64];
+  int m = std::snprintf(tmp, sizeof tmp, " %.6f", v);
+  out.append(tmp, size_t(m));
+}
+
+}  // namespace
+
 void write_problem_text(const Problem &p, std::FILE *f) {
   std::fprintf(f, "%lld %lld %d\n", (long long)p.num_data, (long long)p.num_queries, p.num_attrs);
-  std::string line;
-  char tmp[64];
-  for (int64_t i = 0; i < p.num_data; ++i) {
-    line.clear();
-    line += std::to_string(p.data_labels[i]);
-    const double *row = p.data_attrs + i * p.num_attrs;
-    for (int j = 0; j < p.num_attrs; ++j) {
-      int m = std::snprintf(tmp, sizeof tmp, " %.6f", row[j]);
-      line.append(tmp, size_t(m));
-    }
-    line += '\n';
-    std::fwrite(line.data(), 1, line.size(), f);
-  }
-  for (int64_t i = 0; i < p.num_queries; ++i) {
-    line.assign("Q ");
-    line += std::to_string(p.query_k[i]);
-    const double *row = p.query_attrs + i * p.num_attrs;
-    for (int j = 0; j < p.num_attrs; ++j) {
-      int m = std::snprintf(tmp, sizeof tmp, " %.6f", row[j]);
-      line.append(tmp, size_t(m));
-    }
-    line += '\n';
-    std::fwrite(line.data(), 1, line.size(), f);
+  int threads = int(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  if (threads > 32) threads = 32;
+  const int64_t total = p.num_data + p.num_queries;
+  // rows are formatted in parallel, block by block, and written in order
+  const int64_t rows_per_thread = std::max<int64_t>(1, (8 << 20) / std::max(1, p.num_attrs * 12));
+  const int64_t block = rows_per_thread * threads;
+  std::vector<std::string> bufs;
+  bufs.resize(static_cast<size_t>(threads));
+  for (int64_t b0 = 0; b0 < total; b0 += block) {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+      pool.emplace_back([&, t] {
+        std::string &line = bufs[size_t(t)];
+        line.clear();
+        const int64_t lo = b0 + t * rows_per_thread, hi = std::min(total, lo + rows_per_thread);
+        for (int64_t r = lo; r < hi; ++r) {
+          const double *row;
+          if (r < p.num_data) {
+            line += std::to_string(p.data_labels[r]);
+            row = p.data_attrs + r * p.num_attrs;
+          } else {
+            line += "Q ";
+            line += std::to_string(p.query_k[r - p.num_data]);
+            row = p.query_attrs + (r - p.num_data) * p.num_attrs;
+          }
+          for (int j = 0; j < p.num_attrs; ++j) append_fixed6(line, row[j]);
+          line += '\n';
+        }
+      });
+    for (auto &th : pool) th.join();
+    for (int t = 0; t < threads; ++t) std::fwrite(bufs[size_t(t)].data(), 1, bufs[size_t(t)].size(), f);
   }
 }
 

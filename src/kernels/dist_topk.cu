@@ -583,7 +583,8 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         }
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
-            if (plan.sync && cta_rank == 0 && it.group_rows > 1 && (kb % plan.sync) == 0) {
+            if (plan.sync && cta_rank == 0 && it.group_rows > 1 && kb == 0 &&
+                ((tile - it.tile_begin) % plan.sync) == 0) {
               // Re-align the pairs that sweep this chunk.  They read the same data tiles; L2
               // only holds a few k-blocks of every stream, so once the pairs drift apart each
               // one re-fetches the tile from HBM.  One counter per (group, chunk): arrive,
@@ -713,7 +714,10 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   if (p.pair) cluster = 2;
   p.prefetch = 0;
   p.rot = 0;
-  p.sync = p.k_blocks;   // re-align once per data tile; DMLP_TOPK_SYNC=<k-blocks between alignments>, 0 = off
+  // re-align the clusters of a chunk every `sync` data tiles: about once per 128 k-blocks of
+  // work (a tile of the headline shape); problems with short rows are epilogue-bound and
+  // their tiles are small, so they skip it.  DMLP_TOPK_SYNC=<tiles>, 0 = off
+  p.sync = p.k_blocks >= 16 ? (128 + p.k_blocks - 1) / p.k_blocks : 0;
   p.sync_cnt = nullptr;
   if (const char *e = getenv("DMLP_TOPK_SYNC")) p.sync = atoi(e);
   if (p.sync < 0) p.sync = 0;
@@ -729,25 +733,37 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   int nclusters = cluster == 1 ? num_sms : cluster == 2 ? num_sms / 2 : cluster == 4 ? (num_sms * 33) / 148
                                                                                       : (num_sms * 16) / 148;
   if (nclusters < 1) nclusters = 1;
-  // Split the clusters into `chunks` column ranges x `group_mc` cluster rows.  More
-  // cluster rows per chunk means more CTAs sweeping the same data tiles together
-  // (fewer HBM reads of the data shard: measured fastest at two chunks on the
-  // headline shape); the cap keeps the wave's query tiles within reach of L2.
-  // At least two chunks whenever possible: each contributes 32 keys per query,
-  // which is the head-room the certified filter needs above k.
-  long long tile_bytes = static_cast<long long>(BM) * a_pad * 2;
-  long long wave_bytes = tile_bytes * cluster * nclusters;
+  // Split the clusters into `chunks` column ranges x `group_mc` cluster rows; one wave
+  // processes one group (group_mc x chunks clusters), the row blocks are covered group
+  // by group.  Wanted: (1) every wave fills the chip -- with few row blocks that takes
+  // more chunks; (2) many cluster rows per chunk, because they sweep the same data tiles
+  // together and share them through L2 (measured fastest at two chunks on the headline
+  // shape); (3) the wave's query tiles within reach of L2; (4) at least two chunks when
+  // possible: each contributes 32 keys per query, the head-room the certified filter
+  // needs above k.
+  long long tile_bytes = static_cast<long long>(BM) * a_pad * 2 * cluster;
   long long budget = budget_mb << 20;
-  int c = static_cast<int>((wave_bytes + budget - 1) / budget);
-  if (c < 2) c = 2;
+  int c_min = p.n_tiles >= 2 ? 2 : 1;
+  int c_max = p.n_tiles < 32 ? (p.n_tiles > 0 ? p.n_tiles : 1) : 32;
+  if (c_max > nclusters) c_max = nclusters;
+  if (c_min > c_max) c_min = c_max;
+  // Few, long chunks are best (every (row, chunk) sweep starts with an open threshold and
+  // pays a warm-up of list compactions), so: the fewest chunks allowed, the most cluster
+  // rows per wave that L2 takes, row blocks spread evenly over the waves, and whatever
+  // clusters that leaves idle go to extra chunks.
+  int g_max = nclusters / c_min;
+  while (g_max > 1 && g_max * tile_bytes > budget) --g_max;
+  if (g_max < 1) g_max = 1;
+  const int groups = (p.mc_blocks + g_max - 1) / g_max;
+  int gmc = groups > 0 ? (p.mc_blocks + groups - 1) / groups : 1;
+  if (gmc < 1) gmc = 1;
+  int c = nclusters / gmc;
+  if (c < c_min) c = c_min;
+  if (c > c_max) c = c_max;
   if (const char *e = getenv("DMLP_TOPK_CHUNKS")) c = atoi(e) > 0 ? atoi(e) : c;
-  if (c > nclusters) c = nclusters;
-  int gmc = nclusters / c;
   if (const char *e = getenv("DMLP_TOPK_GMC")) gmc = atoi(e) > 0 ? atoi(e) : gmc;
-  if (gmc > p.mc_blocks) {  // few queries: give the spare clusters to more chunks
-    gmc = p.mc_blocks > 0 ? p.mc_blocks : 1;
-    if (!getenv("DMLP_TOPK_CHUNKS")) c = nclusters / gmc;
-  }
+  if (getenv("DMLP_TOPK_CHUNKS") && !getenv("DMLP_TOPK_GMC")) gmc = nclusters / c > 0 ? nclusters / c : 1;
+  if (gmc > p.mc_blocks) gmc = p.mc_blocks > 0 ? p.mc_blocks : 1;
   if (c > p.n_tiles) c = p.n_tiles > 0 ? p.n_tiles : 1;
   if (c < 1) c = 1;
   p.group_mc = gmc;
