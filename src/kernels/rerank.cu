@@ -13,12 +13,12 @@
 //           accumulation.  It proves completeness (every full chunk list must have
 //           cut off above T: dropped rows score >= the cut-off) or flags the query,
 //           and appends the survivors to a dense (query, row) pair list.
-//   exact   (one warp per query, one lane per survivor) recomputes the distance in
-//           fp64 with the reference's rounding sequence (__dsub_rn/__dmul_rn/
-//           __dadd_rn, one sequential chain per lane).  Rows are streamed in
-//           coalesced 256-byte segments through a per-warp cp.async ring; there
-//           is no block-wide barrier, so a dozen independent warps per SM keep
-//           both the memory system and the dependent fp64 chains busy.
+//   exact   (one warp per 32 pairs, one lane per pair) recomputes the distance in fp64
+//           with the reference's rounding sequence (__dsub_rn/__dmul_rn/__dadd_rn,
+//           one sequential chain per lane).  The pass is bound by fp64 instruction
+//           issue, so warps are packed full from the dense pair list; rows are
+//           streamed in coalesced 256-byte segments through a per-warp cp.async
+//           ring, with no block-wide barrier.
 //   emit    (one warp per query) checks every recomputed pair against its predicted
 //           error, ranks by (distance asc, id desc) and writes the k best as
 //           (distance, id, label) -- locally, or (K5) straight into the receive
@@ -179,11 +179,18 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankA
 // warp cooperatively streams 32-column chunks of the survivors' rows (and of the
 // query row) through a private two-stage cp.async ring, so every global access is
 // a coalesced 256-byte row segment and no block-wide barrier is needed.
+// Measured on B200: this pass is bound by fp64 instruction issue (about one warp-level
+// DADD/DMUL per 12 clocks per SM sub-partition), not by HBM, so what counts is full
+// warps.  A warp therefore takes 32 consecutive entries of the dense pair list, whatever
+// queries they belong to; lane r runs pair r's sequential chain.  The warp streams
+// 32-column chunks of the 32 data rows and of the lanes' query rows (duplicates are L2
+// hits) through a private two-stage cp.async ring: every global access is a coalesced
+// 256-byte row segment and there is no block-wide barrier.
 constexpr int XC = 32;             // columns per chunk
 constexpr int XSTR = XC + 2;       // row stride in doubles (16-byte aligned rows)
-constexpr int XROWS = 33;          // 32 survivors + the query row
+constexpr int XROWS = 64;          // 32 data rows + 32 query rows
 constexpr int XSTAGE = XROWS * XSTR;
-constexpr int X_WARPS = 4;
+constexpr int X_WARPS = 2;
 constexpr int X_SMEM = X_WARPS * 2 * XSTAGE * 8;
 
 template <int BYTES>
@@ -199,71 +206,70 @@ template <bool VEC2>
 __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_kernel(const RerankArgs a, const Scratch sc) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * X_WARPS + warp;
-  if (q >= a.q) return;
-  const int w = sc.q_w[q];
-  if (w == 0) return;
-  const int base = sc.q_base[q];
+  const unsigned count = *sc.counter;
+  const long long total = count < sc.capacity ? static_cast<long long>(count) : sc.capacity;
+  const long long p0 = (static_cast<long long>(blockIdx.x) * X_WARPS + warp) * 32;
+  if (p0 >= total) return;
+  const int cnt = (total - p0) < 32 ? static_cast<int>(total - p0) : 32;
   double *ring = reinterpret_cast<double *>(rr_smem) + static_cast<size_t>(warp) * 2 * XSTAGE;
-  const double *qrow = a.q_attrs + static_cast<long long>(q) * a.a;
+  // this lane's pair: element offsets of its data row and of its query row
+  const long long my_x = lane < cnt ? static_cast<long long>(sc.pair_id[p0 + lane]) * a.a : 0;
+  const long long my_q = lane < cnt ? static_cast<long long>(sc.pair_q[p0 + lane]) * a.a : 0;
   const int nchunks = (a.a + XC - 1) / XC;
 
-  for (int g0 = 0; g0 < w; g0 += 32) {
-    const int cnt = (w - g0) < 32 ? (w - g0) : 32;
-    const int my_id = lane < cnt ? sc.pair_id[base + g0 + lane] : 0;
-    // row r of the stage: r < cnt -> survivor r, r == cnt -> the query row
-    auto issue = [&](int chunk) {
-      if (chunk < nchunks) {
-        double *stage = ring + (chunk & 1) * XSTAGE;
-        const int col0 = chunk * XC;
-        if (VEC2) {
-          // 16 lanes x 16 B cover one 32-column row segment; two rows per instruction
-          const int half = lane >> 4, seg = lane & 15;
-          const int col = col0 + seg * 2;
-          const bool in = col + 2 <= a.a;
-          for (int r0 = 0; r0 <= cnt; r0 += 2) {
-            const int r = r0 + half;
-            const int rid = __shfl_sync(0xFFFFFFFFu, my_id, r < cnt ? r : 0);
-            if (r <= cnt) {
-              const double *src = (r == cnt ? qrow : a.x_attrs + static_cast<long long>(rid) * a.a) + (in ? col : 0);
-              cp_async_zfill<16>(stage + r * XSTR + seg * 2, src, in);
-            }
-          }
-        } else {
-          const int col = col0 + lane;
-          const bool in = col < a.a;
-          for (int r = 0; r <= cnt; ++r) {
-            const int rid = __shfl_sync(0xFFFFFFFFu, my_id, r < cnt ? r : 0);
-            const double *src = (r == cnt ? qrow : a.x_attrs + static_cast<long long>(rid) * a.a) + (in ? col : 0);
-            cp_async_zfill<8>(stage + r * XSTR + lane, src, in);
+  // stage rows 0..31: data rows of lanes 0..31; rows 32..63: their query rows
+  auto issue = [&](int chunk) {
+    if (chunk < nchunks) {
+      double *stage = ring + (chunk & 1) * XSTAGE;
+      const int col0 = chunk * XC;
+      if (VEC2) {
+        // 16 lanes x 16 B cover one 32-column row segment; two rows per instruction
+        const int half = lane >> 4, seg = lane & 15;
+        const int col = col0 + seg * 2;
+        const bool in = col + 2 <= a.a;
+        for (int r0 = 0; r0 < cnt; r0 += 2) {
+          const int r = r0 + half;
+          const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r < cnt ? r : 0);
+          const long long qo = __shfl_sync(0xFFFFFFFFu, my_q, r < cnt ? r : 0);
+          if (r < cnt) {
+            cp_async_zfill<16>(stage + r * XSTR + seg * 2, a.x_attrs + xo + (in ? col : 0), in);
+            cp_async_zfill<16>(stage + (32 + r) * XSTR + seg * 2, a.q_attrs + qo + (in ? col : 0), in);
           }
         }
-      }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-
-    double acc = 0.0;
-    issue(0);
-    for (int chunk = 0; chunk < nchunks; ++chunk) {
-      issue(chunk + 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-      __syncwarp();
-      if (lane < cnt) {
-        const double *stage = ring + (chunk & 1) * XSTAGE;
-        const double *qs = stage + cnt * XSTR;
-        const double *xs = stage + lane * XSTR;
-#pragma unroll 8
-        for (int i = 0; i < XC; ++i) {
-          const double d = __dsub_rn(qs[i], xs[i]);
-          acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
+      } else {
+        const int col = col0 + lane;
+        const bool in = col < a.a;
+        for (int r = 0; r < cnt; ++r) {
+          const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r);
+          const long long qo = __shfl_sync(0xFFFFFFFFu, my_q, r);
+          cp_async_zfill<8>(stage + r * XSTR + lane, a.x_attrs + xo + (in ? col : 0), in);
+          cp_async_zfill<8>(stage + (32 + r) * XSTR + lane, a.q_attrs + qo + (in ? col : 0), in);
         }
       }
-      __syncwarp();
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    if (lane < cnt) sc.pair_dist[base + g0 + lane] = acc;
+    asm volatile("cp.async.commit_group;" ::: "memory");  // always commit: keeps the group count uniform
+  };
+
+  double acc = 0.0;
+  issue(0);
+  for (int chunk = 0; chunk < nchunks; ++chunk) {
+    issue(chunk + 1);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    if (lane < cnt) {
+      const double *stage = ring + (chunk & 1) * XSTAGE;
+      const double *xs = stage + lane * XSTR;
+      const double *qs = stage + (32 + lane) * XSTR;
+#pragma unroll 8
+      for (int i = 0; i < XC; ++i) {
+        const double d = __dsub_rn(qs[i], xs[i]);
+        acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
+      }
+    }
     __syncwarp();
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (lane < cnt) sc.pair_dist[p0 + lane] = acc;
 }
 
 // -------------------------------------------------------------------- emit
@@ -358,7 +364,8 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
   DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
   rerank_select_kernel<<<args.q, RR_THREADS, smem, s>>>(args, sc, lpad);
   DMLP_CUDA_OK(cudaGetLastError());
-  const unsigned blocks = static_cast<unsigned>((args.q + X_WARPS - 1) / X_WARPS);
+  // one warp per 32 pairs; sized for the worst case, surplus warps exit at once
+  const unsigned blocks = static_cast<unsigned>((sc.capacity + 32 * X_WARPS - 1) / (32 * X_WARPS));
   const bool vec2 = (args.a % 2 == 0) && (reinterpret_cast<uintptr_t>(args.q_attrs) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(args.x_attrs) % 16 == 0);
   if (vec2) {
