@@ -3,7 +3,7 @@
 ``KNNClassifier`` runs the whole reference job on one B200: host (pinned)
 arrays -> async H2D -> pack -> tcgen05 filter GEMM with fused top-k -> exact
 fp64 re-rank -> vote + checksum -> D2H.  Queries the filter cannot certify, and
-problems outside the fused path's envelope (k > 24, tiny shapes), run on the
+problems outside the fused path's envelope (k > 96, tiny shapes), run on the
 direct fp64 kernel instead; the answer is bit-identical either way.
 """
 from dataclasses import dataclass

@@ -11,8 +11,8 @@ from .._native import knn_lib
 
 STATS_BYTES = 32
 KP = 32          # keys kept per (query, chunk) by the fused epilogue
-FUSED_MAX_K = 24  # largest k sent to the fused path: each chunk list keeps 32 keys and the
-#                   certified survivor set needs head-room above k
+FUSED_MAX_K = 96  # largest k sent to the fused path: each chunk list keeps 32 keys, so larger k is
+#                   given more chunks (one per 8 of k); the re-rank recomputes up to 256 survivors
 
 _ready = False
 _vp, _i, _i64, _u64, _sz, _dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_size_t, C.c_double
@@ -27,11 +27,11 @@ def _lib():
         lib.dmlp_stats_reset.argtypes = [_vp, _vp]
         lib.dmlp_stats_update.argtypes = [_vp, _i64, _vp, _vp]
         lib.dmlp_pack.argtypes = [_vp, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]
-        lib.dmlp_topk_plan.argtypes = [_i, _i, _i, _i, C.POINTER(_i * 8)]
-        lib.dmlp_dist_topk.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]
+        lib.dmlp_topk_plan.argtypes = [_i, _i, _i, _i, _i, C.POINTER(_i * 8)]
+        lib.dmlp_dist_topk.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp]
         lib.dmlp_rerank.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
                                     _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]
-        lib.dmlp_rerank_workspace_bytes.argtypes = [_i]
+        lib.dmlp_rerank_workspace_bytes.argtypes = [_i, _i]
         lib.dmlp_rerank_workspace_bytes.restype = _sz
         lib.dmlp_exact_workspace_bytes.argtypes = [_i, _i]
         lib.dmlp_exact_workspace_bytes.restype = _sz
@@ -40,7 +40,7 @@ def _lib():
         lib.dmlp_synth_attrs.argtypes = [_vp, _i64, _i, _i64, _dbl, _dbl, _u64, _u64, _vp]
         lib.dmlp_synth_labels.argtypes = [_vp, _i64, _i64, _i, _u64, _vp]
         lib.dmlp_synth_k.argtypes = [_vp, _i64, _i64, _i, _i, _u64, _vp]
-        lib.dmlp_knn_local_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.dmlp_knn_local_workspace_bytes.argtypes = [_i, _i, _i, _i, _i]
         lib.dmlp_knn_local_workspace_bytes.restype = _sz
         lib.dmlp_knn_local.argtypes = [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _vp, _vp, _vp, _vp,
                                        _vp, _vp]
@@ -129,32 +129,34 @@ def pack(src, rng, maxima=None, out=None):
     return h, n2, en
 
 
-def topk_plan(q, n, a_pad, sms=None):
+def topk_plan(q, n, a_pad, sms=None, kmax=0):
     arr = (_i * 8)()
-    _check(_lib().dmlp_topk_plan(q, n, a_pad, sms or sm_count(), C.byref(arr)))
+    _check(_lib().dmlp_topk_plan(q, n, a_pad, sms or sm_count(), kmax, C.byref(arr)))
     keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp", "cluster"]
     return dict(zip(keys, list(arr)[:8]))
 
 
-def dist_topk(qh, xh, xnorm2, cand=None, sms=None):
+def dist_topk(qh, xh, xnorm2, cand=None, sms=None, kmax=0):
     """Filter GEMM + fused top-k.  Returns uint64-as-int64 keys [q, chunks, kp]."""
     q, a_pad = qh.shape
     n = xh.shape[0]
-    plan = topk_plan(q, n, a_pad, sms)
+    plan = topk_plan(q, n, a_pad, sms, kmax)
     if cand is None:
         cand = torch.empty((q, plan["chunks"], plan["kp"]), dtype=torch.int64, device=qh.device)
-    _check(_lib().dmlp_dist_topk(_p(qh), _p(xh), _p(xnorm2), q, n, a_pad, sms or sm_count(), _p(cand), _stream()))
+    _check(_lib().dmlp_dist_topk(_p(qh), _p(xh), _p(xnorm2), q, n, a_pad, sms or sm_count(), kmax, _p(cand),
+                                 _stream()))
     return cand
 
 
 _rerank_ws = {}
 
 
-def rerank_workspace(q, device):
+def rerank_workspace(q, kmax, device):
     """Cached scratch (survivor pair list) for the re-rank kernels."""
-    key = (str(device), q)
+    key = (str(device), q, kmax)
     if key not in _rerank_ws:
-        _rerank_ws[key] = torch.empty(int(_lib().dmlp_rerank_workspace_bytes(q)), dtype=torch.uint8, device=device)
+        _rerank_ws[key] = torch.empty(int(_lib().dmlp_rerank_workspace_bytes(q, kmax)), dtype=torch.uint8,
+                                      device=device)
     return _rerank_ws[key]
 
 
@@ -169,7 +171,7 @@ def rerank(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, 
                torch.empty(q, dtype=torch.int32, device=dev),
                torch.zeros(1, dtype=torch.int32, device=dev))
     od, oi, ol, flags, nflag = out
-    ws = rerank_workspace(q, dev)
+    ws = rerank_workspace(q, kmax, dev)
     _check(_lib().dmlp_rerank(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
                               _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax,
                               _p(od), _p(oi), _p(ol), _p(flags), _p(nflag), _p(ws), ws.numel(), _stream()))
@@ -255,12 +257,13 @@ def peer_gather(args):
     _check(lib.dmlp_peer_gather(C.byref(args), _stream()))
 
 
-def dist_topk_gather(xh, xnorm2, cand, gather):
+def dist_topk_gather(xh, xnorm2, cand, gather, kmax=0):
     """K4: filter GEMM whose query operand is all-gathered from the peers inside the kernel."""
     lib = _lib()
-    lib.dmlp_dist_topk_gather.argtypes = [_vp, _vp, _i, _i, _i, _vp, C.POINTER(GatherArgs), _vp]
+    lib.dmlp_dist_topk_gather.argtypes = [_vp, _vp, _i, _i, _i, _i, _vp, C.POINTER(GatherArgs), _vp]
     n, a_pad = xh.shape
-    _check(lib.dmlp_dist_topk_gather(_p(xh), _p(xnorm2), n, a_pad, sm_count(), _p(cand), C.byref(gather), _stream()))
+    _check(lib.dmlp_dist_topk_gather(_p(xh), _p(xnorm2), n, a_pad, sm_count(), kmax, _p(cand), C.byref(gather),
+                                     _stream()))
     return cand
 
 
@@ -272,14 +275,14 @@ def rerank_scatter(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_
                                         _vp, _vp, C.POINTER(ScatterArgs), _vp, _sz, _vp]
     q, chunks, kp = cand.shape
     n, a = x_attrs.shape
-    ws = rerank_workspace(q, cand.device)
+    ws = rerank_workspace(q, kmax, cand.device)
     _check(lib.dmlp_rerank_scatter(_p(cand), chunks, kp, _p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(q_norm2),
                                    _p(q_errn), _p(rng), _p(x_maxima), q, n, a, pad64(a), id_base, kmax, _p(flags),
                                    _p(nflag), C.byref(scatter), _p(ws), ws.numel(), _stream()))
 
 
-def knn_local_workspace_bytes(q, n, a):
-    return int(_lib().dmlp_knn_local_workspace_bytes(q, n, a, sm_count()))
+def knn_local_workspace_bytes(q, n, a, kmax=0):
+    return int(_lib().dmlp_knn_local_workspace_bytes(q, n, a, sm_count(), kmax))
 
 
 def knn_local(q_attrs, k, x_attrs, x_labels, kmax, id_base=0, rng=None, workspace=None, out=None):
@@ -288,7 +291,7 @@ def knn_local(q_attrs, k, x_attrs, x_labels, kmax, id_base=0, rng=None, workspac
     n = x_attrs.shape[0]
     dev = q_attrs.device
     if workspace is None:
-        workspace = torch.empty(knn_local_workspace_bytes(q, n, a), dtype=torch.uint8, device=dev)
+        workspace = torch.empty(knn_local_workspace_bytes(q, n, a, kmax), dtype=torch.uint8, device=dev)
     if out is None:
         out = (torch.empty((q, kmax), dtype=torch.float64, device=dev),
                torch.empty((q, kmax), dtype=torch.int32, device=dev),

@@ -12,7 +12,7 @@ import torch
 from ..ops import cuda as K
 
 _QB = 4096      # query rows per cuBLAS call (score block = _QB x n fp32)
-_HALVES = 2     # candidate lists per query (column halves), 32 keys each
+_HALVES = 2     # candidate lists per query (column ranges), 32 keys each, at least
 
 
 def _keys_from_topk(vals, idx, base):
@@ -31,7 +31,8 @@ def run_baseline(eng):
     eng.launch_count += 2
     n = eng.x.shape[0]
     qp = eng.qp
-    halves = _HALVES if n >= 2 * 32 else 1
+    halves = max(_HALVES, -(-eng.kmax // 8))      # same rule as the fused planner: one list per 8 of k
+    halves = max(1, min(halves, n // 32)) if n >= 64 else 1
     if not hasattr(eng, "_bl_cand") or eng._bl_cand.shape[1] != halves:
         eng._bl_cand = torch.empty((qp, halves, 32), dtype=torch.int64, device=eng.device)
     cand = eng._bl_cand

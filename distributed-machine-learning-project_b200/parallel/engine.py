@@ -183,7 +183,7 @@ class DistributedKNN:
         self.qh = torch.zeros((self.qp, self.a_pad), dtype=torch.float16, device=dev)
         self.qn = torch.zeros(self.qp, dtype=torch.float32, device=dev)
         self.qe_ = torch.zeros(self.qp, dtype=torch.float32, device=dev)
-        plan = K.topk_plan(self.qp, max(n, 1), self.a_pad)
+        plan = K.topk_plan(self.qp, max(n, 1), self.a_pad, kmax=km)
         self.cand = torch.empty((self.qp, plan["chunks"], plan["kp"]), dtype=torch.int64, device=dev)
         self.lists = (torch.empty((self.qp, km), dtype=torch.float64, device=dev),
                       torch.empty((self.qp, km), dtype=torch.int32, device=dev),
@@ -226,7 +226,7 @@ class DistributedKNN:
         self.pack_table = sym.pointer_table("pack_flags")
         self.list_table = sym.pointer_table("list_flags")
         self.rb_count = torch.zeros(self.qp // 128, dtype=torch.int32, device=dev)
-        plan = K.topk_plan(self.qp, max(self.shard_rows, 1), self.a_pad)
+        plan = K.topk_plan(self.qp, max(self.shard_rows, 1), self.a_pad, kmax=km)
         self.cand = torch.empty((self.qp, plan["chunks"], plan["kp"]), dtype=torch.int64, device=dev)
         self.flags = torch.empty(self.qp, dtype=torch.int32, device=dev)
         self.nflag = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -306,7 +306,7 @@ class DistributedKNN:
             self.sym.signal(self.pack_table, self.epoch)          # "my packed slice is ready"
         self.gather.epoch = self.epoch
         with tr.phase("dist_topk+allgather"):
-            K.dist_topk_gather(self.xh, self.xn, self.cand, self.gather)   # K4
+            K.dist_topk_gather(self.xh, self.xn, self.cand, self.gather, kmax=self.kmax)   # K4
         self.nflag.zero_()
         with tr.phase("rerank+scatter"):
             K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
@@ -365,7 +365,7 @@ class DistributedKNN:
                 K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
                 K.pack(q_all, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
             with tr.phase("dist_topk"):
-                K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand)
+                K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand, kmax=self.kmax)
             nflag.zero_()
             with tr.phase("rerank"):
                 K.rerank(self.cand, q_all, self.x, self.labels, k_all, self.qn, self.qe_, self.stats, self.stats,
@@ -539,11 +539,11 @@ class DistributedKNN:
             K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(qh, qn, qe))
             key = e - b
             if key not in self._cand_by_rows:
-                plan = K.topk_plan(key, max(self.shard_rows, 1), self.a_pad)
+                plan = K.topk_plan(key, max(self.shard_rows, 1), self.a_pad, kmax=self.kmax)
                 self._cand_by_rows[key] = torch.empty((key, plan["chunks"], plan["kp"]), dtype=torch.int64,
                                                       device=self.device)
             cand = self._cand_by_rows[key]
-            K.dist_topk(qh, self.xh, self.xn, cand=cand)
+            K.dist_topk(qh, self.xh, self.xn, cand=cand, kmax=self.kmax)
             K.rerank(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], qn, qe, self.stats, self.stats,
                      self.id_base, self.kmax, out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
             self.launch_count += 5 + (1 if dec else 0)

@@ -52,18 +52,20 @@ int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *strea
 
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
  * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
- * candidate buffer holds q * chunks * kp 64-bit keys. */
-int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]);
+ * candidate buffer holds q * chunks * kp 64-bit keys.  kmax = the largest k any query
+ * asks for (0 = unknown): every chunk keeps at most 32 candidates per query, so larger k
+ * is given more chunks.  The fused path is meant for kmax <= 96. */
+int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[8]);
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
-                   int num_sms, uint64_t *cand, void *stream);
+                   int num_sms, int kmax, uint64_t *cand, void *stream);
 
 /* ---- K2 exact_rerank (reference: engine.cpp:12-18 semantics) ------------------
  * Writes, per query, kmax slots of (dist, id, label): the exact local top-k in
  * (distance asc, id desc) order, padded with (1e18, -1, -1).  flags[q] != 0 marks
  * a query the filter could not certify; *num_flagged counts them.  Scratch (the
- * survivor pair list) comes from the caller: dmlp_rerank_workspace_bytes(q) bytes,
+ * survivor pair list) comes from the caller: dmlp_rerank_workspace_bytes(q, kmax) bytes,
  * 256-byte aligned. */
-size_t dmlp_rerank_workspace_bytes(int q);
+size_t dmlp_rerank_workspace_bytes(int q, int kmax);
 int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                 const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
                 const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax,
@@ -100,7 +102,7 @@ int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k,
  * `range` may be NULL (the range is then computed from these two arrays) or a
  * stats block already merged across ranks.  Scratch layout is private; size it
  * with dmlp_knn_local_workspace_bytes. */
-size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms);
+size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms, int kmax);
 int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels,
                    int n, int a, int id_base, int kmax, const void *range, void *workspace,
                    size_t workspace_bytes, double *out_dist, int *out_id, int *out_label, int *flags,
@@ -161,8 +163,8 @@ typedef struct dmlp_gather_args {
   int *status;            /* device int: set non-zero if a peer never showed up */
   double timeout_seconds;
 } dmlp_gather_args;
-int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, uint64_t *cand,
-                          const dmlp_gather_args *g, void *stream);
+int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, int kmax,
+                          uint64_t *cand, const dmlp_gather_args *g, void *stream);
 
 /* K5, GEMM/top-k -> reduce-scatter of k-lists (reference: MPI_Gather of k-lists to
  * row 0 + re-select, engine.cpp:283-308): dmlp_rerank with its outputs redirected

@@ -46,7 +46,7 @@ for rep in range(args.reps + 2):
     timed("stats", lambda: (K.stats_update(x, st), K.stats_update(qq, st)))
     xh, xn, xe = timed("pack_x", lambda: K.pack(x, st, st))
     qh, qn, qe = timed("pack_q", lambda: K.pack(qq, st, qst))
-    cand = timed("dist_topk", lambda: K.dist_topk(qh, xh, xn))
+    cand = timed("dist_topk", lambda: K.dist_topk(qh, xh, xn, kmax=args.kmax))
     od, oi, ol, flags, nflag = timed("rerank", lambda: K.rerank(cand, qq, x, lab, k, qn, qe, st, st, 0, args.kmax))
     timed("finalize", lambda: K.finalize(od[None], oi[None], ol[None], k))
 import ctypes
@@ -59,7 +59,7 @@ K._lib().dmlp_debug_rerank_w(None)
 wf = wbuf.float()
 wstats = {"mean": wf.mean().item(), "p50": wf.median().item(), "p99": wf.kthvalue(int(0.99 * Q)).values.item(),
           "max": wf.max().item(), "k_mean": k.float().mean().item()}
-plan = K.topk_plan(Q, N, xh.shape[1])
+plan = K.topk_plan(Q, N, xh.shape[1], kmax=args.kmax)
 med = {n: statistics.median(v) for n, v in times.items()}
 flops = 2.0 * Q * N * K.pad64(A)
 print(json.dumps({"shape": [Q, N, A], "plan": plan, "ms": med, "total_ms": sum(med.values()),

@@ -690,7 +690,7 @@ int make_fp16_tile_map(CUtensorMap *map, const __half *base, long long rows, int
   return 0;
 }
 
-TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
+TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax) {
   TopkPlan p;
   p.q_rows = q_rows;
   p.n = n;
@@ -743,7 +743,10 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms) {
   // needs above k.
   long long tile_bytes = static_cast<long long>(BM) * a_pad * 2 * cluster;
   long long budget = budget_mb << 20;
-  int c_min = p.n_tiles >= 2 ? 2 : 1;
+  // the certified survivor set is about 1.6 k per query, spread over the chunks, and a
+  // chunk can contribute at most 32: one chunk per 8 of k keeps every list far from full
+  int c_min = 2 > (kmax + 7) / 8 ? 2 : (kmax + 7) / 8;
+  if (c_min > p.n_tiles) c_min = p.n_tiles > 0 ? p.n_tiles : 1;
   int c_max = p.n_tiles < 32 ? (p.n_tiles > 0 ? p.n_tiles : 1) : 32;
   if (c_max > nclusters) c_max = nclusters;
   if (c_min > c_max) c_min = c_max;

@@ -65,7 +65,9 @@ struct TopkPlan {
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
   int hint_q, hint_x;  ///< L2 eviction hints for query / data tiles: 0 normal, 1 first, 2 last
 };
-TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms);
+/// `kmax`: largest k any query asks for (0 = unknown); larger k gets more chunks, because
+/// every chunk contributes at most 32 candidates per query.
+TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax = 0);
 
 // pack.cu
 int launch_stats_reset(PackStats *st, cudaStream_t s);
@@ -132,7 +134,7 @@ struct RerankArgs {
   void *workspace = nullptr;       // >= rerank_workspace_bytes(q), 256-byte aligned
   size_t workspace_bytes = 0;
 };
-size_t rerank_workspace_bytes(int q);
+size_t rerank_workspace_bytes(int q, int kmax);
 int launch_rerank(const RerankArgs &args, cudaStream_t s);
 void set_rerank_debug_w(int *w_out);  // diagnostics: next launches record survivors per query here
 

@@ -35,8 +35,13 @@ namespace k {
 namespace {
 
 constexpr int RR_THREADS = 128;
-constexpr int WMAX = 64;        // survivors recomputed per query, at most
-constexpr int PAIRS_PER_Q = 32; // pair-list capacity per query on average
+constexpr int WMAX = 256;       // survivors recomputed per query, at most
+
+// pair-list capacity per query on average: survivors are about 1.6 k
+inline long long pairs_per_query(int kmax) {
+  long long v = 2LL * kmax + 16;
+  return v < 32 ? 32 : (v > WMAX ? WMAX : v);
+}
 
 enum : int { kFlagCutoff = 1, kFlagOverflow = 2, kFlagModel = 4 };
 
@@ -56,10 +61,10 @@ struct Scratch {
 
 size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 
-Scratch carve(void *ws, int q) {
+Scratch carve(void *ws, int q, int kmax) {
   Scratch s;
   unsigned char *p = static_cast<unsigned char *>(ws);
-  const long long cap = static_cast<long long>(q) * PAIRS_PER_Q + WMAX;
+  const long long cap = static_cast<long long>(q) * pairs_per_query(kmax) + WMAX;
   s.capacity = cap;
   s.counter = reinterpret_cast<unsigned *>(p); p += 256;
   s.q_base = reinterpret_cast<int *>(p); p += up256(sizeof(int) * q);
@@ -339,9 +344,9 @@ int *g_debug_w = nullptr;
 
 void set_rerank_debug_w(int *w_out) { g_debug_w = w_out; }
 
-size_t rerank_workspace_bytes(int q) {
+size_t rerank_workspace_bytes(int q, int kmax) {
   if (q < 1) q = 1;
-  const size_t cap = static_cast<size_t>(q) * PAIRS_PER_Q + WMAX;
+  const size_t cap = static_cast<size_t>(q) * pairs_per_query(kmax) + WMAX;
   return 256 + 2 * up256(sizeof(int) * q) + up256(sizeof(QMeta) * q) + 2 * up256(sizeof(int) * cap) +
          up256(sizeof(float) * cap) + up256(sizeof(double) * cap);
 }
@@ -353,10 +358,10 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
   const int L = args.chunks * args.kp;
   DMLP_REQUIRE(L > 0 && L <= 8192, "rerank: chunks * kp must be in (0, 8192]");
   DMLP_REQUIRE(args.kmax > 0, "rerank: kmax must be positive");
-  DMLP_REQUIRE(args.workspace != nullptr && args.workspace_bytes >= rerank_workspace_bytes(args.q),
-               "rerank: workspace missing or smaller than rerank_workspace_bytes(q)");
+  DMLP_REQUIRE(args.workspace != nullptr && args.workspace_bytes >= rerank_workspace_bytes(args.q, args.kmax),
+               "rerank: workspace missing or smaller than rerank_workspace_bytes(q, kmax)");
   DMLP_REQUIRE((reinterpret_cast<uintptr_t>(args.workspace) & 255) == 0, "rerank: workspace must be 256-byte aligned");
-  const Scratch sc = carve(args.workspace, args.q);
+  const Scratch sc = carve(args.workspace, args.q, args.kmax);
   DMLP_CUDA_OK(cudaMemsetAsync(sc.counter, 0, sizeof(unsigned), s));
   int lpad = 64;
   while (lpad < L) lpad <<= 1;

@@ -75,18 +75,18 @@ int dmlp_stats_set(void *stats, double lo, double hi, void *stream) {
   return 0;
 }
 
-int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int plan_out[8]) {
-  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[8]) {
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
   plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.chunks;
   plan_out[4] = p.k_blocks; plan_out[5] = p.grid; plan_out[6] = p.kp; plan_out[7] = p.cluster;
   return 0;
 }
 
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
-                   int num_sms, uint64_t *cand, void *stream) {
+                   int num_sms, int kmax, uint64_t *cand, void *stream) {
   if (num_sms <= 0)
     if (int rc = current_sm_count(&num_sms)) return rc;
-  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
   return launch_dist_topk(static_cast<const __half *>(q_fp16), static_cast<const __half *>(x_fp16), x_norm2, p,
                           reinterpret_cast<unsigned long long *>(cand), nullptr, st(stream));
 }
@@ -110,14 +110,14 @@ int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs,
   return launch_rerank(r, st(stream));
 }
 
-int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, uint64_t *cand,
-                          const dmlp_gather_args *g, void *stream) {
+int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, int kmax,
+                          uint64_t *cand, const dmlp_gather_args *g, void *stream) {
   DMLP_REQUIRE(g != nullptr && g->world >= 1 && g->world <= kMaxPeers, "dist_topk_gather: world must be in [1, 8]");
   DMLP_REQUIRE(g->slice_rows > 0 && g->slice_rows % 256 == 0, "dist_topk_gather: slice_rows must be a multiple of 256");
   if (num_sms <= 0)
     if (int rc = current_sm_count(&num_sms)) return rc;
   const int q = g->world * g->slice_rows;
-  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms);
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
   DMLP_REQUIRE(p.pair == 1, "dist_topk_gather: needs the CTA-pair kernel");
   // start the sweep at this rank's own slice: its rows are ready without any transfer,
   // and every GPU pulls from a different peer first
@@ -160,7 +160,7 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
 
 void dmlp_debug_rerank_w(int *w_out) { set_rerank_debug_w(w_out); }
 
-size_t dmlp_rerank_workspace_bytes(int q) { return rerank_workspace_bytes(q); }
+size_t dmlp_rerank_workspace_bytes(int q, int kmax) { return rerank_workspace_bytes(q, kmax); }
 
 size_t dmlp_exact_workspace_bytes(int n, int batch) { return exact_workspace_bytes(n, batch); }
 
@@ -203,10 +203,10 @@ struct LocalLayout {
   size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, rerank, rerank_bytes, total;
   int a_pad, chunks;
 };
-LocalLayout local_layout(int q, int n, int a, int num_sms) {
+LocalLayout local_layout(int q, int n, int a, int num_sms, int kmax) {
   LocalLayout L;
   L.a_pad = pad64(a > 0 ? a : 1);
-  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, num_sms);
+  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, num_sms, kmax);
   L.chunks = p.chunks;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
@@ -219,16 +219,16 @@ LocalLayout local_layout(int q, int n, int a, int num_sms) {
   L.qn = take(size_t(q) * 4);
   L.qe = take(size_t(q) * 4);
   L.cand = take(size_t(q) * p.chunks * 32 * 8);
-  L.rerank_bytes = rerank_workspace_bytes(q);
+  L.rerank_bytes = rerank_workspace_bytes(q, kmax);
   L.rerank = take(L.rerank_bytes);
   L.total = off;
   return L;
 }
 }  // namespace
 
-size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms) {
+size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms, int kmax) {
   if (num_sms <= 0) num_sms = 148;
-  return local_layout(q, n, a, num_sms).total;
+  return local_layout(q, n, a, num_sms, kmax).total;
 }
 
 int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels, int n,
@@ -236,7 +236,7 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
                    double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *stream) {
   int sms = 0;
   if (int rc = current_sm_count(&sms)) return rc;
-  LocalLayout L = local_layout(q, n, a, sms);
+  LocalLayout L = local_layout(q, n, a, sms, kmax);
   DMLP_REQUIRE(workspace_bytes >= L.total, "knn_local: workspace too small");
   DMLP_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "knn_local: workspace must be 256-byte aligned");
   unsigned char *w = static_cast<unsigned char *>(workspace);
@@ -258,7 +258,7 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   // the row maxima live in the stats blocks (range fields of q_stats stay unused)
   if (int rc = launch_pack(x_attrs, n, a, L.a_pad, rng, xh, xn, xe, stats, s)) return rc;
   if (int rc = launch_pack(q_attrs, q, a, L.a_pad, rng, qh, qn, qe, q_stats, s)) return rc;
-  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms);
+  TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms, kmax);
   if (int rc = launch_dist_topk(qh, xh, xn, p, cand, nullptr, s)) return rc;
   if (num_flagged) DMLP_CUDA_OK(cudaMemsetAsync(num_flagged, 0, sizeof(int), s));
   RerankArgs r;

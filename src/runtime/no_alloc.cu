@@ -50,7 +50,7 @@ extern "C" int dmlp_knn_local_static(const double *q_attrs, const int *k, int q,
   DMLP_CUDA_OK(cudaGetDevice(&dev));
   DMLP_REQUIRE(dev >= 0 && dev < kMaxDevices, "knn_local_static: device index beyond the per-device address table");
   DMLP_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const size_t need = dmlp_knn_local_workspace_bytes(q, n, a, sms);
+  const size_t need = dmlp_knn_local_workspace_bytes(q, n, a, sms, kmax);
   if (need > static_cast<size_t>(DMLP_STATIC_SCRATCH_BYTES)) {
     dmlp::k::set_error("knn_local_static: this problem needs " + std::to_string(need) +
                        " bytes of scratch but the built-in scratch holds " +

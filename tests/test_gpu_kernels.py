@@ -96,7 +96,8 @@ def test_dist_topk_against_torch(K, q, n, a):
 
 @pytest.mark.parametrize("n,q,a,kmin,kmax,lo,hi", [
     (5000, 300, 64, 1, 16, -100.0, 100.0), (2049, 257, 33, 3, 24, 0.0, 10.0), (900, 129, 7, 1, 5, -1.0, 1.0),
-    (40000, 256, 128, 16, 16, -100.0, 100.0), (300, 130, 256, 1, 8, 0.0, 1000.0)])
+    (40000, 256, 128, 16, 16, -100.0, 100.0), (300, 130, 256, 1, 8, 0.0, 1000.0),
+    (30000, 300, 64, 30, 60, -100.0, 100.0), (8000, 150, 32, 96, 96, 0.0, 10.0)])
 def test_knn_local_matches_oracle(K, n, q, a, kmin, kmax, lo, hi):
     data, labels, queries, k = cpu.synth(n, q, a, lo, hi, kmin, kmax, 7, seed=13)
     want_label, want_sum, want_ids, want_dist, off = cpu.knn(data, labels, queries, k)

@@ -84,9 +84,12 @@ def test_distributed_matches_oracle(tmp_path, repo_root, impl, shape, kind):
         assert '"peer_fused": true' in out
 
 
-def test_distributed_large_k_takes_exact_path(tmp_path, repo_root):
+def test_distributed_large_k(tmp_path, repo_root):
+    """k up to 60 stays on the fused path (more chunks); k = 120 takes the exact kernels."""
     world = _world()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
-    out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 30, 60, f"{world}x1")
-    assert out.count('"checked"') == world
+    out = _run(tmp_path, repo_root, world, "fused", 20000, 300, 64, 30, 60, f"{world}x1")
+    assert out.count('"checked"') == world and '"peer_fused": true' in out
+    out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 100, 120, f"{world}x1")
+    assert out.count('"checked"') == world and '"peer_fused": false' in out

@@ -28,7 +28,7 @@ def _abi():
     from dmlp_b200._native import knn_lib
     lib = knn_lib()
     lib.dmlp_last_error.restype = C.c_char_p
-    lib.dmlp_knn_local_workspace_bytes.argtypes = [_i, _i, _i, _i]
+    lib.dmlp_knn_local_workspace_bytes.argtypes = [_i, _i, _i, _i, _i]
     lib.dmlp_knn_local_workspace_bytes.restype = _sz
     lib.dmlp_knn_local.argtypes = [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp]
     lib.dmlp_knn_local.restype = _i
@@ -57,7 +57,7 @@ def _problem(n, q, a, kmax, seed):
 def _run_both(lib, n, q, a, kmax, seed, id_base):
     x, labels, qq, k = _problem(n, q, a, kmax, seed)
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    need = lib.dmlp_knn_local_workspace_bytes(q, n, a, sms)
+    need = lib.dmlp_knn_local_workspace_bytes(q, n, a, sms, kmax)
     assert need <= STATIC_BYTES, "test problem must fit the built-in scratch"
     ws = torch.empty(need, dtype=torch.uint8, device="cuda")
     want, got = _outputs(q, kmax), _outputs(q, kmax)
@@ -86,7 +86,7 @@ def test_static_scratch_entry_refuses_oversized_problem():
     lib = _abi()
     n, q, a = 200000, 4096, 1024     # ~420 MB of packed rows: far beyond 64 MiB
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    assert lib.dmlp_knn_local_workspace_bytes(q, n, a, sms) > STATIC_BYTES
+    assert lib.dmlp_knn_local_workspace_bytes(q, n, a, sms, 4) > STATIC_BYTES
     dummy = torch.zeros(16, dtype=torch.float64, device="cuda")
     p = C.c_void_p(dummy.data_ptr())
     rc = lib.dmlp_knn_local_static(p, p, q, p, p, n, a, 0, 4, p, p, p, p, p, None)
