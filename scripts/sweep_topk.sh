@@ -1,7 +1,11 @@
 #!/bin/bash
+# Sweep the work-decomposition knobs of dist_topk on the headline shape (run under gpurun).
+#   DMLP_TOPK_GMC    cluster rows (CTA pairs) per chunk and wave
+#   DMLP_TOPK_CHUNKS column ranges per query
+#   DMLP_TOPK_SYNC   re-alignment period in data tiles (0 = off)
 mkdir -p gpurun_out
-for cfg in "128 37 2" "64 37 2" "32 37 2" "16 37 2" "8 37 2" "32 18 4" "16 18 4" "16 12 6"; do
+for cfg in "37 2 1" "37 2 0" "24 3 1" "18 4 1" "12 6 1"; do
   set -- $cfg
-  echo -n "sync_kb=$1 gmc=$2 chunks=$3: "
-  DMLP_TOPK_SYNC=$1 DMLP_TOPK_GMC=$2 DMLP_TOPK_CHUNKS=$3 timeout 120 python scripts/phase_times.py --reps 2 | python -c "import sys,json; d=json.loads(sys.stdin.read()); p=d['plan']; print('grid',p['grid'],'gm',p['group_m'],'chunks',p['chunks'], round(d['ms']['dist_topk'],2),'ms', round(d['dist_topk_tflops'],1),'TF flagged',d['flagged'])"
+  echo -n "gmc=$1 chunks=$2 sync=$3: "
+  DMLP_TOPK_GMC=$1 DMLP_TOPK_CHUNKS=$2 DMLP_TOPK_SYNC=$3 timeout 120 python scripts/phase_times.py --reps 2 | python -c "import sys,json; d=json.loads(sys.stdin.read()); p=d['plan']; print('grid',p['grid'],'gm',p['group_m'],'chunks',p['chunks'], round(d['ms']['dist_topk'],2),'ms', round(d['dist_topk_tflops'],1),'TF flagged',d['flagged'])"
 done 2>&1 | tee gpurun_out/sweep_topk.log

@@ -133,12 +133,6 @@ __device__ __forceinline__ void tma_load_2d_mcast(void *smem_dst, const CUtensor
       "h"(cta_mask), "l"(policy)
       : "memory");
 }
-// Pull a tile from HBM into L2 ahead of the load that will consume it.
-__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap *map, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
-               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
-               : "memory");
-}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

@@ -576,11 +576,6 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           }
           asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
         }
-        if (plan.prefetch > 0) {
-          // experiment: offset the pairs that sweep the same chunk by a fixed lag
-          const int pos = (it.m >> 1) % plan.group_mc;
-          for (int w = 0; w < pos; ++w) __nanosleep(plan.prefetch);
-        }
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
             if (plan.sync && cta_rank == 0 && it.group_rows > 1 && kb == 0 &&
@@ -712,7 +707,6 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   if (const char *e = getenv("DMLP_TOPK_PAIR")) p.pair = atoi(e) != 0;
   if (p.m_blocks < 2) p.pair = 0;
   if (p.pair) cluster = 2;
-  p.prefetch = 0;
   p.rot = 0;
   // re-align the clusters of a chunk every `sync` data tiles: about once per 128 k-blocks of
   // work (a tile of the headline shape); problems with short rows are epilogue-bound and
@@ -721,7 +715,7 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   p.sync_cnt = nullptr;
   if (const char *e = getenv("DMLP_TOPK_SYNC")) p.sync = atoi(e);
   if (p.sync < 0) p.sync = 0;
-  if (const char *e = getenv("DMLP_TOPK_PREFETCH")) p.prefetch = atoi(e);
+
   // Cluster: CTAs that sweep the same data tiles in lock step and share each
   // tile through TMA multicast.  Never wider than the number of row blocks.
   if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) cluster = 4;

@@ -59,7 +59,6 @@ struct TopkPlan {
   int cluster;     ///< CTAs per cluster; they sweep the same data tiles via TMA multicast
   int mc_blocks;   ///< ceil(m_blocks / cluster): row-block groups handled by one cluster
   int group_mc;    ///< cluster rows per wave
-  int prefetch;    ///< experiment knob (producer start lag in ns); 0 = off
   int sync;        ///< > 0: clusters sweeping the same chunk re-align every `sync` data tiles (keeps their tile reads within L2 reach)
   unsigned *sync_cnt;  ///< device counters for `sync`, one per (group, chunk), zeroed per launch
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
