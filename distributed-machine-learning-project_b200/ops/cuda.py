@@ -257,6 +257,28 @@ def peer_gather(args):
     _check(lib.dmlp_peer_gather(C.byref(args), _stream()))
 
 
+class DataGatherArgs(C.Structure):
+    _fields_ = [("world", _i), ("rank", _i), ("a", _i), ("epoch", C.c_uint32), ("peer_base", _vp * 8),
+                ("off_xh", _u64), ("off_xn", _u64), ("off_xe", _u64), ("off_x64", _u64), ("off_labels", _u64),
+                ("off_pack_flags", _u64), ("part_begin", _i * 9), ("tile_count", _vp), ("status", _vp),
+                ("timeout_seconds", _dbl)]
+
+
+def dist_topk_rows(qh, n, cand, gather, kmax=0):
+    """Filter GEMM whose data operand is all-gathered from the row's peers inside the kernel."""
+    lib = _lib()
+    lib.dmlp_dist_topk_rows.argtypes = [_vp, _i, _i, _i, _i, _i, _vp, C.POINTER(DataGatherArgs), _vp]
+    q, a_pad = qh.shape
+    _check(lib.dmlp_dist_topk_rows(_p(qh), q, n, a_pad, sm_count(), kmax, _p(cand), C.byref(gather), _stream()))
+    return cand
+
+
+def maxima_from_norms(norm2, errn, st):
+    lib = _lib()
+    lib.dmlp_maxima_from_norms.argtypes = [_vp, _vp, _i64, _vp, _vp]
+    _check(lib.dmlp_maxima_from_norms(_p(norm2), _p(errn), norm2.numel(), _p(st), _stream()))
+
+
 def dist_topk_gather(xh, xnorm2, cand, gather, kmax=0):
     """K4: filter GEMM whose query operand is all-gathered from the peers inside the kernel."""
     lib = _lib()

@@ -110,14 +110,17 @@ class DistributedKNN:
         self.fused_ok = km <= K.FUSED_MAX_K and n > 0
         self.peer_fused = R > 1 and self.impl == "fused" and self.fused_ok
         self.peer_rows = C > 1 and self.impl == "fused"
+        # data operand gathered inside the GEMM (needs the CTA-pair kernel: >= 256 queries per column)
+        self.rows_fused = self.peer_rows and R == 1 and self.fused_ok and self.nq >= 256
         with torch.cuda.device(dev):
             self.status = torch.zeros(1, dtype=torch.int32, device=dev)
             self.stats = K.new_stats(dev)
             self.q_stats = K.new_stats(dev)
             self._alloc_shard(x_part, labels_part)
-            self.xh = torch.empty((n, self.a_pad), dtype=torch.float16, device=dev)
-            self.xn = torch.empty(n, dtype=torch.float32, device=dev)
-            self.xe = torch.empty(n, dtype=torch.float32, device=dev)
+            if not self.rows_fused:
+                self.xh = torch.empty((n, self.a_pad), dtype=torch.float16, device=dev)
+                self.xn = torch.empty(n, dtype=torch.float32, device=dev)
+                self.xe = torch.empty(n, dtype=torch.float32, device=dev)
             if self.peer_fused:
                 self._alloc_symmetric(q_slice, k_slice)
             else:
@@ -141,11 +144,32 @@ class DistributedKNN:
             lay.add("done_flags", 128)
             lay.add("x64", n * a * 8)
             lay.add("labels", n * 4)
+            if self.rows_fused:
+                lay.add("pack_flags", 128)
+                lay.add("xh", n * self.a_pad * 2)
+                lay.add("xn", n * 4)
+                lay.add("xe", n * 4)
             self.row_sym = sym = SymmetricBuffer(lay, dev, self.row_group)
             self.x = sym.view("x64", torch.float64, (n, a))
             self.labels = sym.view("labels", torch.int32)
             self.part_table = sym.pointer_table("part_flags")
             self.done_table = sym.pointer_table("done_flags")
+            if self.rows_fused:
+                self.xh = sym.view("xh", torch.float16, (n, self.a_pad))
+                self.xn = sym.view("xn", torch.float32)
+                self.xe = sym.view("xe", torch.float32)
+                self.row_pack_table = sym.pointer_table("pack_flags")
+                self.tile_count = torch.zeros((n + 255) // 256, dtype=torch.int32, device=dev)
+                dg = K.DataGatherArgs()
+                dg.world, dg.rank, dg.a = C, self.c, a
+                for p in range(C):
+                    dg.peer_base[p] = sym.peer_ptrs[p]
+                    dg.part_begin[p] = even_slice(n, C, p)[0]
+                dg.part_begin[C] = n
+                dg.off_xh, dg.off_xn, dg.off_xe = lay.off["xh"], lay.off["xn"], lay.off["xe"]
+                dg.off_x64, dg.off_labels, dg.off_pack_flags = lay.off["x64"], lay.off["labels"], lay.off["pack_flags"]
+                dg.tile_count, dg.status, dg.timeout_seconds = self.tile_count.data_ptr(), self.status.data_ptr(), 20.0
+                self.data_gather = dg
             self._row_gather_args = []
             for name, row_bytes in (("x64", a * 8), ("labels", 4)):
                 g = K.PeerGatherArgs()
@@ -253,6 +277,8 @@ class DistributedKNN:
         with torch.cuda.device(self.device):
             self.epoch += 1
             self.tracer.begin_step()
+            if self.rows_fused:
+                return self._run_rows_fused()
             with self.tracer.phase("row_gather"):
                 self._gather_shard()
             if self.impl == "nccl_cublas":
@@ -294,6 +320,49 @@ class DistributedKNN:
         self.launch_count += 4
         if self.R > 1:
             dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.col_group)
+
+    def _pack_part_and_signal(self):
+        """rows_fused: pack this rank's part of the data shard into the row-symmetric buffer and
+        tell the row it is ready; the GEMM's communication warps fetch the other parts."""
+        b, e = self.part_rows
+        K.pack(self.x_part, self.stats, None, out=(self.xh[b:e], self.xn[b:e], self.xe[b:e]))
+        self.row_sym.signal(self.row_pack_table, self.epoch)
+        self.data_gather.epoch = self.epoch
+        self.launch_count += 2
+
+    def _run_rows_fused(self):
+        """Grid 1 x C on resident inputs: the row all-gather of the data shard runs inside the
+        filter GEMM (packed rows just ahead of the tiles that need them, fp64 rows after)."""
+        tr = self.tracer
+        od, oi, ol, flags, nflag = self.lists
+        with tr.phase("stats"):
+            K.stats_reset(self.stats)
+            K.stats_reset(self.q_stats)
+            K.stats_update(self.x_part, self.stats)
+            K.stats_update(self.q_slice, self.stats)
+            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.row_group)
+            self.launch_count += 4
+        with tr.phase("pack"):
+            self._wait_part_readers(self.epoch - 1)   # peers may still be pulling the previous step's copy
+            self._pack_part_and_signal()
+            K.pack(self.q_slice, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
+        with tr.phase("dist_topk+row_allgather"):
+            K.dist_topk_rows(self.qh, self.shard_rows, self.cand, self.data_gather, kmax=self.kmax)
+            self.row_sym.signal(self.done_table, self.epoch)     # "I have finished reading your parts"
+            K.maxima_from_norms(self.xn, self.xe, self.stats)
+        nflag.zero_()
+        with tr.phase("rerank"):
+            K.rerank(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
+                     self.stats, self.id_base, self.kmax, out=self.lists)
+        self.launch_count += 7
+        flagged = int(nflag.item())
+        if flagged:
+            rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)
+            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows, out=(od, oi, ol))
+            self.launch_count += 3
+        self.last_flagged = flagged
+        with tr.phase("finalize"):
+            return self._reduce_and_finalize_nccl(od, oi, ol)
 
     def _run_peer_fused(self):
         r0, tr = self.r * self.qs, self.tracer
@@ -470,11 +539,12 @@ class DistributedKNN:
             torch.cuda.current_stream().synchronize()
             return self.host_out
 
-    def _wait_part_readers(self):
+    def _wait_part_readers(self, upto=None):
         """Before this rank's part of the data shard is overwritten: every rank of the row
         must have finished pulling the previous step's copy."""
-        if self.peer_rows and self.epoch > 0:
-            self.row_sym.wait("done_flags", self.epoch, self.status)
+        step = self.epoch if upto is None else upto
+        if self.peer_rows and step > 0:
+            self.row_sym.wait("done_flags", step, self.status)
 
     def _run_copy_then_compute(self):
         h = self.host
@@ -513,11 +583,15 @@ class DistributedKNN:
         main.wait_event(e_x)
         if dec:
             K.expand_decimal6(self.x_wire, self.x_part)
-        self._gather_shard()
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
-        K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+        gather_pending = self.rows_fused
+        if gather_pending:
+            self._pack_part_and_signal()
+        else:
+            self._gather_shard()
+            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
         od, oi, ol, flags, nflag = self.lists
         nflag.zero_()
         self.launch_count += 4 + (1 if dec else 0)
@@ -543,7 +617,14 @@ class DistributedKNN:
                 self._cand_by_rows[key] = torch.empty((key, plan["chunks"], plan["kp"]), dtype=torch.int64,
                                                       device=self.device)
             cand = self._cand_by_rows[key]
-            K.dist_topk(qh, self.xh, self.xn, cand=cand, kmax=self.kmax)
+            if gather_pending:      # the first GEMM of the step also gathers the data shard
+                K.dist_topk_rows(qh, self.shard_rows, cand, self.data_gather, kmax=self.kmax)
+                self.row_sym.signal(self.done_table, self.epoch)
+                K.maxima_from_norms(self.xn, self.xe, self.stats)
+                gather_pending = False
+                self.launch_count += 2
+            else:
+                K.dist_topk(qh, self.xh, self.xn, cand=cand, kmax=self.kmax)
             K.rerank(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], qn, qe, self.stats, self.stats,
                      self.id_base, self.kmax, out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
             self.launch_count += 5 + (1 if dec else 0)

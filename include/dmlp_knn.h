@@ -166,6 +166,29 @@ typedef struct dmlp_gather_args {
 int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, int kmax,
                           uint64_t *cand, const dmlp_gather_args *g, void *stream);
 
+/* The same fusion for the data operand (reference: the row MPI_Bcast of a data shard,
+ * engine.cpp:129-131): the `world` ranks of a grid row each pack one part of the shard --
+ * rows [part_begin[p], part_begin[p+1]) -- into their symmetric buffer (packed rows at
+ * off_xh, norms at off_xn / off_xe, fp64 rows at off_x64, labels at off_labels), signal
+ * pack_flags and call dmlp_dist_topk_rows.  The communication warps of the GEMM pull the
+ * other parts tile by tile in sweep order, then the fp64 rows and labels for the re-rank;
+ * afterwards the local buffer holds the whole shard.  tile_count: ceil(n / 256) local
+ * counters, zeroed once at set-up.  Run dmlp_maxima_from_norms on the gathered norm
+ * arrays before the re-rank. */
+typedef struct dmlp_data_gather_args {
+  int world, rank, a;
+  uint32_t epoch;
+  void *peer_base[8];
+  uint64_t off_xh, off_xn, off_xe, off_x64, off_labels, off_pack_flags;
+  int part_begin[9];
+  uint32_t *tile_count;
+  int *status;
+  double timeout_seconds;
+} dmlp_data_gather_args;
+int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms, int kmax, uint64_t *cand,
+                        const dmlp_data_gather_args *g, void *stream);
+int dmlp_maxima_from_norms(const float *norm2, const float *errn, int64_t rows, void *maxima, void *stream);
+
 /* K5, GEMM/top-k -> reduce-scatter of k-lists (reference: MPI_Gather of k-lists to
  * row 0 + re-select, engine.cpp:283-308): dmlp_rerank with its outputs redirected
  * into the owner's receive buffers [world][slice_rows][kmax] (off_dist, off_id,

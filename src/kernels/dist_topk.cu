@@ -168,7 +168,7 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
       float *xn = xn_all + acc * BN;
       for (int i = e_tid; i < BN; i += EPI_THREADS) {
         const int col = tile * BN + i;
-        xn[i] = col < plan.n ? __ldg(xnorm2 + col) : inf;
+        xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
       }
       named_barrier_sync(1, EPI_THREADS);
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -506,10 +506,121 @@ __device__ void gather_warp(const TopkPlan &plan, const GatherArgs &ga, int lane
   }
 }
 
+// Communication warp for the data operand (fused row all-gather).  Rows are taken tile by
+// tile in sweep order, the chunks interleaved; a finished row bumps its tile's counter.
+// Then the fp64 rows and labels of the other parts follow, starting with a different peer
+// on every rank.
+__device__ void data_gather_warp(const TopkPlan &plan, const DataGatherArgs &dg, int lane) {
+  const int G = gridDim.x, b = blockIdx.x;
+  unsigned ready_mask = 1u << dg.rank;
+  bool dead = false;
+  auto wait_peer = [&](int owner) {
+    if ((ready_mask >> owner) & 1u) return;
+    const unsigned *flag = reinterpret_cast<const unsigned *>(dg.peer_base[dg.rank] + dg.off_pack_flags) + owner;
+    const long long t0 = clock64();
+    while (static_cast<int>(ld_acquire_sys(flag) - dg.epoch) < 0) {
+      if (clock64() - t0 > dg.timeout_cycles) {
+        if (lane == 0 && dg.status) atomicExch(dg.status, 400 + owner);
+        dead = true;
+        break;
+      }
+      __nanosleep(100);
+    }
+    ready_mask |= 1u << owner;
+  };
+  auto owner_of = [&](int row) {
+    int o = 0;
+    while (o + 1 < dg.world && row >= dg.part_begin[o + 1]) ++o;
+    return o;
+  };
+  const int vec_per_row = plan.a_pad / 8;  // int4 = 8 halves
+  const int per_chunk = (plan.n_tiles + plan.chunks - 1) / plan.chunks;
+  const long long total = static_cast<long long>(per_chunk) * plan.chunks * BN;
+  for (long long seq = b; seq < total; seq += G) {
+    const int i = static_cast<int>(seq % BN);
+    const long long ts = seq / BN;
+    const int c = static_cast<int>(ts % plan.chunks), j = static_cast<int>(ts / plan.chunks);
+    const int tb = static_cast<int>(static_cast<long long>(c) * plan.n_tiles / plan.chunks);
+    const int te = static_cast<int>(static_cast<long long>(c + 1) * plan.n_tiles / plan.chunks);
+    const int tile = tb + j;
+    if (tile >= te) continue;
+    const int row = tile * BN + i;
+    if (row >= plan.n) continue;
+    const int owner = owner_of(row);
+    if (owner != dg.rank) {
+      wait_peer(owner);
+      if (!dead) {
+        const int4 *src = reinterpret_cast<const int4 *>(dg.peer_base[owner] + dg.off_xh) +
+                          static_cast<long long>(row) * vec_per_row;
+        int4 *dst = reinterpret_cast<int4 *>(dg.peer_base[dg.rank] + dg.off_xh) + static_cast<long long>(row) * vec_per_row;
+        for (int v0 = 0; v0 < vec_per_row; v0 += 32 * 8) {
+          int4 tmp[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < vec_per_row) tmp[u] = src[v];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < vec_per_row) dst[v] = tmp[u];
+          }
+        }
+        if (lane == 0) {
+          reinterpret_cast<float *>(dg.peer_base[dg.rank] + dg.off_xn)[row] =
+              reinterpret_cast<const float *>(dg.peer_base[owner] + dg.off_xn)[row];
+          reinterpret_cast<float *>(dg.peer_base[dg.rank] + dg.off_xe)[row] =
+              reinterpret_cast<const float *>(dg.peer_base[owner] + dg.off_xe)[row];
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      atomicAdd(dg.tile_count + tile, 1u);
+    }
+  }
+  // fp64 rows + labels of the other parts, for the re-rank kernel that follows
+  const bool vec_ok = (dg.a % 2) == 0;
+  for (int pj = 1; pj < dg.world && !dead; ++pj) {
+    const int owner = (dg.rank + pj) % dg.world;
+    wait_peer(owner);
+    if (dead) break;
+    for (int row = dg.part_begin[owner] + b; row < dg.part_begin[owner + 1]; row += G) {
+      const double *src = reinterpret_cast<const double *>(dg.peer_base[owner] + dg.off_x64) +
+                          static_cast<long long>(row) * dg.a;
+      double *dst = reinterpret_cast<double *>(dg.peer_base[dg.rank] + dg.off_x64) + static_cast<long long>(row) * dg.a;
+      if (vec_ok) {
+        const int n2 = dg.a / 2;
+        const double2 *s2 = reinterpret_cast<const double2 *>(src);
+        double2 *d2 = reinterpret_cast<double2 *>(dst);
+        for (int v0 = 0; v0 < n2; v0 += 32 * 8) {
+          double2 tmp[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < n2) tmp[u] = s2[v];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int v = v0 + u * 32 + lane;
+            if (v < n2) d2[v] = tmp[u];
+          }
+        }
+      } else {
+        for (int v = lane; v < dg.a; v += 32) dst[v] = src[v];
+      }
+      if (lane == 0)
+        reinterpret_cast<int *>(dg.peer_base[dg.rank] + dg.off_labels)[row] =
+            reinterpret_cast<const int *>(dg.peer_base[owner] + dg.off_labels)[row];
+    }
+  }
+}
+
 __global__ void __launch_bounds__(THREADS2, 1)
 dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
                       const float *__restrict__ xnorm2, const TopkPlan plan,
-                      unsigned long long *__restrict__ cand, const GatherArgs ga) {
+                      unsigned long long *__restrict__ cand, const GatherArgs ga, const DataGatherArgs dg) {
   using L = Layout2;
   constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of the data tile
   extern __shared__ uint8_t smem_raw[];
@@ -583,6 +694,20 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
         }
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
+          if (dg.world > 1) {
+            // the tile's packed rows (and norms) may still be on their way from the rank that packed them
+            const int rows_in_tile = min(BN, plan.n - tile * BN);
+            const unsigned target = dg.epoch * static_cast<unsigned>(rows_in_tile);
+            const long long t0 = clock64();
+            while (static_cast<int>(ld_acquire_gpu(dg.tile_count + tile) - target) < 0) {
+              if (clock64() - t0 > dg.timeout_cycles) {
+                if (dg.status) atomicExch(dg.status, 500);
+                break;
+              }
+              __nanosleep(64);
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
+          }
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
             if (plan.sync && cta_rank == 0 && it.group_rows > 1 && kb == 0 &&
                 ((tile - it.tile_begin) % plan.sync) == 0) {
@@ -641,6 +766,7 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     }
   } else if (warp == 6) {
     if (ga.world > 1) gather_warp(plan, ga, lane);
+    if (dg.world > 1) data_gather_warp(plan, dg, lane);
   } else {
     if (cta_rank == 0)
       epilogue_loop<false>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
@@ -786,7 +912,8 @@ __device__ unsigned g_sync_counters[kSyncCounters];
 }  // namespace
 
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan_in,
-                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s) {
+                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s,
+                     const DataGatherArgs *data_gather) {
   TopkPlan plan = plan_in;
   if (plan.q_rows <= 0 || plan.n <= 0) return 0;
   {
@@ -823,6 +950,10 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   if (gather != nullptr) ga = *gather;
   DMLP_REQUIRE(ga.world == 1 || plan.pair, "dist_topk: the fused operand gather needs the CTA-pair kernel");
   DMLP_REQUIRE(ga.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
+  DataGatherArgs dg;
+  if (data_gather != nullptr) dg = *data_gather;
+  DMLP_REQUIRE(dg.world == 1 || plan.pair, "dist_topk: the fused data gather needs the CTA-pair kernel");
+  DMLP_REQUIRE(dg.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -832,7 +963,7 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   if (plan.pair)
-    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel, tm_q, tm_x, xnorm2, plan, cand, ga));
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
   else
     DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_kernel, tm_q, tm_x, xnorm2, plan, cand));
   return 0;

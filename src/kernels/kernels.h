@@ -92,6 +92,23 @@ struct GatherArgs {
   long long timeout_cycles = 0;
 };
 
+/// The same idea for the data operand (the reference's row Bcast of a data shard,
+/// engine.cpp:129-131, fused into the GEMM): the ranks of a grid row each packed one part
+/// of the shard; the communication warps pull the other parts' packed rows and norms tile
+/// by tile in the order the sweep needs them (per-tile counters gate the TMA producers),
+/// then the fp64 rows and labels for the re-rank.
+struct DataGatherArgs {
+  int world = 1, rank = 0;
+  int a = 0;                   ///< fp64 row length
+  unsigned epoch = 0;
+  unsigned char *peer_base[kMaxPeers] = {};
+  unsigned long long off_xh = 0, off_xn = 0, off_xe = 0, off_x64 = 0, off_labels = 0, off_pack_flags = 0;
+  int part_begin[kMaxPeers + 1] = {};  ///< rank p packed rows [part_begin[p], part_begin[p + 1])
+  unsigned *tile_count = nullptr;      ///< local, one counter per 256-row data tile, monotonically increasing
+  int *status = nullptr;
+  long long timeout_cycles = 0;
+};
+
 /// Where the exact k-lists go (K5): straight into the owner rank's receive
 /// buffer [world][slice_rows][kmax], through the peer mapping.
 struct ScatterArgs {
@@ -104,9 +121,13 @@ struct ScatterArgs {
 int launch_expand_decimal6(const int *src, double *dst, long long count, cudaStream_t s);
 int launch_encode_decimal6(const double *src, int *dst, long long count, int *bad, cudaStream_t s);
 
+/// max row norm / error norm over packed rows, from the norm arrays (after a gather)
+int launch_maxima_from_norms(const float *norm2, const float *errn, long long rows, PackStats *maxima, cudaStream_t s);
+
 // dist_topk.cu  (cand: [q_rows][chunks][kp] keys, ascending per list)
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
-                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s);
+                     unsigned long long *cand, const GatherArgs *gather, cudaStream_t s,
+                     const DataGatherArgs *data_gather = nullptr);
 
 // rerank.cu
 struct RerankArgs {

@@ -166,6 +166,35 @@ int launch_encode_decimal6(const double *src, int *dst, long long count, int *ba
   return 0;
 }
 
+__global__ void __launch_bounds__(256) maxima_from_norms_kernel(const float *__restrict__ norm2,
+                                                                const float *__restrict__ errn, long long rows,
+                                                                PackStats *maxima) {
+  float mn = 0.f, me = 0.f;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < rows; i += stride) {
+    mn = fmaxf(mn, norm2[i]);
+    me = fmaxf(me, errn[i]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = fmaxf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+    me = fmaxf(me, __shfl_xor_sync(0xFFFFFFFFu, me, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(reinterpret_cast<int *>(&maxima->max_norm), __float_as_int(__fsqrt_ru(mn) * (1.0f + 1e-6f)));
+    atomicMax(reinterpret_cast<int *>(&maxima->max_err), __float_as_int(me));
+  }
+}
+
+int launch_maxima_from_norms(const float *norm2, const float *errn, long long rows, PackStats *maxima,
+                             cudaStream_t s) {
+  if (rows <= 0) return 0;
+  long long blocks = (rows + 256 * 4 - 1) / (256 * 4);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  maxima_from_norms_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(norm2, errn, rows, maxima);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int launch_stats_reset(PackStats *st, cudaStream_t s) {
   stats_reset_kernel<<<1, 32, 0, s>>>(st);
   DMLP_CUDA_OK(cudaGetLastError());

@@ -134,6 +134,32 @@ int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a
                           reinterpret_cast<unsigned long long *>(cand), &ga, st(stream));
 }
 
+int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms, int kmax, uint64_t *cand,
+                        const dmlp_data_gather_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr && g->world >= 1 && g->world <= kMaxPeers, "dist_topk_rows: world must be in [1, 8]");
+  if (num_sms <= 0)
+    if (int rc = current_sm_count(&num_sms)) return rc;
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
+  DMLP_REQUIRE(p.pair == 1 || g->world == 1, "dist_topk_rows: needs the CTA-pair kernel (at least 256 queries)");
+  DataGatherArgs dg;
+  dg.world = g->world; dg.rank = g->rank; dg.a = g->a; dg.epoch = g->epoch;
+  for (int i = 0; i < g->world; ++i) dg.peer_base[i] = static_cast<unsigned char *>(g->peer_base[i]);
+  for (int i = 0; i <= g->world; ++i) dg.part_begin[i] = g->part_begin[i];
+  DMLP_REQUIRE(dg.part_begin[0] == 0 && dg.part_begin[g->world] == n, "dist_topk_rows: parts must cover [0, n)");
+  dg.off_xh = g->off_xh; dg.off_xn = g->off_xn; dg.off_xe = g->off_xe; dg.off_x64 = g->off_x64;
+  dg.off_labels = g->off_labels; dg.off_pack_flags = g->off_pack_flags;
+  dg.tile_count = g->tile_count; dg.status = g->status;
+  dg.timeout_cycles = static_cast<long long>((g->timeout_seconds > 0 ? g->timeout_seconds : 20.0) * 1.5e9);
+  const __half *xh = reinterpret_cast<const __half *>(dg.peer_base[dg.rank] + dg.off_xh);
+  const float *xn = reinterpret_cast<const float *>(dg.peer_base[dg.rank] + dg.off_xn);
+  return launch_dist_topk(static_cast<const __half *>(q_fp16), xh, xn, p,
+                          reinterpret_cast<unsigned long long *>(cand), nullptr, st(stream), &dg);
+}
+
+int dmlp_maxima_from_norms(const float *norm2, const float *errn, int64_t rows, void *maxima, void *stream) {
+  return launch_maxima_from_norms(norm2, errn, rows, static_cast<PackStats *>(maxima), st(stream));
+}
+
 int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                         const int *x_labels, const int *k, const float *q_norm2, const float *q_errn,
                         const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
