@@ -93,3 +93,24 @@ def test_distributed_large_k(tmp_path, repo_root):
     assert out.count('"checked"') == world and '"peer_fused": true' in out
     out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 100, 120, f"{world}x1")
     assert out.count('"checked"') == world and '"peer_fused": false' in out
+
+
+def test_engine_binary_device_grids(tmp_path, repo_root):
+    """The C++ driver (`engine`, one process for all GPUs) on R x C device grids vs its CPU backend."""
+    import hashlib
+    n_gpu = torch.cuda.device_count()
+    if n_gpu < 2:
+        pytest.skip("needs at least 2 GPUs")
+    exe = os.path.join(repo_root, "engine")
+    args = ["--synth", "30000", "900", "48", "-100", "100", "1", "20", "7", "5"]
+
+    def run(env_extra):
+        res = subprocess.run([exe, *args], capture_output=True, text=True, env=dict(os.environ, **env_extra), timeout=240)
+        assert res.returncode == 0, res.stderr[-2000:]
+        return hashlib.md5("".join(sorted(res.stdout.splitlines(True))).encode()).hexdigest()
+
+    want = run({"DMLP_BACKEND": "cpu"})
+    grids = [f"{n_gpu}x1", f"1x{n_gpu}"] + ([f"2x{n_gpu // 2}"] if n_gpu >= 4 else [])
+    for g in grids:
+        assert run({"DMLP_BACKEND": "gpu", "DMLP_GRID": g}) == want, g
+    assert run({"DMLP_BACKEND": "gpu_exact", "DMLP_GRID": f"{n_gpu}x1"}) == want
