@@ -257,6 +257,17 @@ def peer_gather(args):
     _check(lib.dmlp_peer_gather(C.byref(args), _stream()))
 
 
+def dist_topk_part(qh, xh_part, xnorm2_part, cand, chunk_base, row_base, kmax=0):
+    """Filter GEMM on a slice of the data shard, writing lists [chunk_base, ...) of `cand`
+    ([q, cand_chunks, kp]) with shard-wide row ids."""
+    lib = _lib()
+    lib.dmlp_dist_topk_part.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _vp]
+    q, a_pad = qh.shape
+    _check(lib.dmlp_dist_topk_part(_p(qh), _p(xh_part), _p(xnorm2_part), q, xh_part.shape[0], a_pad, sm_count(), kmax,
+                                   _p(cand), cand.shape[1], chunk_base, row_base, _stream()))
+    return cand
+
+
 class DataGatherArgs(C.Structure):
     _fields_ = [("world", _i), ("rank", _i), ("a", _i), ("epoch", C.c_uint32), ("peer_base", _vp * 8),
                 ("off_xh", _u64), ("off_xn", _u64), ("off_xe", _u64), ("off_x64", _u64), ("off_labels", _u64),

@@ -523,6 +523,10 @@ class DistributedKNN:
                 self.x_wire = torch.empty(self.x_part.shape, dtype=torch.int32, device=dev)
                 self.q_wire = [torch.empty((rows, self.a), dtype=torch.int32, device=dev) for _ in range(2)]
             self._cand_by_rows = {}
+            self.x_parts = max(1, int(os.environ.get("DMLP_E2E_XPARTS", "4")))
+            if self.shard_rows < 4096 * self.x_parts:
+                self.x_parts = 1
+            self._tiled = None
             torch.cuda.synchronize(dev)
 
     def run_from_host(self):
@@ -530,7 +534,9 @@ class DistributedKNN:
         With a single-rank column the copy of the next query chunk overlaps the
         kernels of the current one (two streams)."""
         with torch.cuda.device(self.device):
-            if getattr(self, "streamed", False):
+            if getattr(self, "streamed", False) and self.world == 1 and self.x_parts > 1:
+                label, checksum = self._run_tiled()
+            elif getattr(self, "streamed", False):
                 label, checksum = self._run_streamed()
             else:
                 label, checksum = self._run_copy_then_compute()
@@ -562,6 +568,117 @@ class DistributedKNN:
         self.labels_part.copy_(h["labels"], non_blocking=True)
         self.k_slice.copy_(h["k"], non_blocking=True)
         return self.run_resident()
+
+    def _tiled_schedule(self):
+        """Static schedule of the single-GPU end-to-end step: the data shard is cut into
+        `x_parts` row ranges and the queries into chunks; pieces are copied in an order that
+        lets work start after the first two pieces, and each (query chunk, data part) pair is
+        filtered as soon as both have arrived."""
+        if self._tiled is not None:
+            return self._tiled
+        n, nq, rows = self.shard_rows, self.nq, self.chunk_rows
+        part = _round_up(-(-n // self.x_parts), 256)
+        xparts = [(b, min(b + part, n)) for b in range(0, n, part)]
+        qch = [(b, min(b + rows, nq)) for b in range(0, nq, rows)]
+        cands, bases = [], []
+        for (b, e) in qch:
+            base, acc = [], 0
+            for (pb, pe) in xparts:
+                base.append(acc)
+                acc += K.topk_plan(e - b, pe - pb, self.a_pad, kmax=self.kmax)["chunks"]
+            bases.append(base)
+            cands.append(torch.empty((e - b, acc, K.KP), dtype=torch.int64, device=self.device))
+        # copy order: q0, x0, then alternate data parts and query chunks
+        order, xi, qi = [("q", 0), ("x", 0)], 1, 1
+        while xi < len(xparts) or qi < len(qch):
+            if xi < len(xparts):
+                order.append(("x", xi))
+                xi += 1
+            if qi < len(qch):
+                order.append(("q", qi))
+                qi += 1
+        self._tiled = (xparts, qch, cands, bases, order)
+        return self._tiled
+
+    def _run_tiled(self):
+        h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream
+        dec = self.wire == "decimal6"
+        xparts, qch, cands, bases, order = self._tiled_schedule()
+        od, oi, ol, flags, nflag = self.lists
+        cs.wait_stream(main)                      # previous step's readers of the buffers are done
+        self.epoch += 1
+        e_small = torch.cuda.Event()
+        with torch.cuda.stream(cs):
+            self.labels_part.copy_(h["labels"], non_blocking=True)
+            self.k_slice.copy_(h["k"], non_blocking=True)
+            e_small.record(cs)
+        K.stats_reset(self.stats)
+        K.stats_reset(self.q_stats)
+        K.stats_set(self.stats, *self.host_range)
+        nflag.zero_()
+        self.launch_count += 2
+        have_x, have_q = set(), set()
+        done, reranked = set(), set()
+        e_free, n_qcopies = [None, None], 0
+        for kind, idx in order:
+            ev = torch.cuda.Event()
+            if kind == "x":
+                pb, pe = xparts[idx]
+                with torch.cuda.stream(cs):
+                    (self.x_wire if dec else self.x_part)[pb:pe].copy_(h["x"][pb:pe], non_blocking=True)
+                    ev.record(cs)
+                main.wait_event(ev)
+                if dec:
+                    K.expand_decimal6(self.x_wire[pb:pe], self.x_part[pb:pe])
+                K.pack(self.x[pb:pe], self.stats, self.stats, out=(self.xh[pb:pe], self.xn[pb:pe], self.xe[pb:pe]))
+                have_x.add(idx)
+            else:
+                b, e = qch[idx]
+                slot = n_qcopies & 1
+                n_qcopies += 1
+                with torch.cuda.stream(cs):
+                    if dec:
+                        if e_free[slot] is not None:
+                            cs.wait_event(e_free[slot])      # the expand two chunks ago has drained this buffer
+                        self.q_wire[slot][: e - b].copy_(h["q"][b:e], non_blocking=True)
+                    else:
+                        self.q_slice[b:e].copy_(h["q"][b:e], non_blocking=True)
+                    ev.record(cs)
+                main.wait_event(ev)
+                if dec:
+                    K.expand_decimal6(self.q_wire[slot][: e - b], self.q_slice[b:e])
+                    e_free[slot] = torch.cuda.Event()
+                    e_free[slot].record(main)
+                K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(self.qh[b:e], self.qn[b:e], self.qe_[b:e]))
+                have_q.add(idx)
+            self.launch_count += 1 + (1 if dec else 0)
+            for i in sorted(have_q):
+                b, e = qch[i]
+                for p_ in sorted(have_x):
+                    if (i, p_) in done:
+                        continue
+                    pb, pe = xparts[p_]
+                    K.dist_topk_part(self.qh[b:e], self.xh[pb:pe], self.xn[pb:pe], cands[i], bases[i][p_], pb,
+                                     kmax=self.kmax)
+                    done.add((i, p_))
+                    self.launch_count += 1
+                if i not in reranked and all((i, p_) in done for p_ in range(len(xparts))):
+                    main.wait_event(e_small)
+                    K.rerank(cands[i], self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], self.qn[b:e],
+                             self.qe_[b:e], self.stats, self.stats, self.id_base, self.kmax,
+                             out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
+                    reranked.add(i)
+                    self.launch_count += 3
+        label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+        self.launch_count += 1
+        flagged = int(nflag.item())
+        if flagged:
+            rows_f = torch.nonzero(flags[: self.nq], as_tuple=False).flatten().to(torch.int32)
+            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows_f, out=(od, oi, ol))
+            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+            self.launch_count += 4
+        self.last_flagged = flagged
+        return label, checksum
 
     def _run_streamed(self):
         h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream

@@ -59,6 +59,15 @@ int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
                    int num_sms, int kmax, uint64_t *cand, void *stream);
 
+/* The same kernel on a slice of the data shard: rows [row_base, row_base + n_part) whose
+ * packed rows / norms start at x_fp16_part / x_norm2_part.  The launch writes lists
+ * [chunk_base, chunk_base + chunks(q, n_part)) of a candidate buffer that has cand_chunks
+ * lists per query, and emits shard-wide row ids.  Lets a caller start filtering while the
+ * rest of the shard is still arriving from the host (see DistributedKNN.run_from_host). */
+int dmlp_dist_topk_part(const void *q_fp16, const void *x_fp16_part, const float *x_norm2_part, int q, int n_part,
+                        int a_pad, int num_sms, int kmax, uint64_t *cand, int cand_chunks, int chunk_base,
+                        int row_base, void *stream);
+
 /* ---- K2 exact_rerank (reference: engine.cpp:12-18 semantics) ------------------
  * Writes, per query, kmax slots of (dist, id, label): the exact local top-k in
  * (distance asc, id desc) order, padded with (1e18, -1, -1).  flags[q] != 0 marks

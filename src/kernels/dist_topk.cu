@@ -191,7 +191,7 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
         tmem_ld_wait();
         // score 8 columns at a time; the append path runs only for an octet that holds a hit,
         // which is rare once the row's threshold has tightened
-        const int id0 = tile * BN + c0;
+        const int id0 = plan.row_base + tile * BN + c0;
 #pragma unroll
         for (int o = 0; o < 4; ++o) {
           float s[8];
@@ -222,7 +222,8 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
     __syncwarp();
     for (int r = 0; r < 32; ++r) {
       const long long qrow = static_cast<long long>(it.m) * BM + quarter * 32 + r;
-      unsigned long long *out = qrow < plan.q_rows ? cand + (qrow * plan.chunks + it.chunk) * KP : nullptr;
+      unsigned long long *out =
+          qrow < plan.q_rows ? cand + (qrow * plan.cand_chunks + plan.chunk_base + it.chunk) * KP : nullptr;
       compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, out);
     }
     cnt = 0;
@@ -840,6 +841,9 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   if (p.m_blocks < 2) p.pair = 0;
   if (p.pair) cluster = 2;
   p.rot = 0;
+  p.cand_chunks = 0;  // filled in once the chunk count is known
+  p.chunk_base = 0;
+  p.row_base = 0;
   // re-align the clusters of a chunk every `sync` data tiles: about once per 128 k-blocks of
   // work (a tile of the headline shape); problems with short rows are epilogue-bound and
   // their tiles are small, so they skip it.  DMLP_TOPK_SYNC=<tiles>, 0 = off
@@ -898,6 +902,7 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   p.group_mc = gmc;
   p.group_m = gmc * cluster;
   p.chunks = c;
+  p.cand_chunks = c;
   long long items = static_cast<long long>((p.mc_blocks + gmc - 1) / gmc) * gmc * c;
   int use = static_cast<int>(items < nclusters ? (items > 0 ? items : 1) : nclusters);
   // one wave = one whole group (gmc x c clusters), so that clusters sharing a chunk run side by side

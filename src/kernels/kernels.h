@@ -61,6 +61,9 @@ struct TopkPlan {
   int group_mc;    ///< cluster rows per wave
   int sync;        ///< > 0: clusters sweeping the same chunk re-align every `sync` data tiles (keeps their tile reads within L2 reach)
   unsigned *sync_cnt;  ///< device counters for `sync`, one per (group, chunk), zeroed per launch
+  int cand_chunks; ///< lists per query in the candidate buffer (>= chunks; several launches can share one buffer)
+  int chunk_base;  ///< first list index this launch writes
+  int row_base;    ///< added to the row ids this launch emits (the operand is a slice of a larger shard)
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
   int hint_q, hint_x;  ///< L2 eviction hints for query / data tiles: 0 normal, 1 first, 2 last
 };

@@ -134,6 +134,21 @@ int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a
                           reinterpret_cast<unsigned long long *>(cand), &ga, st(stream));
 }
 
+int dmlp_dist_topk_part(const void *q_fp16, const void *x_fp16_part, const float *x_norm2_part, int q, int n_part,
+                        int a_pad, int num_sms, int kmax, uint64_t *cand, int cand_chunks, int chunk_base,
+                        int row_base, void *stream) {
+  if (num_sms <= 0)
+    if (int rc = current_sm_count(&num_sms)) return rc;
+  TopkPlan p = make_topk_plan(q, n_part, a_pad, 32, num_sms, kmax);
+  DMLP_REQUIRE(chunk_base >= 0 && chunk_base + p.chunks <= cand_chunks,
+               "dist_topk_part: this launch's lists do not fit the candidate buffer");
+  p.cand_chunks = cand_chunks;
+  p.chunk_base = chunk_base;
+  p.row_base = row_base;
+  return launch_dist_topk(static_cast<const __half *>(q_fp16), static_cast<const __half *>(x_fp16_part), x_norm2_part,
+                          p, reinterpret_cast<unsigned long long *>(cand), nullptr, st(stream));
+}
+
 int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms, int kmax, uint64_t *cand,
                         const dmlp_data_gather_args *g, void *stream) {
   DMLP_REQUIRE(g != nullptr && g->world >= 1 && g->world <= kMaxPeers, "dist_topk_rows: world must be in [1, 8]");

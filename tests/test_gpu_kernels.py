@@ -187,15 +187,19 @@ def test_decimal6_wire_round_trip(K):
     assert not K.encode_decimal6(big)[1]
 
 
-def test_streamed_end_to_end_single_gpu(K):
+@pytest.mark.parametrize("n_total,parts", [(9000, 1), (20000, 4)])
+def test_streamed_end_to_end_single_gpu(K, n_total, parts):
+    """run_from_host: copies overlapped with compute; with a large enough shard the data is
+    cut into parts and every (query chunk, data part) pair is filtered as it arrives."""
     from dmlp_b200.parallel import DistributedKNN
     eng = DistributedKNN(device=torch.device("cuda", 0))
-    eng.synth_problem(n_total=9000, q_total=40000, a=64, lo=-100.0, hi=100.0, min_k=1, max_k=12, num_labels=5, seed=3)
+    eng.synth_problem(n_total=n_total, q_total=40000, a=64, lo=-100.0, hi=100.0, min_k=1, max_k=12, num_labels=5,
+                      seed=3)
     _, ref = eng.run_resident()
     ref = ref.cpu().numpy().copy()
     for wire in ("auto", "fp64"):
         eng.stage_host_inputs(wire=wire)
-        assert eng.streamed and eng.wire == ("decimal6" if wire == "auto" else "fp64")
+        assert eng.streamed and eng.wire == ("decimal6" if wire == "auto" else "fp64") and eng.x_parts == parts
         for _ in range(2):
             _, chk = eng.run_from_host()
             assert (chk.numpy() == ref).all(), wire
