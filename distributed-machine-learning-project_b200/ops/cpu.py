@@ -30,6 +30,8 @@ def _lib():
         lib.dmlp_parse_header.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int64),
                                           C.POINTER(C.c_int64), C.POINTER(C.c_int)]
         lib.dmlp_parse_text.argtypes = [C.c_char_p, C.c_size_t, C.c_int, _d, _i, _d, _i]
+        lib.dmlp_parse_update.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int), _d, C.c_int,
+                                          C.POINTER(C.c_int)]
         lib.dmlp_synth_fill.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_int,
                                         C.c_int, C.c_int, C.c_uint64, _d, _i, _d, _i]
         lib.dmlp_choose_grid.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -127,6 +129,16 @@ def parse_text(text, threads=0):
     _check(_lib().dmlp_parse_text(text, len(text), threads, data.reshape(-1), labels,
                                   queries.reshape(-1), k))
     return data, labels, queries, k
+
+
+def parse_update(line, max_attrs=1 << 16):
+    """Parse one update record 'id v0 v1 ...' (reference: common.cpp:46-55).  Returns (id, values)."""
+    if isinstance(line, str):
+        line = line.encode()
+    ident, count = C.c_int(), C.c_int()
+    buf = np.empty(max_attrs, np.float64)
+    _check(_lib().dmlp_parse_update(line, len(line), C.byref(ident), buf, max_attrs, C.byref(count)))
+    return ident.value, buf[:min(count.value, max_attrs)].copy()
 
 
 def synth(n, q, a, lo=-100.0, hi=100.0, min_k=1, max_k=1, num_labels=2, seed=42):

@@ -16,6 +16,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <vector>
 
 #include "dmlp/views.h"
 
@@ -69,6 +70,10 @@ class Problem {
 /// same conditions the reference checks.  `threads` <= 0 picks the hardware
 /// concurrency.
 void parse_problem(const char *text, size_t len, int threads, Problem *out);
+
+/// One update record `id v0 v1 ...` (reference: parse_update, common.cpp:46-55 -- never
+/// called there either; kept so the Update type of common.h has its parser).
+bool parse_update_line(const char *text, size_t len, int *id, std::vector<double> *new_attrs);
 
 /// Read everything from `f` (stdin in the driver) and parse it.
 void read_problem(std::FILE *f, int threads, Problem *out);

@@ -48,6 +48,10 @@ int dmlp_parse_header(const char *text, size_t len, int64_t *n, int64_t *q, int 
 int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attrs, int *data_labels,
                     double *query_attrs, int *query_k);
 
+/* One update record "id v0 v1 ..." (reference: parse_update, common.cpp:46-55; unused by its
+ * engine).  *count receives the number of values found; at most `capacity` are stored. */
+int dmlp_parse_update(const char *text, size_t len, int *id, double *attrs, int capacity, int *count);
+
 /* Host twin of the device fill kernel (generate_input.py:13-21 distribution). */
 int dmlp_synth_fill(int64_t n, int64_t q, int a, double lo, double hi, int min_k, int max_k,
                     int num_labels, uint64_t seed, double *data_attrs, int *data_labels,

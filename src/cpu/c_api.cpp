@@ -143,6 +143,15 @@ int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attr
   });
 }
 
+int dmlp_parse_update(const char *text, size_t len, int *id, double *attrs, int capacity, int *count) {
+  return guarded([&] {
+    std::vector<double> v;
+    if (!dmlp::parse_update_line(text, len, id, &v)) throw std::runtime_error("Line is empty");
+    *count = static_cast<int>(v.size());
+    for (int i = 0; i < *count && i < capacity; ++i) attrs[i] = v[size_t(i)];
+  });
+}
+
 int dmlp_synth_fill(int64_t n, int64_t q, int a, double lo, double hi, int min_k, int max_k,
                     int num_labels, uint64_t seed, double *data_attrs, int *data_labels,
                     double *query_attrs, int *query_k) {

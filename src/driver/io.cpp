@@ -157,6 +157,26 @@ void parse_problem(const char *text, size_t len, int threads, Problem *out) {
     if (!e.empty()) throw std::runtime_error(e);
 }
 
+bool parse_update_line(const char *text, size_t len, int *id, std::vector<double> *new_attrs) {
+  const char *end = text + len;
+  while (end > text && (end[-1] == '\n' || end[-1] == '\r')) --end;
+  const char *p = skip_blank(text, end);
+  if (p == end) return false;
+  p = take_int(p, end, id);
+  new_attrs->clear();
+  for (;;) {
+    p = skip_blank(p, end);
+    if (p < end && *p == '+') ++p;
+    if (p >= end) break;
+    double v = 0.0;
+    auto r = std::from_chars(p, end, v);
+    if (r.ec != std::errc()) break;  // a failed extraction ends the list, as operator>> does
+    new_attrs->push_back(v);
+    p = r.ptr;
+  }
+  return true;
+}
+
 void read_problem(std::FILE *f, int threads, Problem *out) {
   std::vector<char> buf;
   size_t used = 0;

@@ -23,7 +23,8 @@ assert (checksum == want_sum[ob:oe]).all() and (label == want_label[ob:oe]).all(
 owned = [None] * dist.get_world_size()
 dist.all_gather_object(owned, (ob, oe))
 assert sorted(i for b, e in owned for i in range(b, e)) == list(range(q))      # every query owned exactly once
-print("rank", dist.get_rank(), "ok", flush=True)
+sys.stdout.write(f"rank{dist.get_rank()}-ok\n")
+sys.stdout.flush()
 dist.destroy_process_group()
 '''
 
@@ -37,4 +38,4 @@ def test_gloo_grid_matches_oracle(tmp_path, repo_root, world, grid):
                           "--nnodes=1", f"--nproc-per-node={world}", str(script), grid],
                          capture_output=True, text=True, env=env, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
-    assert res.stdout.count(" ok") == world
+    assert res.stdout.count("-ok") == world, res.stdout

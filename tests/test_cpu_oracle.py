@@ -135,6 +135,16 @@ def test_parser_errors_match_reference_messages():
     assert k.tolist() == [1, 1]
 
 
+def test_parse_update_record():
+    # reference: parse_update (common.cpp:46-55): an id, then as many values as the line holds
+    ident, vals = cpu.parse_update("17 1.5 -2.25 3e2 +4\n")
+    assert ident == 17 and vals.tolist() == [1.5, -2.25, 300.0, 4.0]
+    ident, vals = cpu.parse_update("3")
+    assert ident == 3 and vals.size == 0
+    with pytest.raises(RuntimeError, match="Line is empty"):
+        cpu.parse_update("   \n")
+
+
 def test_exact_distance_is_sequential_non_fused():
     rng = np.random.default_rng(1)
     a, b = rng.uniform(-100, 100, 257), rng.uniform(-100, 100, 257)
