@@ -84,6 +84,12 @@ int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs,
 /* Diagnostics: subsequent dmlp_rerank* launches also record, per query, how many
  * survivors they recomputed in fp64 (device int[q]); NULL turns it off. */
 void dmlp_debug_rerank_w(int *w_out);
+/* Diagnostics: with DMLP_TOPK_PROF=1 in the environment the CTA-pair filter kernel records, per CTA,
+ * {mma total, mma operand wait, mma accumulator wait, producer total, producer stage wait, producer
+ * re-alignment wait, epilogue accumulator wait, epilogue total, epilogue norm staging, accumulator
+ * loads, scoring and appends, list compaction, list flush, 3 unused} in SM cycles; this copies the
+ * counters of the last launch to host memory (16 values per CTA) and returns the number of CTAs. */
+int dmlp_debug_topk_prof(unsigned long long *host_out, int max_ctas);
 
 /* ---- exact fp64 brute force (reference: engine.cpp:233-257 as written) --------
  * Processes `count` queries: rows query_rows[0..count) or, with NULL, rows

@@ -103,21 +103,30 @@ __device__ __forceinline__ void warp_sort64(unsigned long long &a, unsigned long
 
 // Warp-cooperative compaction of one row's list: sort, keep the KP smallest,
 // publish the new count and threshold to the lane that owns the row.  With
-// `emit` the sorted keys are also written to global memory.
-__device__ __forceinline__ void compact_row(unsigned long long *row_keys, int rot, int r, int lane, int &cnt,
-                                            float &tau, unsigned long long *emit) {
-  const int rcnt = __shfl_sync(0xFFFFFFFFu, cnt, r);
-  unsigned long long a = (lane < rcnt) ? row_keys[(lane + rot) & (CAP - 1)] : kKeyInvalid;
-  unsigned long long b = (lane + 32 < rcnt) ? row_keys[(lane + 32 + rot) & (CAP - 1)] : kKeyInvalid;
+// `emit` the sorted keys are also written to global memory.  The sort is kept
+// out of line: it is the bulk of the epilogue's code and is called from several
+// places; one copy keeps the epilogue within the instruction cache.
+__device__ __noinline__ unsigned long long compact_sorted(uint32_t row_addr, int rot, int rcnt, int lane,
+                                                          unsigned long long *emit) {
+  unsigned long long a = kKeyInvalid, b = kKeyInvalid;
+  const uint32_t addr_a = row_addr + (((lane + rot) & (CAP - 1)) << 3);
+  const uint32_t addr_b = row_addr + (((lane + 32 + rot) & (CAP - 1)) << 3);
+  if (lane < rcnt) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(a) : "r"(addr_a) : "memory");
+  if (lane + 32 < rcnt) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(b) : "r"(addr_b) : "memory");
   warp_sort64(a, b, lane);
-  row_keys[(lane + rot) & (CAP - 1)] = a;
-  const unsigned long long last = __shfl_sync(0xFFFFFFFFu, a, KP - 1);
+  asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr_a), "l"(a) : "memory");
+  if (emit != nullptr) emit[lane] = a;
+  __syncwarp();
+  return __shfl_sync(0xFFFFFFFFu, a, KP - 1);
+}
+__device__ __forceinline__ void compact_row(uint32_t row_addr, int rot, int r, int lane, int &cnt, float &tau,
+                                            unsigned long long *emit) {
+  const int rcnt = __shfl_sync(0xFFFFFFFFu, cnt, r);
+  const unsigned long long last = compact_sorted(row_addr, rot, rcnt, lane, emit);
   if (lane == r) {
     cnt = rcnt < KP ? rcnt : KP;
     tau = (rcnt >= KP) ? key_score(last) : std::numeric_limits<float>::infinity();
   }
-  if (emit != nullptr) emit[lane] = a;
-  __syncwarp();
 }
 
 // Smem layout.  `STG` pipeline stages of (query tile, data tile[ half]) precede the
@@ -151,64 +160,107 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quarter = warp & 3;              // tensor-memory lane quarter this warp may read
   const int row_in_tile = quarter * 32 + lane;
-  unsigned long long *lists = reinterpret_cast<unsigned long long *>(smem + off_list);
-  const uint32_t keys_base = smem_u32(lists + row_in_tile * CAP);  // this row's list, shared-space address
+  const uint32_t lists_addr = smem_u32(smem + off_list);  // [BM][CAP] keys, shared-space address
+  const uint32_t keys_base = lists_addr + row_in_tile * CAP * 8;  // this row's list, shared-space address
   float *xn_all = reinterpret_cast<float *>(smem + off_xn);
   const int e_tid = threadIdx.x - 64;
   const float inf = std::numeric_limits<float>::infinity();
   int cnt = 0;
   float tau = inf;
   uint32_t acc_it = 0;
+  uint32_t uses[2] = {0, 0};  // how often each accumulator stage has been drained
+  long long prof_wait = 0, prof_stage = 0, prof_ld = 0, prof_score = 0, prof_compact = 0, prof_flush = 0;
+  const bool prof = plan.prof != nullptr;
+  const long long prof_t0 = prof ? clock64() : 0;
 
   for (int t = cluster_id; t < total_items; t += num_clusters) {
     Item it;
     if (!get_item(plan, t, cta_rank, &it)) continue;
     for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
-      const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
-      float *xn = xn_all + acc * BN;
+      // stages alternate tile by tile; the wide pair kernel restarts at stage 0 with every item
+      // (its odd tiles own stage 1, and an item with an odd tile count leaves that one unused)
+      const uint32_t acc = plan.wide ? static_cast<uint32_t>((tile - it.tile_begin) & 1) : (acc_it & 1);
+      const uint32_t acc_phase = (acc ? uses[1] : uses[0]) & 1;
+      if (acc) ++uses[1]; else ++uses[0];
+      float *xn = xn_all + (acc_it & 1) * BN;  // (not `acc`: two tiles in a row can share a stage across items)
+      const long long ps0 = prof ? clock64() : 0;
       for (int i = e_tid; i < BN; i += EPI_THREADS) {
         const int col = tile * BN + i;
         xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
       }
       named_barrier_sync(1, EPI_THREADS);
+      const long long pw0 = prof ? clock64() : 0;
+      if (prof) prof_stage += pw0 - ps0;
       mbar_wait(&tfull_bar[acc], acc_phase);
+      if (prof) prof_wait += clock64() - pw0;
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       // (one tcgen05.ld in flight at a time: overlapping the load of the next 32 columns with
       // the scoring of the current ones measured 25-80 % slower, for the MMA as well)
+      const uint32_t xn_addr = smem_u32(xn);
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        // make room for up to 32 appends per row
-        __syncwarp();
-        unsigned need = __ballot_sync(0xFFFFFFFFu, cnt > CAP - 32);
-        while (need) {
-          const int r = __ffs(need) - 1;
-          need &= need - 1;
-          compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, nullptr);
-        }
         uint32_t v[32];
+        float x[32];
+        const long long pl0 = prof ? clock64() : 0;
         tmem_ld_32x32(t_row + c0, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)  // the norms of these 32 rows (same address in every lane: a broadcast)
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(x[4 * i]), "=f"(x[4 * i + 1]), "=f"(x[4 * i + 2]), "=f"(x[4 * i + 3])
+                       : "r"(xn_addr + (c0 + 4 * i) * 4));
         tmem_ld_wait();
-        // score 8 columns at a time; the append path runs only for an octet that holds a hit,
-        // which is rare once the row's threshold has tightened
+        if (prof) {  // the load is only complete once a register it fills can be read
+          uint32_t sink;
+          asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(v[31]));
+          asm volatile("" ::"r"(sink));
+        }
+        const long long pl1 = prof ? clock64() : 0;
+        if (prof) prof_ld += pl1 - pl0;
+        long long pc_blk = 0;
+        // all 32 scores at once (independent FMAs), then one octet at a time: the octet's minimum
+        // against the threshold decides, for the whole warp, whether its append code runs at all
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = fmaf(-2.0f, __uint_as_float(v[j]), x[j]);
         const int id0 = plan.row_base + tile * BN + c0;
 #pragma unroll
         for (int o = 0; o < 4; ++o) {
-          float s[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) s[j] = fmaf(-2.0f, __uint_as_float(v[8 * o + j]), xn[c0 + 8 * o + j]);
-          const float mn = fminf(fminf(fminf(s[0], s[1]), fminf(s[2], s[3])), fminf(fminf(s[4], s[5]), fminf(s[6], s[7])));
-          if (mn < tau) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (s[j] < tau) {
-                const unsigned long long key = make_key(s[j], id0 + 8 * o + j);
-                const uint32_t addr = keys_base + (((cnt + row_in_tile) & (CAP - 1)) << 3);
-                asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr), "l"(key) : "memory");
-                ++cnt;
-              }
+          const float *sc = x + 8 * o;
+          const float mn = fminf(fminf(fminf(sc[0], sc[1]), fminf(sc[2], sc[3])),
+                                 fminf(fminf(sc[4], sc[5]), fminf(sc[6], sc[7])));
+          if (!__any_sync(0xFFFFFFFFu, mn < tau)) continue;
+          // Room for the 8 appends an octet can make.  Compacting only when a list is nearly
+          // full (not whenever it holds more than KP keys) costs a slightly stale threshold
+          // and saves most of the sorts: a row appends ~250 keys per 30 000 columns, mostly one
+          // at a time, and a sort per append was the bulk of the epilogue's instructions.
+          unsigned need = __ballot_sync(0xFFFFFFFFu, cnt > CAP - 8);
+          if (need) {
+            const long long pc0 = prof ? clock64() : 0;
+            while (need) {
+              const int r = __ffs(need) - 1;
+              need &= need - 1;
+              compact_row(lists_addr + (quarter * 32 + r) * CAP * 8, quarter * 32 + r, r, lane, cnt, tau, nullptr);
             }
+            if (prof) pc_blk += clock64() - pc0;
           }
+          // branch-free appends: every lane runs the same 8 predicated stores
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t addr = keys_base + (((cnt + row_in_tile) & (CAP - 1)) << 3);
+            const uint32_t ob = float_to_ordered(sc[j]);
+            const int hit = sc[j] < tau;
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "setp.ne.s32 p, %0, 0;\n\t"
+                "@p st.shared.v2.b32 [%1], {%2, %3};\n\t}" ::"r"(hit),
+                "r"(addr), "r"(id0 + 8 * o + j), "r"(ob)
+                : "memory");
+            cnt += hit;
+          }
+        }
+        if (prof) {
+          prof_compact += pc_blk;
+          prof_score += clock64() - pl1 - pc_blk;
         }
       }
       tc_fence_before();
@@ -220,14 +272,26 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
     }
     // flush this (row block, chunk): sorted kp keys per row
     __syncwarp();
+    const long long pf0 = prof ? clock64() : 0;
     for (int r = 0; r < 32; ++r) {
       const long long qrow = static_cast<long long>(it.m) * BM + quarter * 32 + r;
       unsigned long long *out =
           qrow < plan.q_rows ? cand + (qrow * plan.cand_chunks + plan.chunk_base + it.chunk) * KP : nullptr;
-      compact_row(lists + (quarter * 32 + r) * CAP, quarter * 32 + r, r, lane, cnt, tau, out);
+      compact_row(lists_addr + (quarter * 32 + r) * CAP * 8, quarter * 32 + r, r, lane, cnt, tau, out);
     }
     cnt = 0;
     tau = inf;
+    if (prof) prof_flush += clock64() - pf0;
+  }
+  if (prof && quarter == 0 && lane == 0) {
+    unsigned long long *o = plan.prof + blockIdx.x * 16;
+    o[6] = prof_wait;
+    o[7] = clock64() - prof_t0;
+    o[8] = prof_stage;
+    o[9] = prof_ld;
+    o[10] = prof_score;
+    o[11] = prof_compact;
+    o[12] = prof_flush;
   }
 }
 
@@ -618,20 +682,28 @@ __device__ void data_gather_warp(const TopkPlan &plan, const DataGatherArgs &dg,
   }
 }
 
+template <bool WIDE>
 __global__ void __launch_bounds__(THREADS2, 1)
 dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
                       const float *__restrict__ xnorm2, const TopkPlan plan,
                       unsigned long long *__restrict__ cand, const GatherArgs ga, const DataGatherArgs dg) {
-  using L = Layout2;
-  constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of the data tile
+  // WIDE: every stage holds one query tile and this CTA's halves of TWO data tiles, and both
+  // accumulator stages are filled side by side (256 x 512 per pair and k-loop).  The query
+  // operand then crosses L2 -> SM once per two data tiles: 48 instead of 64 bytes per SM and
+  // clock at full tensor rate, against an L2 that delivers ~43 (measured 8.7 TB/s at 72 %).
+  // The price is that the two stages drain while the MMA waits.
+  constexpr int NST = WIDE ? STAGES : STAGES2;
+  constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of one data tile
+  constexpr int BS_BYTES = WIDE ? B_BYTES : BH_BYTES;  // data bytes per stage
+  using L = Layout<NST, BS_BYTES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kOffBar);
-  uint64_t *full_bar = bars;                    // [STAGES2]  (the leader's copy is the live one)
-  uint64_t *empty_bar = bars + STAGES2;         // [STAGES2]  per CTA, released by the leader's commits
-  uint64_t *tfull_bar = bars + 2 * STAGES2;     // [2]        per CTA
-  uint64_t *tempty_bar = bars + 2 * STAGES2 + 2;  // [2]      leader's copy collects both epilogues
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES2 + 4);
+  uint64_t *full_bar = bars;                    // [NST]  (the leader's copy is the live one)
+  uint64_t *empty_bar = bars + NST;         // [NST]  per CTA, released by the leader's commits
+  uint64_t *tfull_bar = bars + 2 * NST;     // [2]        per CTA
+  uint64_t *tempty_bar = bars + 2 * NST + 2;  // [2]      leader's copy collects both epilogues
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * NST + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -645,7 +717,7 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int s = 0; s < STAGES2; ++s) {
+      for (int s = 0; s < NST; ++s) {
         mbar_init(&full_bar[s], 1);
         mbar_init(&empty_bar[s], 1);
       }
@@ -675,6 +747,8 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      long long pw_empty = 0, pw_sync = 0;
+      const long long p_t0 = plan.prof ? clock64() : 0;
       const uint64_t pol_q = plan.hint_q == 2 ? kL2EvictLast : (plan.hint_q == 1 ? kL2EvictFirst : kL2EvictNormal);
       const uint64_t pol_x = plan.hint_x == 2 ? kL2EvictLast : (plan.hint_x == 1 ? kL2EvictFirst : kL2EvictNormal);
       for (int t = cluster_id; t < total_items; t += num_clusters) {
@@ -694,24 +768,28 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           }
           asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
         }
-        for (int tile = it.tile_begin; tile < it.tile_end; ++tile) {
+        constexpr int TSTEP = WIDE ? 2 : 1;
+        for (int tile = it.tile_begin; tile < it.tile_end; tile += TSTEP) {
+          const bool two = WIDE && tile + 1 < it.tile_end;
           if (dg.world > 1) {
             // the tile's packed rows (and norms) may still be on their way from the rank that packed them
-            const int rows_in_tile = min(BN, plan.n - tile * BN);
-            const unsigned target = dg.epoch * static_cast<unsigned>(rows_in_tile);
-            const long long t0 = clock64();
-            while (static_cast<int>(ld_acquire_gpu(dg.tile_count + tile) - target) < 0) {
-              if (clock64() - t0 > dg.timeout_cycles) {
-                if (dg.status) atomicExch(dg.status, 500);
-                break;
+            for (int h = 0; h <= (two ? 1 : 0); ++h) {
+              const int rows_in_tile = min(BN, plan.n - (tile + h) * BN);
+              const unsigned target = dg.epoch * static_cast<unsigned>(rows_in_tile);
+              const long long t0 = clock64();
+              while (static_cast<int>(ld_acquire_gpu(dg.tile_count + tile + h) - target) < 0) {
+                if (clock64() - t0 > dg.timeout_cycles) {
+                  if (dg.status) atomicExch(dg.status, 500);
+                  break;
+                }
+                __nanosleep(64);
               }
-              __nanosleep(64);
             }
             asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
           }
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
             if (plan.sync && cta_rank == 0 && it.group_rows > 1 && kb == 0 &&
-                ((tile - it.tile_begin) % plan.sync) == 0) {
+                (((tile - it.tile_begin) / TSTEP) % plan.sync) == 0) {
               // Re-align the pairs that sweep this chunk.  They read the same data tiles; L2
               // only holds a few k-blocks of every stream, so once the pairs drift apart each
               // one re-fetches the tile from HBM.  One counter per (group, chunk): arrive,
@@ -724,15 +802,26 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
               while (static_cast<int>(ld_acquire_gpu(cnt) - target) < 0) {
                 if (clock64() - t0 > 2000000000LL) break;  // never hang on a lost peer
               }
+              if (plan.prof) pw_sync += clock64() - t0;
             }
+            const long long pe0 = plan.prof ? clock64() : 0;
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + BH_BYTES));
+            if (plan.prof) pw_empty += clock64() - pe0;
+            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + (two ? 2 : 1) * BH_BYTES));
             tma_load_2d_pair(smem + L::kOffA + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM, pol_q);
-            tma_load_2d_pair(smem + L::kOffB + stage * BH_BYTES, &tm_x, &full_bar[stage], kb * BK,
+            tma_load_2d_pair(smem + L::kOffB + stage * BS_BYTES, &tm_x, &full_bar[stage], kb * BK,
                              tile * BN + cta_rank * (BN / 2), pol_x);
-            if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+            if (two)
+              tma_load_2d_pair(smem + L::kOffB + stage * BS_BYTES + BH_BYTES, &tm_x, &full_bar[stage], kb * BK,
+                               (tile + 1) * BN + cta_rank * (BN / 2), pol_x);
+            if (++stage == NST) { stage = 0; phase ^= 1; }
           }
         }
+      }
+      if (plan.prof) {
+        plan.prof[blockIdx.x * 16 + 3] = clock64() - p_t0;
+        plan.prof[blockIdx.x * 16 + 4] = pw_empty;
+        plan.prof[blockIdx.x * 16 + 5] = pw_sync;
       }
     }
   } else if (warp == 1) {
@@ -742,27 +831,80 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_it = 0;
+      uint32_t uses[2] = {0, 0};  // fills of each accumulator stage (same count as the epilogue keeps)
+      long long mw_full = 0, mw_tempty = 0;
+      const long long m_t0 = plan.prof ? clock64() : 0;
       for (int t = cluster_id; t < total_items; t += num_clusters) {
         Item it;
         if (!get_item(plan, t, cta_rank, &it)) continue;
+        if constexpr (WIDE) {
+          for (int tile = it.tile_begin; tile < it.tile_end; tile += 2) {
+            const bool two = tile + 1 < it.tile_end;
+            const long long w0 = plan.prof ? clock64() : 0;
+            mbar_wait(&tempty_bar[0], (uses[0] & 1) ^ 1);
+            if (plan.prof) mw_tempty += clock64() - w0;
+            tc_fence_after();
+            for (int kb = 0; kb < plan.k_blocks; ++kb) {
+              const long long w1 = plan.prof ? clock64() : 0;
+              mbar_wait(&full_bar[stage], phase);
+              if (plan.prof) mw_full += clock64() - w1;
+              tc_fence_after();
+              const uint64_t da = make_smem_desc_sw128(smem_u32(smem + L::kOffA + stage * A_BYTES));
+              const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BS_BYTES));
+#pragma unroll
+              for (int kk = 0; kk < BK / 16; ++kk)
+                umma_f16_pair(tmem_base, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+              if (two) {
+                if (kb == 0) {  // the second stage drains after the first: wait as late as possible
+                  const long long w2 = plan.prof ? clock64() : 0;
+                  mbar_wait(&tempty_bar[1], (uses[1] & 1) ^ 1);
+                  if (plan.prof) mw_tempty += clock64() - w2;
+                  tc_fence_after();
+                }
+                const uint64_t db1 = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BS_BYTES + BH_BYTES));
+#pragma unroll
+                for (int kk = 0; kk < BK / 16; ++kk)
+                  umma_f16_pair(tmem_base + BN, da + 2 * kk, db1 + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+              }
+              umma_commit_pair(&empty_bar[stage]);  // frees this stage in both CTAs
+              if (++stage == NST) { stage = 0; phase ^= 1; }
+            }
+            umma_commit_pair(&tfull_bar[0]);
+            ++uses[0];
+            if (two) {
+              umma_commit_pair(&tfull_bar[1]);
+              ++uses[1];
+            }
+          }
+        } else {
         for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
           const uint32_t acc = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
+          const long long w0 = plan.prof ? clock64() : 0;
           mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+          if (plan.prof) mw_tempty += clock64() - w0;
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * BN;
           for (int kb = 0; kb < plan.k_blocks; ++kb) {
+            const long long w1 = plan.prof ? clock64() : 0;
             mbar_wait(&full_bar[stage], phase);
+            if (plan.prof) mw_full += clock64() - w1;
             tc_fence_after();
             const uint64_t da = make_smem_desc_sw128(smem_u32(smem + L::kOffA + stage * A_BYTES));
-            const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BH_BYTES));
+            const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BS_BYTES));
 #pragma unroll
             for (int kk = 0; kk < BK / 16; ++kk)
               umma_f16_pair(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
             umma_commit_pair(&empty_bar[stage]);  // frees this stage in both CTAs
-            if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+            if (++stage == NST) { stage = 0; phase ^= 1; }
           }
           umma_commit_pair(&tfull_bar[acc]);      // both CTAs' epilogues may read their rows
         }
+        }
+      }
+      if (plan.prof) {
+        plan.prof[blockIdx.x * 16 + 0] = clock64() - m_t0;
+        plan.prof[blockIdx.x * 16 + 1] = mw_full;
+        plan.prof[blockIdx.x * 16 + 2] = mw_tempty;
       }
     }
   } else if (warp == 6) {
@@ -840,6 +982,12 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   if (const char *e = getenv("DMLP_TOPK_PAIR")) p.pair = atoi(e) != 0;
   if (p.m_blocks < 2) p.pair = 0;
   if (p.pair) cluster = 2;
+  // wide tiles pay when the k-loop is long enough to amortise draining both accumulators
+  // with the MMA idle (measured: A = 8192 11 % faster, A = 1024 27 % slower)
+  p.wide = p.k_blocks >= 64;
+  p.prof = nullptr;
+  if (const char *e = getenv("DMLP_TOPK_WIDE")) p.wide = atoi(e) != 0;
+  if (!p.pair) p.wide = 0;
   p.rot = 0;
   p.cand_chunks = 0;  // filled in once the chunk count is known
   p.chunk_base = 0;
@@ -914,7 +1062,18 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
 namespace {
 constexpr int kSyncCounters = 16384;
 __device__ unsigned g_sync_counters[kSyncCounters];
+constexpr int kProfCtas = 256;
+__device__ unsigned long long g_prof[kProfCtas * 16];
+int g_prof_ctas = 0;
 }  // namespace
+
+int dist_topk_prof_read(unsigned long long *host_out, int max_ctas) {
+  const int n = g_prof_ctas < max_ctas ? g_prof_ctas : max_ctas;
+  if (n <= 0) return 0;
+  DMLP_CUDA_OK(cudaDeviceSynchronize());
+  DMLP_CUDA_OK(cudaMemcpyFromSymbol(host_out, g_prof, sizeof(unsigned long long) * 16 * n));
+  return n;
+}
 
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan_in,
                      unsigned long long *cand, const GatherArgs *gather, cudaStream_t s,
@@ -937,14 +1096,25 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
       plan.sync = 0;
     }
   }
+  plan.prof = nullptr;
+  if (getenv("DMLP_TOPK_PROF") && plan.pair && plan.grid <= kProfCtas) {
+    void *p = nullptr;
+    DMLP_CUDA_OK(cudaGetSymbolAddress(&p, g_prof));
+    DMLP_CUDA_OK(cudaMemsetAsync(p, 0, sizeof(unsigned long long) * 16 * plan.grid, s));
+    plan.prof = static_cast<unsigned long long *>(p);
+    g_prof_ctas = plan.grid;
+  }
   DMLP_REQUIRE(plan.kp == KP, "dist_topk: this build keeps 32 keys per (query, chunk)");
   DMLP_REQUIRE(plan.a_pad % BK == 0 && plan.a_pad > 0, "dist_topk: a_pad must be a positive multiple of 64");
   CUtensorMap tm_q, tm_x;
   if (int rc = make_fp16_tile_map(&tm_q, qh, plan.q_rows, plan.a_pad, BM)) return rc;
   if (int rc = make_fp16_tile_map(&tm_x, xh, plan.n, plan.a_pad, plan.pair ? BN / 2 : BN / plan.cluster)) return rc;
-  const int smem_bytes = plan.pair ? Layout2::kBytes : Layout1::kBytes;
-  if (plan.pair)
-    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  if (!plan.pair) plan.wide = 0;
+  const int smem_bytes = plan.pair ? (plan.wide ? Layout1::kBytes : Layout2::kBytes) : Layout1::kBytes;
+  if (plan.pair && plan.wide)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  else if (plan.pair)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   else
     DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg = {};
@@ -967,8 +1137,10 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (plan.pair)
-    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+  if (plan.pair && plan.wide)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<true>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+  else if (plan.pair)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<false>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
   else
     DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_kernel, tm_q, tm_x, xnorm2, plan, cand));
   return 0;

@@ -64,6 +64,8 @@ struct TopkPlan {
   int cand_chunks; ///< lists per query in the candidate buffer (>= chunks; several launches can share one buffer)
   int chunk_base;  ///< first list index this launch writes
   int row_base;    ///< added to the row ids this launch emits (the operand is a slice of a larger shard)
+  int wide;        ///< pair kernel only: 1 = one query tile meets two data tiles per k-block (256 x 512 per pair; query tiles are read half as often)
+  unsigned long long *prof;  ///< diagnostics (DMLP_TOPK_PROF=1): per CTA 16 cycle counters, see dist_topk_prof_read
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
   int hint_q, hint_x;  ///< L2 eviction hints for query / data tiles: 0 normal, 1 first, 2 last
 };
@@ -131,6 +133,13 @@ int launch_maxima_from_norms(const float *norm2, const float *errn, long long ro
 int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, const TopkPlan &plan,
                      unsigned long long *cand, const GatherArgs *gather, cudaStream_t s,
                      const DataGatherArgs *data_gather = nullptr);
+
+/// Diagnostics of the last dist_topk launch made with DMLP_TOPK_PROF=1 (pair kernel): per CTA
+/// {mma total, mma wait for operands, mma wait for a drained accumulator, producer total,
+///  producer wait for a free stage, producer re-alignment wait, epilogue wait for a full
+///  accumulator, epilogue total, epilogue norm staging, accumulator loads, scoring and appends,
+///  list compaction, list flush, 3 unused} in SM cycles (16 values per CTA).  Returns the number of CTAs written.
+int dist_topk_prof_read(unsigned long long *host_out, int max_ctas);
 
 // rerank.cu
 struct RerankArgs {

@@ -200,6 +200,7 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
 }
 
 void dmlp_debug_rerank_w(int *w_out) { set_rerank_debug_w(w_out); }
+int dmlp_debug_topk_prof(unsigned long long *host_out, int max_ctas) { return dist_topk_prof_read(host_out, max_ctas); }
 
 size_t dmlp_rerank_workspace_bytes(int q, int kmax) { return rerank_workspace_bytes(q, kmax); }
 
