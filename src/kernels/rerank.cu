@@ -180,17 +180,18 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankA
 }
 
 // ------------------------------------------------------------------- exact
-// One warp per query.  Lane r owns survivor r and runs its sequential chain; the
-// warp cooperatively streams 32-column chunks of the survivors' rows (and of the
-// query row) through a private two-stage cp.async ring, so every global access is
-// a coalesced 256-byte row segment and no block-wide barrier is needed.
-// Measured on B200: this pass is bound by fp64 instruction issue (about one warp-level
-// DADD/DMUL per 12 clocks per SM sub-partition), not by HBM, so what counts is full
-// warps.  A warp therefore takes 32 consecutive entries of the dense pair list, whatever
-// queries they belong to; lane r runs pair r's sequential chain.  The warp streams
-// 32-column chunks of the 32 data rows and of the lanes' query rows (duplicates are L2
-// hits) through a private two-stage cp.async ring: every global access is a coalesced
-// 256-byte row segment and there is no block-wide barrier.
+// A warp takes 32 consecutive entries of the dense pair list, whatever queries they belong
+// to (full warps); lane r runs pair r's sequential chain.  The warp streams 32-column chunks
+// of the 32 data rows and of the lanes' query rows (duplicates are L2 hits) through a private
+// two-stage cp.async ring: every global access is a coalesced 256-byte row segment and there
+// is no block-wide barrier.
+// Measured on B200 (headline shape, 1.03 M pairs x 8192 columns, profiles/ncu_final_kernels_v2_r1.txt):
+// 57 GB from HBM in 23.7 M SM cycles = 13.0 ms at 1.83 GHz (4.4 TB/s, 0.67 of the measured copy
+// rate), 16-17 ms at the ~1.3 GHz a power-capped step runs at; fp64 pipe 11 % busy, 6 warps per
+// SM.  Tried and slower: 16-column chunks with 2, 3 or 4 stages (17.7-18.3 ms), 32 columns x 3
+// stages (25.7 ms, 4 warps per SM), one cp.async.bulk per lane and row segment (50 ms: the
+// copy engine is per-warp uniform and 256-byte copies are far below its efficient size),
+// chains spread over 4 warps, per-thread global loads.
 constexpr int XC = 32;             // columns per chunk
 constexpr int XSTR = XC + 2;       // row stride in doubles (16-byte aligned rows)
 constexpr int XROWS = 64;          // 32 data rows + 32 query rows
