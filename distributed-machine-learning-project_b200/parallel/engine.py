@@ -517,7 +517,7 @@ class DistributedKNN:
             self.d2h_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host_out)
             self.streamed = self.R == 1 and self.fused_ok and self.impl == "fused"
             self.copy_stream = torch.cuda.Stream(device=dev)
-            rows = min(self.E2E_CHUNK_ROWS, max(self.nq, 1))
+            rows = min(int(os.environ.get("DMLP_E2E_QROWS", self.E2E_CHUNK_ROWS)), max(self.nq, 1))
             self.chunk_rows = rows
             if use_dec:
                 self.x_wire = torch.empty(self.x_part.shape, dtype=torch.int32, device=dev)

@@ -34,7 +34,7 @@ for line in sass.splitlines():
         flush()
         name, counts = m.group(1), collections.Counter()
         continue
-    m = re.match(r"\s+/\*[0-9a-f]{4,6}\*/\s+(?:@!?U?P\d\s+)?([A-Z][A-Z0-9_.]*)", line)
+    m = re.match(r"\s+/\*[0-9a-f]{4,6}\*/\s+(?:@!?U?P\d\s+)?([A-Z][A-Za-z0-9_.]*)", line)
     if m and counts is not None:
         counts[m.group(1)] += 1
 flush()
