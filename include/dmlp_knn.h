@@ -84,6 +84,10 @@ int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs,
 /* Diagnostics: subsequent dmlp_rerank* launches also record, per query, how many
  * survivors they recomputed in fp64 (device int[q]); NULL turns it off. */
 void dmlp_debug_rerank_w(int *w_out);
+/* Host replay of the filter kernel's work enumeration for the plan dmlp_topk_plan() returns: 8 ints
+ * per item and CTA {cluster, cta rank, row block, chunk, first tile, end tile, wave group, cluster
+ * rows in the group}.  Needs no GPU.  Returns the number of items (only max_items are stored). */
+int dmlp_debug_topk_items(int q, int n, int a_pad, int num_sms, int kmax, int *out, int max_items);
 /* Diagnostics: with DMLP_TOPK_PROF=1 in the environment the CTA-pair filter kernel records, per CTA,
  * {mma total, mma operand wait, mma accumulator wait, producer total, producer stage wait, producer
  * re-alignment wait, epilogue accumulator wait, epilogue total, epilogue norm staging, accumulator

@@ -53,12 +53,12 @@ struct Item {
 
 // Work items are enumerated per cluster: item t names a cluster row (`cluster`
 // consecutive 128-query blocks, one per CTA of the cluster) and a chunk.
-__device__ __forceinline__ bool get_item(const TopkPlan &p, int t, int cta_rank, Item *it) {
+__host__ __device__ __forceinline__ bool get_item(const TopkPlan &p, int t, int cta_rank, Item *it) {
   const int per_group = p.group_mc * p.chunks;
   const int g = t / per_group;
   const int rem = t - g * per_group;
   const int m0 = g * p.group_mc;
-  const int gm = min(p.group_mc, p.mc_blocks - m0);
+  const int gm = p.group_mc < p.mc_blocks - m0 ? p.group_mc : p.mc_blocks - m0;
   if (gm <= 0 || rem >= gm * p.chunks) return false;
   const int c = rem / gm;
   it->group = g;
@@ -1066,6 +1066,26 @@ constexpr int kProfCtas = 256;
 __device__ unsigned long long g_prof[kProfCtas * 16];
 int g_prof_ctas = 0;
 }  // namespace
+
+int enumerate_topk_items(const TopkPlan &plan, int *out, int max_items) {
+  const int num_clusters = plan.grid / plan.cluster;
+  const int per_group = plan.group_mc * plan.chunks;
+  const int total_items = ((plan.mc_blocks + plan.group_mc - 1) / plan.group_mc) * per_group;
+  int n = 0;
+  for (int cluster_id = 0; cluster_id < num_clusters; ++cluster_id)
+    for (int t = cluster_id; t < total_items; t += num_clusters)
+      for (int rank = 0; rank < plan.cluster; ++rank) {
+        Item it;
+        if (!get_item(plan, t, rank, &it)) continue;
+        if (n < max_items) {
+          int *o = out + static_cast<long long>(n) * 8;
+          o[0] = cluster_id; o[1] = rank; o[2] = it.m; o[3] = it.chunk;
+          o[4] = it.tile_begin; o[5] = it.tile_end; o[6] = it.group; o[7] = it.group_rows;
+        }
+        ++n;
+      }
+  return n;
+}
 
 int dist_topk_prof_read(unsigned long long *host_out, int max_ctas) {
   const int n = g_prof_ctas < max_ctas ? g_prof_ctas : max_ctas;

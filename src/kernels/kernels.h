@@ -134,6 +134,12 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
                      unsigned long long *cand, const GatherArgs *gather, cudaStream_t s,
                      const DataGatherArgs *data_gather = nullptr);
 
+/// The work items of a plan in the order the kernel walks them (host replay of the kernel's
+/// enumeration, for tests): 8 ints per item and CTA {cluster, cta rank, row block, chunk,
+/// first tile, end tile, wave group, cluster rows in the group}.  Returns the item count
+/// (which may exceed max_items; only max_items are stored).
+int enumerate_topk_items(const TopkPlan &plan, int *out, int max_items);
+
 /// Diagnostics of the last dist_topk launch made with DMLP_TOPK_PROF=1 (pair kernel): per CTA
 /// {mma total, mma wait for operands, mma wait for a drained accumulator, producer total,
 ///  producer wait for a free stage, producer re-alignment wait, epilogue wait for a full

@@ -1,0 +1,128 @@
+"""Work decomposition of the filter GEMM, checked on the host (no GPU needed).
+
+The planner (make_topk_plan) and the kernel's item enumeration (get_item) are a
+contract: every (128-query row block, 256-point data tile) must be visited exactly
+once, every candidate list (row block, chunk) must be produced exactly once, and the
+clusters that re-align on a (wave group, chunk) counter must all be resident at the
+same time.  dmlp_debug_topk_items replays the enumeration on the host.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from dmlp_b200 import _native
+
+SMS = 148
+
+
+def _lib():
+    try:
+        lib = _native.knn_lib()
+    except OSError as e:  # CPU-only build of the repo (make NO_CUDA=1)
+        pytest.skip(f"libdmlp_knn.so not built: {e}")
+    lib.dmlp_topk_plan.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int * 8)]
+    lib.dmlp_debug_topk_items.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_int]
+    return lib
+
+
+def plan_and_items(q, n, a_pad, kmax, sms=SMS):
+    lib = _lib()
+    arr = (C.c_int * 8)()
+    assert lib.dmlp_topk_plan(q, n, a_pad, sms, kmax, C.byref(arr)) == 0
+    keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp", "cluster"]
+    plan = dict(zip(keys, list(arr)))
+    cap = 1 << 16
+    buf = np.zeros((cap, 8), dtype=np.int32)
+    cnt = lib.dmlp_debug_topk_items(q, n, a_pad, sms, kmax, buf.ctypes.data, cap)
+    assert 0 < cnt <= cap
+    return plan, buf[:cnt]
+
+
+SHAPES = [
+    (65536, 65536, 8192, 16),     # headline: wide pair kernel, 37 x 2
+    (16384, 262144, 1024, 16),    # mid: narrow pair kernel
+    (10000, 1000000, 64, 16),     # short rows, odd tile counts per chunk
+    (9000, 777, 128, 4),          # fewer tiles than clusters
+    (300, 5000, 64, 8),           # three row blocks
+    (128, 100000, 64, 16),        # a single row block: one-CTA kernel
+    (65536, 65536, 8192, 96),     # large k: many chunks
+    (1, 1, 64, 1),
+    (257, 257, 4096, 40),
+]
+
+
+@pytest.mark.parametrize("q,n,a_pad,kmax", SHAPES)
+def test_every_tile_of_every_row_block_once(q, n, a_pad, kmax):
+    plan, items = plan_and_items(q, n, a_pad, kmax)
+    mb, nt, chunks = plan["m_blocks"], plan["n_tiles"], plan["chunks"]
+    assert mb == -(-q // 128) and nt == -(-n // 256) and plan["k_blocks"] == a_pad // 64
+    assert plan["grid"] % plan["cluster"] == 0 and plan["grid"] <= SMS
+    seen = np.zeros((mb, nt), dtype=np.int32)
+    lists = np.zeros((mb, chunks), dtype=np.int32)
+    for cl, rank, m, chunk, tb, te, group, rows in items:
+        assert 0 <= chunk < chunks and 0 <= tb <= te <= nt
+        if m >= mb:
+            continue  # phantom block of a partly filled cluster row: computes on zero fill, writes nothing
+        seen[m, tb:te] += 1
+        lists[m, chunk] += 1
+    assert (seen == 1).all()
+    assert (lists == 1).all()
+
+
+@pytest.mark.parametrize("q,n,a_pad,kmax", SHAPES)
+def test_chunks_tile_the_data_and_leave_room_for_k(q, n, a_pad, kmax):
+    plan, items = plan_and_items(q, n, a_pad, kmax)
+    by_chunk = {}
+    for _, _, _, chunk, tb, te, _, _ in items:
+        by_chunk.setdefault(int(chunk), set()).add((int(tb), int(te)))
+    assert all(len(v) == 1 for v in by_chunk.values())          # a chunk has one tile range
+    ranges = sorted(next(iter(v)) for v in by_chunk.values())
+    assert ranges[0][0] == 0 and ranges[-1][1] == plan["n_tiles"]
+    assert all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))  # contiguous, no overlap
+    # every chunk keeps 32 keys per query; the certified survivor set is about 1.6 k
+    if plan["n_tiles"] >= (kmax + 7) // 8:
+        assert plan["chunks"] * plan["kp"] >= 2 * min(kmax, n) or plan["chunks"] == plan["n_tiles"]
+
+
+@pytest.mark.parametrize("q,n,a_pad,kmax", SHAPES)
+def test_realignment_groups_are_co_resident(q, n, a_pad, kmax):
+    """Clusters that wait for each other on a (group, chunk) counter must be distinct clusters
+    working on the group in the same position of their item lists, otherwise the wait of the
+    pair kernel could never complete."""
+    plan, items = plan_and_items(q, n, a_pad, kmax)
+    if plan["cluster"] != 2:
+        return
+    nclusters = plan["grid"] // 2
+    lead = items[items[:, 1] == 0]
+    pos, nxt = {}, {}
+    for cl, _, m, chunk, _, _, group, rows in lead:
+        i = nxt.get(int(cl), 0)
+        nxt[int(cl)] = i + 1
+        pos.setdefault((int(group), int(chunk)), []).append((int(cl), i, int(rows)))
+    whole_wave = plan["group_m"] // 2 * plan["chunks"] * 2 == plan["grid"]
+    for (group, chunk), members in pos.items():
+        cls = [c for c, _, _ in members]
+        assert len(set(cls)) == len(cls) <= nclusters
+        assert all(r == len(members) for _, _, r in members)      # the counter's target is the member count
+        if whole_wave:
+            assert len({i for _, i, _ in members}) == 1            # same wave for all of them
+
+
+def test_wide_tile_only_for_long_rows(monkeypatch):
+    # (the switch itself is internal; what is visible is that both plans cover the work)
+    for a_pad in (2048, 4096, 8192):
+        plan, items = plan_and_items(4096, 8192, a_pad, 16)
+        assert plan["cluster"] == 2 and len(items) > 0
+
+
+def test_env_overrides_are_respected(monkeypatch):
+    monkeypatch.setenv("DMLP_TOPK_CHUNKS", "4")
+    monkeypatch.setenv("DMLP_TOPK_GMC", "18")
+    plan, items = plan_and_items(65536, 65536, 8192, 16)
+    assert plan["chunks"] == 4 and plan["group_m"] == 36 and plan["grid"] == 144
+    monkeypatch.delenv("DMLP_TOPK_CHUNKS")
+    monkeypatch.delenv("DMLP_TOPK_GMC")
+    plan, _ = plan_and_items(65536, 65536, 8192, 16)
+    assert plan["chunks"] == 2 and plan["group_m"] == 74 and plan["grid"] == 148
