@@ -94,6 +94,47 @@ def test_dist_topk_against_torch(K, q, n, a):
             assert (np.diff(sc[r, got]) >= -1e-5 * mag).all()  # emitted ascending
 
 
+@pytest.mark.parametrize("q,n,a,chunks,gmc,sync", [(600, 5000, 64, 3, 2, 0), (300, 5000, 256, 2, 1, 0),
+                                                   (1000, 9000, 128, 5, 2, 0), (257, 777, 128, 0, 0, 0),
+                                                   (1000, 5000, 1024, 3, 2, 1), (1000, 5000, 1024, 3, 2, 3)])
+def test_dist_topk_wide_tile_equals_narrow(K, q, n, a, chunks, gmc, sync, monkeypatch):
+    """The wide (256 x 512 per pair) kernel must produce the very lists of the narrow one.
+    The forced decompositions give chunks of 6/7/7, 10/10 and 7/7/7/7/8 tiles (odd counts end
+    with a step that fills one accumulator only) and several items per cluster (the
+    accumulator bookkeeping carries over from item to item)."""
+    if chunks:
+        monkeypatch.setenv("DMLP_TOPK_CHUNKS", str(chunks))
+        monkeypatch.setenv("DMLP_TOPK_GMC", str(gmc))
+    if sync:  # re-alignment of the pairs that sweep a chunk, every `sync` tiles (both kernels)
+        monkeypatch.setenv("DMLP_TOPK_SYNC", str(sync))
+    data, _, queries, _ = cpu.synth(n, q, a, -100.0, 100.0, 1, 1, 2, seed=11)
+    x, qq = _dev(data), _dev(queries)
+    st = K.new_stats()
+    K.stats_update(x, st)
+    K.stats_update(qq, st)
+    xh, xn, _ = K.pack(x, st, st)
+    qh, _, _ = K.pack(qq, st)
+    got = {}
+    for wide in ("0", "1"):
+        monkeypatch.setenv("DMLP_TOPK_WIDE", wide)
+        got[wide] = K.dist_topk(qh, xh, xn).clone()
+        torch.cuda.synchronize()
+    assert got["0"].shape == got["1"].shape and torch.equal(got["0"], got["1"])
+
+
+def test_knn_local_long_rows_take_the_wide_tile(K):
+    # 4096 values per row: the planner picks the wide tile by itself
+    n, q, a, kmax = 3000, 520, 4096, 12
+    data, labels, queries, k = cpu.synth(n, q, a, -100.0, 100.0, 3, kmax, 5, seed=21)
+    want_label, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    od, oi, ol, flags, nflag = K.knn_local(_dev(queries), _dev(k), _dev(data), _dev(labels), kmax)
+    label, checksum = K.finalize(od[None], oi[None], ol[None], _dev(k))[:2]
+    torch.cuda.synchronize()
+    assert int(nflag.item()) == 0
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+    assert (label.cpu().numpy() == want_label).all()
+
+
 @pytest.mark.parametrize("n,q,a,kmin,kmax,lo,hi", [
     (5000, 300, 64, 1, 16, -100.0, 100.0), (2049, 257, 33, 3, 24, 0.0, 10.0), (900, 129, 7, 1, 5, -1.0, 1.0),
     (40000, 256, 128, 16, 16, -100.0, 100.0), (300, 130, 256, 1, 8, 0.0, 1000.0),
