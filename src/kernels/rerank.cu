@@ -26,6 +26,8 @@
 // Flagged queries are re-run by the caller on the exact path (exact.cu).
 #include <limits>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -278,6 +280,88 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_kernel(const Rerank
   if (lane < cnt) sc.pair_dist[p0 + lane] = acc;
 }
 
+// Variant that stages every distinct query row once.  The dense pair list keeps a query's
+// pairs together, so the 32 pairs of a warp belong to a few queries only (about two at
+// k ~ 10); the ring then needs 32 data rows + XQ query rows per stage instead of 64 rows:
+// less shared memory per warp (10 instead of 6 resident warps per SM), fewer staging
+// instructions and 40 % less L2 -> SM traffic.  A warp whose pairs span more than XQ queries
+// (tiny k) handles them XQ queries at a time.  Measured on the headline shape inside a step:
+// 17.3 -> 11.4 ms (profiles/sweep_rerank_dedup_r1.log).
+constexpr int XQ = 8;
+constexpr int XD_ROWS = 32 + XQ;
+constexpr int XD_STAGE = XD_ROWS * XSTR;
+constexpr int XD_SMEM = X_WARPS * 2 * XD_STAGE * 8;
+
+__global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const RerankArgs a, const Scratch sc) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned count = *sc.counter;
+  const long long total = count < sc.capacity ? static_cast<long long>(count) : sc.capacity;
+  const long long p0 = (static_cast<long long>(blockIdx.x) * X_WARPS + warp) * 32;
+  if (p0 >= total) return;
+  const int cnt = (total - p0) < 32 ? static_cast<int>(total - p0) : 32;
+  double *ring = reinterpret_cast<double *>(rr_smem) + static_cast<size_t>(warp) * 2 * XD_STAGE;
+  const bool have = lane < cnt;
+  const int my_qi = have ? sc.pair_q[p0 + lane] : -1;
+  const long long my_x = have ? static_cast<long long>(sc.pair_id[p0 + lane]) * a.a : 0;
+  // runs of equal query index -> slot number of this lane's query, and the lane that starts each run
+  const int prev_qi = __shfl_up_sync(0xFFFFFFFFu, my_qi, 1);
+  const unsigned starts = __ballot_sync(0xFFFFFFFFu, have && (lane == 0 || my_qi != prev_qi));
+  const int slot = __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1;
+  const int distinct = __popc(starts);
+  // lane s (< distinct) holds the row offset of the query of slot s
+  const int start_lane = lane < distinct ? static_cast<int>(__fns(starts, 0, lane + 1)) : 0;
+  const long long slot_q = static_cast<long long>(__shfl_sync(0xFFFFFFFFu, my_qi, start_lane)) * a.a;
+  const int nchunks = (a.a + XC - 1) / XC;
+  const int sub = lane >> 4, seg = lane & 15;  // 16 lanes x 16 B cover one 32-column row segment
+
+  double acc = 0.0;
+  for (int base = 0; base < distinct; base += XQ) {
+    const bool active = have && slot >= base && slot < base + XQ;
+    const unsigned amask = __ballot_sync(0xFFFFFFFFu, active);
+    const int nq = min(XQ, distinct - base);
+    auto issue = [&](int chunk) {
+      if (chunk < nchunks) {
+        double *stage = ring + (chunk & 1) * XD_STAGE;
+        const int col = chunk * XC + seg * 2;
+        const bool in = col + 2 <= a.a;
+        for (int r0 = 0; r0 < cnt; r0 += 2) {  // data rows of the lanes handled in this pass
+          const int r = r0 + sub;
+          const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r < cnt ? r : 0);
+          if (r < cnt && ((amask >> r) & 1u))
+            cp_async_zfill<16>(stage + r * XSTR + seg * 2, a.x_attrs + xo + (in ? col : 0), in);
+        }
+        for (int s0 = 0; s0 < nq; s0 += 2) {   // one copy of each query row
+          const int sl = s0 + sub;
+          const long long qo = __shfl_sync(0xFFFFFFFFu, slot_q, base + (sl < nq ? sl : 0));
+          if (sl < nq) cp_async_zfill<16>(stage + (32 + sl) * XSTR + seg * 2, a.q_attrs + qo + (in ? col : 0), in);
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");  // always commit: keeps the group count uniform
+    };
+    issue(0);
+    for (int chunk = 0; chunk < nchunks; ++chunk) {
+      issue(chunk + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
+      if (active) {
+        const double *stage = ring + (chunk & 1) * XD_STAGE;
+        const double *xs = stage + lane * XSTR;
+        const double *qs = stage + (32 + slot - base) * XSTR;
+#pragma unroll 8
+        for (int i = 0; i < XC; ++i) {
+          const double d = __dsub_rn(qs[i], xs[i]);
+          acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
+        }
+      }
+      __syncwarp();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+  }
+  if (have) sc.pair_dist[p0 + lane] = acc;
+}
+
 // -------------------------------------------------------------------- emit
 __global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc) {
   __shared__ double s_dist[RR_THREADS / 32][WMAX];
@@ -374,7 +458,14 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
   const unsigned blocks = static_cast<unsigned>((sc.capacity + 32 * X_WARPS - 1) / (32 * X_WARPS));
   const bool vec2 = (args.a % 2 == 0) && (reinterpret_cast<uintptr_t>(args.q_attrs) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(args.x_attrs) % 16 == 0);
-  if (vec2) {
+  static const bool dedup = []() {
+    const char *e = getenv("DMLP_RERANK_DEDUP");  // 0: stage a query row per pair (the first version)
+    return e == nullptr || atoi(e) != 0;
+  }();
+  if (vec2 && dedup) {
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, XD_SMEM));
+    rerank_exact_dedup_kernel<<<blocks, X_WARPS * 32, XD_SMEM, s>>>(args, sc);
+  } else if (vec2) {
     DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, X_SMEM));
     rerank_exact_kernel<true><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);
   } else {
