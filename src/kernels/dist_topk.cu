@@ -21,6 +21,15 @@
 // sweep; each (query, chunk) pair emits its `kp` best (score, row) keys sorted
 // ascending.  Rows a chunk dropped all score >= the last key it kept, which is
 // what rerank.cu needs to certify the filter.
+//
+// Three kernels share the epilogue: dist_topk_kernel (one CTA per 128 x 256 tile,
+// used when there is a single row block), dist_topk_pair_kernel<false> (CTA pair,
+// tcgen05 cta_group::2, 256 x 256 per pair and k-step, two accumulator stages so the
+// drain of one tile overlaps the MMAs of the next) and dist_topk_pair_kernel<true>
+// (the "wide" tile for long rows: one query tile against two data tiles per k-block,
+// 256 x 512 per pair, both accumulator stages filled side by side).  The pair kernels
+// also carry the communication warp of the fused all-gathers (K4, data rows) and the
+// per-tile re-alignment of the pairs that sweep the same chunk.
 #include <cstdlib>
 #include <limits>
 
