@@ -64,6 +64,25 @@ class KNNClassifier:
         self.labels = _as_device(labels, torch.int32, self.device)
         return self
 
+    def update(self, ids, new_attrs, new_labels=None):
+        """Apply update records to the resident points: row ids[i] gets new_attrs[i] (and
+        new_labels[i]).  The reference declares this record (`Update{id, new_attrs}`,
+        common.h:35-38, with its parser common.cpp:46-55) but never applies one; here it is
+        a device-side row replacement, and the next classify() sees the new points."""
+        if self.data is None:
+            raise RuntimeError("update() before fit()")
+        idx = _as_device(np.atleast_1d(np.asarray(ids, dtype=np.int64)), torch.int64, self.device)
+        rows = _as_device(new_attrs, torch.float64, self.device).reshape(idx.numel(), -1)
+        if rows.shape[1] != self.data.shape[1]:
+            raise ValueError(f"update rows have {rows.shape[1]} attributes, the dataset has {self.data.shape[1]}")
+        if idx.numel() and (int(idx.min()) < 0 or int(idx.max()) >= self.data.shape[0]):
+            raise IndexError("update id out of range")
+        self.data.index_copy_(0, idx, rows)
+        if new_labels is not None:
+            lab = _as_device(np.atleast_1d(np.asarray(new_labels, dtype=np.int32)), torch.int32, self.device)
+            self.labels.index_copy_(0, idx, lab)
+        return self
+
     def classify(self, queries, k, kmax=None, id_base=0):
         """Classify `queries` ([q, a]) asking k[i] neighbours each."""
         with torch.cuda.device(self.device):

@@ -212,6 +212,27 @@ def test_model_api_all_paths(K):
     assert (knn(data, labels, queries, big_k).checksums_u64() == want_sum).all()
 
 
+def test_model_update_records(K):
+    """Update{id, new_attrs} (reference: common.h:35-38, parse_update common.cpp:46-55) applied
+    to the resident dataset: point 17 moves onto query 5 and becomes its nearest neighbour."""
+    from dmlp_b200.models import KNNClassifier
+    data, labels, queries, k = cpu.synth(3000, 200, 32, -100.0, 100.0, 1, 12, 5, seed=31)
+    model = KNNClassifier(want_lists=True).fit(data, labels)
+    ident, vals = cpu.parse_update("17 " + " ".join(f"{v:.6f}" for v in queries[5]))
+    assert ident == 17 and (vals == queries[5]).all()
+    model.update(ident, vals, new_labels=4)
+    data2, labels2 = data.copy(), labels.copy()
+    data2[17], labels2[17] = vals, 4
+    _, want_sum, *_ = cpu.knn(data2, labels2, queries, k)
+    res = model.classify(queries, k)
+    assert (res.checksums_u64() == want_sum).all()
+    assert int(res.ids[5, 0]) == 17 and float(res.dist[5, 0]) == 0.0
+    with pytest.raises(IndexError):
+        model.update(3000, vals)
+    with pytest.raises(ValueError):
+        model.update(1, vals[:-1])
+
+
 def test_decimal6_wire_round_trip(K):
     data, *_ = cpu.synth(500, 1, 33, -100.0, 100.0, 1, 1, 2, seed=8)
     x = _dev(data)
