@@ -19,7 +19,6 @@ import os
 import re
 import shutil
 import subprocess
-import sys
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))

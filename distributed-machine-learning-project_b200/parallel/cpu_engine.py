@@ -4,7 +4,6 @@ ones.  It exists so the multi-process plumbing -- who loads what, who owns which
 queries, how lists travel -- is testable without GPUs, and it
 is the multi-process counterpart of the reference's MPI run."""
 import numpy as np
-import torch
 import torch.distributed as dist
 
 from ..ops import cpu

@@ -88,6 +88,8 @@ void dmlp_debug_rerank_w(int *w_out);
  * per item and CTA {cluster, cta rank, row block, chunk, first tile, end tile, wave group, cluster
  * rows in the group}.  Needs no GPU.  Returns the number of items (only max_items are stored). */
 int dmlp_debug_topk_items(int q, int n, int a_pad, int num_sms, int kmax, int *out, int max_items);
+/* 1 if the plan for this shape uses the wide (256 x 512 per CTA pair) tile. */
+int dmlp_debug_topk_wide(int q, int n, int a_pad, int num_sms, int kmax);
 /* Diagnostics: with DMLP_TOPK_PROF=1 in the environment the CTA-pair filter kernel records, per CTA,
  * {mma total, mma operand wait, mma accumulator wait, producer total, producer stage wait, producer
  * re-alignment wait, epilogue accumulator wait, epilogue total, epilogue norm staging, accumulator

@@ -82,6 +82,10 @@ int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[
   return 0;
 }
 
+int dmlp_debug_topk_wide(int q, int n, int a_pad, int num_sms, int kmax) {
+  return make_topk_plan(q, n, a_pad, 32, num_sms, kmax).wide;
+}
+
 int dmlp_debug_topk_items(int q, int n, int a_pad, int num_sms, int kmax, int *out, int max_items) {
   TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
   return enumerate_topk_items(p, out, max_items);

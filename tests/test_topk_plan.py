@@ -7,7 +7,6 @@ clusters that re-align on a (wave group, chunk) counter must all be resident at 
 same time.  dmlp_debug_topk_items replays the enumeration on the host.
 """
 import ctypes as C
-import os
 
 import numpy as np
 import pytest
@@ -111,10 +110,17 @@ def test_realignment_groups_are_co_resident(q, n, a_pad, kmax):
 
 
 def test_wide_tile_only_for_long_rows(monkeypatch):
-    # (the switch itself is internal; what is visible is that both plans cover the work)
-    for a_pad in (2048, 4096, 8192):
+    lib = _lib()
+    lib.dmlp_debug_topk_wide.argtypes = [C.c_int] * 5
+    for a_pad, want in ((64, 0), (2048, 0), (4096, 1), (8192, 1)):
+        assert lib.dmlp_debug_topk_wide(4096, 8192, a_pad, SMS, 16) == want
         plan, items = plan_and_items(4096, 8192, a_pad, 16)
         assert plan["cluster"] == 2 and len(items) > 0
+    assert lib.dmlp_debug_topk_wide(100, 8192, 8192, SMS, 16) == 0   # single row block: one-CTA kernel
+    monkeypatch.setenv("DMLP_TOPK_WIDE", "0")
+    assert lib.dmlp_debug_topk_wide(4096, 8192, 8192, SMS, 16) == 0
+    monkeypatch.setenv("DMLP_TOPK_WIDE", "1")
+    assert lib.dmlp_debug_topk_wide(4096, 8192, 64, SMS, 16) == 1
 
 
 def test_env_overrides_are_respected(monkeypatch):

@@ -14,7 +14,6 @@ other test before this one can stop it.
 """
 import ctypes as C
 
-import numpy as np
 import pytest
 import torch
 
