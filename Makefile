@@ -57,6 +57,19 @@ $(LIBDIR)/libdmlp_knn.so: $(KERNEL_O)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(SM_FLAGS) -shared $^ -o $@ -lcudart
 
+# ATen operator library (torch.ops.dmlp_b200.*): the same kernels behind PyTorch's dispatcher,
+# current stream and caching allocator.  Built against the torch of $(PYTHON).
+PYTHON    ?= python
+TORCH_DIR  = $(shell $(PYTHON) -c "import os, torch; print(os.path.dirname(torch.__file__))" 2>/dev/null)
+TORCH_ABI  = $(shell $(PYTHON) -c "import torch; print(int(torch._C._GLIBCXX_USE_CXX11_ABI))" 2>/dev/null)
+.PHONY: torchops
+torchops: $(LIBDIR)/libdmlp_torch.so
+$(LIBDIR)/libdmlp_torch.so: src/torch/ops.cpp include/dmlp_knn.h $(LIBDIR)/libdmlp_knn.so
+	$(CXX) -O2 -std=c++17 -fPIC -shared -Wall -D_GLIBCXX_USE_CXX11_ABI=$(TORCH_ABI) -Iinclude \
+	  -isystem $(TORCH_DIR)/include -isystem $(TORCH_DIR)/include/torch/csrc/api/include -isystem /usr/local/cuda/include \
+	  $< -o $@ -L$(LIBDIR) -ldmlp_knn -L$(TORCH_DIR)/lib -ltorch -ltorch_cpu -ltorch_cuda -lc10 -lc10_cuda \
+	  -Wl,-rpath,'$$ORIGIN' -Wl,-rpath,$(TORCH_DIR)/lib
+
 tools: tools/dmlp-gen
 tools/dmlp-gen: $(B)/tools/dmlp_gen.o $(B)/src/driver/io.o
 	$(CXX) -pthread $^ -o $@

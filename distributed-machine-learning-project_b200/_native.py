@@ -46,3 +46,16 @@ def cpu_lib():
 def knn_lib():
     """The CUDA library.  Raises if it is missing: GPU ops never fall back silently."""
     return _load("libdmlp_knn.so")
+
+
+def torch_ops():
+    """Load the ATen operator library (torch.ops.dmlp_b200.*) and return that namespace."""
+    import torch
+    if "torch_ops" not in _cache:
+        knn_lib()  # its dependency, from the same directory
+        path = os.path.join(LIB_DIR, "libdmlp_torch.so")
+        if not os.path.exists(path):
+            build((os.path.relpath(path, ROOT),))
+        torch.ops.load_library(path)
+        _cache["torch_ops"] = torch.ops.dmlp_b200
+    return _cache["torch_ops"]
