@@ -85,6 +85,8 @@ def main():
         args.gpus = world
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from dmlp_b200.utils.numa import bind_to_gpu_node
+    numa_node = bind_to_gpu_node(local_rank)   # pinned staging buffers next to the GPU (best effort)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -172,6 +174,7 @@ def main():
             "config": {"model": "knn synthetic hidden(num_attrs)=%d batch(num_queries)=%d per GPU" % (A, args.num_queries),
                        "global_batch": Q, "seq_len": A, "num_data_total": N, "queries_per_gpu": Q // world,
                        "weak_scaling_axis": args.scale,
+                       "host_numa_node": numa_node,
                        "k": [args.min_k, args.max_k],
                        "parallelism": "grid R=%d (data shards) x C=%d (query shards)" % (eng.R, eng.C),
                        "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed"

@@ -92,3 +92,25 @@ def test_run_bench_harness_flow(repo_root, tmp_path):
     assert "Output found in cache. Skipping..." in res.stdout
     for stale in ("outputs/test_1.err", "outputs/test_1.out", "inputs/input1.in"):
         os.remove(os.path.join(repo_root, stale))
+
+
+def test_numa_binding_helpers(tmp_path, monkeypatch):
+    """utils.numa: sysfs parsing on a fake tree; binding is best effort and never raises."""
+    from dmlp_b200.utils import numa
+    assert numa.parse_cpulist("0-3,8,10-11") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa.parse_cpulist("") == set() and numa.parse_cpulist("x-y") == set()
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("56-111\n")
+    assert numa.gpu_numa_node("00000000:1B:00.0", str(tmp_path)) == 1
+    assert numa.gpu_numa_node("0000:1b:00.0", str(tmp_path)) == 1
+    assert numa.gpu_numa_node("0000:2c:00.0", str(tmp_path)) is None
+    (dev / "numa_node").write_text("-1\n")
+    assert numa.gpu_numa_node("0000:1b:00.0", str(tmp_path)) is None
+    assert numa.node_cpus(1, str(tmp_path)) == set(range(56, 112))
+    assert numa.bind_to_gpu_node(0) is None           # off unless DMLP_NUMA_BIND=1
+    monkeypatch.setenv("DMLP_NUMA_BIND", "1")
+    assert numa.bind_to_gpu_node(0) is None           # no GPU here: nothing changes, nothing raises
