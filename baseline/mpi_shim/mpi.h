@@ -18,6 +18,7 @@
 
 #include <sys/socket.h>
 #include <sys/stat.h>
+#include <sys/time.h>
 #include <sys/types.h>
 #include <sys/un.h>
 #include <unistd.h>
@@ -96,6 +97,9 @@ inline int MPI_Init(int *, char ***) {
   ::unlink(mine.c_str());
   if (::bind(ls, reinterpret_cast<sockaddr *>(&addr), sizeof addr) < 0) shim_die("bind");
   if (::listen(ls, shim_size) < 0) shim_die("listen");
+  timeval patience{};  // a rank that never shows up must not hang the others for ever
+  patience.tv_sec = 180;
+  ::setsockopt(ls, SOL_SOCKET, SO_RCVTIMEO, &patience, sizeof patience);
   for (int peer = 0; peer < shim_rank; ++peer) {
     sockaddr_un pa{};
     pa.sun_family = AF_UNIX;

@@ -45,11 +45,13 @@ def ensure_reference():
     newest_src = max(os.path.getmtime(os.path.join(REF_SRC, f)) for f in ("engine.cpp", "common.cpp"))
     if not os.path.exists(REF_BIN) or os.path.getmtime(REF_BIN) < newest_src:
         os.makedirs(os.path.dirname(REF_BIN), exist_ok=True)
+        tmp = REF_BIN + ".tmp%d" % os.getpid()
         cmd = ["g++", "-O3", "-I", os.path.join(ROOT, "baseline", "mpi_shim"), os.path.join(REF_SRC, "engine.cpp"),
-               os.path.join(REF_SRC, "common.cpp"), "-o", REF_BIN]
+               os.path.join(REF_SRC, "common.cpp"), "-o", tmp]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             return "reference does not compile here: " + res.stderr.strip().splitlines()[-1][:200]
+        os.replace(tmp, REF_BIN)   # other launched ranks may be waiting for the binary: appear atomically
     return None
 
 
@@ -70,27 +72,22 @@ def _run_ranks(args, world, rank, out, err):
     port = os.environ.get("MASTER_PORT", "0")
     sock_dir = os.path.join(tempfile.gettempdir(), "dmlp_mpi_%s" % port)
     os.makedirs(sock_dir, exist_ok=True)
-    ready = os.path.join(sock_dir, "ready")
     gen = os.path.join(ROOT, "tools", "dmlp-gen")
     if rank == 0:
         if err is None and not os.path.exists(gen):
             if subprocess.run(["make", "-C", ROOT, "tools"], capture_output=True, text=True).returncode != 0:
                 err = "input generator did not build"
-        with open(ready, "w") as f:           # tells the other launched processes whether to start a rank
-            f.write(err or "ok")
         if err:
+            # the other launched processes give up on their own: their rank finds no rank 0 to connect to
             out["unavailable"] = err
             print(json.dumps(out))
             return 0
     else:
         t0 = time.time()
-        while not os.path.exists(ready) or os.path.getsize(ready) == 0:
-            if time.time() - t0 > 600:
+        while not os.path.exists(REF_BIN):       # rank 0 may still be building it
+            if time.time() - t0 > 300:
                 return 0
-            time.sleep(0.05)
-        with open(ready) as f:
-            if f.read().strip() != "ok":
-                return 0
+            time.sleep(0.1)
     env = dict(os.environ, DMLP_MPI_DIR=sock_dir)
     n, a = args.num_data, args.num_attrs
     q = max(1, getattr(args, "ref_queries", 8)) * world      # weak scaling: the timed queries grow with the ranks
@@ -105,10 +102,6 @@ def _run_ranks(args, world, rank, out, err):
     _, stderr = rp.communicate()
     gp.wait()
     wall = time.time() - t0
-    try:
-        os.remove(ready)
-    except OSError:
-        pass
     m = re.search(r"Time taken:\s*([0-9]+)\s*ms", stderr or "")
     if rp.returncode != 0 or not m:
         out["unavailable"] = "reference run failed: " + (stderr or "").strip()[-200:]
