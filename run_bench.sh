@@ -9,9 +9,9 @@
 # What differs from the reference, and why:
 #   * no Slurm / mpirun: one process drives every visible GPU (DMLP_NGPU, DMLP_GRID);
 #   * baseline: benchmarks/bench_N need OpenMPI 4, which this image lacks, so the
-#     baseline is the unmodified reference engine.cpp built against a one-rank MPI
-#     stand-in (baseline/_ref_build/engine_ref, valid for constant k), else this
-#     repository's CPU oracle (DMLP_BACKEND=cpu ./engine);
+#     baseline is the unmodified reference engine.cpp built against the MPI stand-in
+#     (baseline/_ref_build/engine_ref, valid for constant k; REF_RANKS=4 runs it on four
+#     ranks, it aborts on 2 or 8), else this repository's CPU oracle (DMLP_BACKEND=cpu ./engine);
 #   * inputs: inputs.zip is not shipped; missing inputs/inputN.in are generated
 #     with tools/generate_input.py at the sizes below (override with INPUT_ARGS_N).
 set -u
@@ -82,7 +82,10 @@ run_config() {
     python3 tools/generate_input.py ${!args_var} --seed 42 --output "$inp" > /dev/null
   fi
   if [ -f "outputs/test_$n.err" ]; then echo "Output found in cache. Skipping..."
-  elif [ -x baseline/_ref_build/engine_ref ]; then baseline/_ref_build/engine_ref < "$inp" 2> "outputs/test_$n.err" > "outputs/test_$n.out"
+  elif [ -x baseline/_ref_build/engine_ref ]; then
+    # REF_RANKS=4 (or 9): the reference on several ranks through the stand-in launcher; its lines
+    # come out once per rank and iteration, hence the sort -u
+    tools/dmlp-mpirun -n "${REF_RANKS:-1}" baseline/_ref_build/engine_ref < "$inp" 2> "outputs/test_$n.err" | sort -u > "outputs/test_$n.out"
   else DMLP_BACKEND=cpu ./engine < "$inp" 2> "outputs/test_$n.err" > "outputs/test_$n.out"; fi
   DMLP_GRID=${DMLP_GRID:-$(grid_for "$n")} ./engine < "$inp" 2> outputs/tmp.err > outputs/tmp.out || cat outputs/tmp.err
   compare_times "outputs/test_$n.err" outputs/tmp.err
