@@ -83,15 +83,24 @@ int dmlp_cpu_local_lists(const double *data_attrs, const int *data_labels, int64
     std::vector<std::thread> pool;
     for (int t = 0; t < threads; ++t)
       pool.emplace_back([&, t] {
-        std::vector<dmlp::Neighbor> tmp(static_cast<size_t>(kmax > 0 ? kmax : 1));
-        for (int64_t i = q * t / threads; i < q * (t + 1) / threads; ++i) {
-          int k = query_k[i] < 0 ? 0 : (query_k[i] > kmax ? kmax : query_k[i]);
-          dmlp::local_topk(d, query_attrs + i * a, k, tmp.data());
+        const int64_t qb = q * t / threads, qe = q * (t + 1) / threads;
+        const size_t stride = static_cast<size_t>(kmax > 0 ? kmax : 1);
+        std::vector<dmlp::Neighbor> tmp(stride * static_cast<size_t>(qe - qb));
+        std::vector<dmlp::Neighbor *> outs(static_cast<size_t>(qe - qb));
+        std::vector<int> kk(static_cast<size_t>(qe - qb));
+        for (int64_t i = qb; i < qe; ++i) {
+          kk[size_t(i - qb)] = query_k[i] < 0 ? 0 : (query_k[i] > kmax ? kmax : query_k[i]);
+          outs[size_t(i - qb)] = tmp.data() + stride * size_t(i - qb);
+        }
+        dmlp::local_topk_many(d, query_attrs + qb * a, kk.data(), int(qe - qb), outs.data());
+        for (int64_t i = qb; i < qe; ++i) {
+          const int k = kk[size_t(i - qb)];
+          const dmlp::Neighbor *row = outs[size_t(i - qb)];
           for (int j = 0; j < kmax; ++j) {
             const bool real = j < k;
-            out_dist[i * kmax + j] = real ? tmp[size_t(j)].dist : dmlp::kSentinelDist;
-            out_id[i * kmax + j] = real ? tmp[size_t(j)].id : dmlp::kSentinelId;
-            out_label[i * kmax + j] = real ? tmp[size_t(j)].label : -1;
+            out_dist[i * kmax + j] = real ? row[j].dist : dmlp::kSentinelDist;
+            out_id[i * kmax + j] = real ? row[j].id : dmlp::kSentinelId;
+            out_label[i * kmax + j] = real ? row[j].label : -1;
           }
         }
       });

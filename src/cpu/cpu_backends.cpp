@@ -174,6 +174,89 @@ void local_topk(const DatasetView &data, const double *query, int k, Neighbor *o
   heap.finish();
 }
 
+namespace {
+
+constexpr int kPointGroup = 8;   // points per transposed group (one AVX-512 register of doubles)
+constexpr int kQueryBlock = 16;  // queries that share one pass over the data
+
+// Distances of queries to eight points held attribute-major (`pt[i * 8 + j]` = attribute i of
+// point j).  The eight points are the SIMD dimension, written with GCC vector types so that the
+// compiler cannot pick another one; every lane runs exact_sqdist's sequence (the file is
+// compiled with -ffp-contract=off: no fused multiply-add in any clone).  Four queries at a
+// time give four independent add chains per loaded point vector.
+typedef double v8d __attribute__((vector_size(64), aligned(8)));
+
+__attribute__((target_clones("avx512f", "avx2", "default")))
+void sqdist_group8(const double *q, const double *pt, int dim, double *out) {
+  v8d s = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < dim; ++i) {
+    const v8d p = *reinterpret_cast<const v8d *>(pt + static_cast<size_t>(i) * kPointGroup);
+    const v8d d = q[i] - p;
+    const v8d m = d * d;
+    s = s + m;
+  }
+  *reinterpret_cast<v8d *>(out) = s;
+}
+
+__attribute__((target_clones("avx512f", "avx2", "default")))
+void sqdist_group8_x4(const double *q0, const double *q1, const double *q2, const double *q3, const double *pt,
+                      int dim, double *out) {
+  v8d s0 = {0, 0, 0, 0, 0, 0, 0, 0}, s1 = s0, s2 = s0, s3 = s0;
+  for (int i = 0; i < dim; ++i) {
+    const v8d p = *reinterpret_cast<const v8d *>(pt + static_cast<size_t>(i) * kPointGroup);
+    const v8d d0 = q0[i] - p, d1 = q1[i] - p, d2 = q2[i] - p, d3 = q3[i] - p;
+    const v8d m0 = d0 * d0, m1 = d1 * d1, m2 = d2 * d2, m3 = d3 * d3;
+    s0 = s0 + m0;
+    s1 = s1 + m1;
+    s2 = s2 + m2;
+    s3 = s3 + m3;
+  }
+  v8d *o = reinterpret_cast<v8d *>(out);
+  o[0] = s0; o[1] = s1; o[2] = s2; o[3] = s3;
+}
+
+}  // namespace
+
+void local_topk_many(const DatasetView &data, const double *queries, const int *k, int nq, Neighbor *const *outs) {
+  const int a = data.a;
+  std::vector<double> pt(static_cast<size_t>(a > 0 ? a : 1) * kPointGroup);
+  std::vector<BoundedHeap> heaps;
+  for (int b = 0; b < nq; b += kQueryBlock) {
+    const int nb = std::min(kQueryBlock, nq - b);
+    heaps.clear();
+    for (int i = 0; i < nb; ++i) heaps.emplace_back(outs[b + i], clamp_k(k[b + i]));
+    int64_t r = 0;
+    for (; r + kPointGroup <= data.n; r += kPointGroup) {
+      const double *rows = data.attrs + r * a;
+      for (int j = 0; j < kPointGroup; ++j)
+        for (int i = 0; i < a; ++i) pt[static_cast<size_t>(i) * kPointGroup + j] = rows[static_cast<size_t>(j) * a + i];
+      int i = 0;
+      double d[4 * kPointGroup];
+      const double *qrow = queries + static_cast<size_t>(b) * a;
+      for (; i + 4 <= nb; i += 4) {
+        sqdist_group8_x4(qrow + static_cast<size_t>(i) * a, qrow + static_cast<size_t>(i + 1) * a,
+                         qrow + static_cast<size_t>(i + 2) * a, qrow + static_cast<size_t>(i + 3) * a, pt.data(), a, d);
+        for (int u = 0; u < 4; ++u)
+          for (int j = 0; j < kPointGroup; ++j)
+            heaps[static_cast<size_t>(i + u)].offer(
+                Neighbor{d[u * kPointGroup + j], data.id_base + static_cast<int>(r + j), data.labels[r + j]});
+      }
+      for (; i < nb; ++i) {
+        sqdist_group8(qrow + static_cast<size_t>(i) * a, pt.data(), a, d);
+        for (int j = 0; j < kPointGroup; ++j)
+          heaps[static_cast<size_t>(i)].offer(
+              Neighbor{d[j], data.id_base + static_cast<int>(r + j), data.labels[r + j]});
+      }
+    }
+    for (; r < data.n; ++r)
+      for (int i = 0; i < nb; ++i)
+        heaps[static_cast<size_t>(i)].offer(Neighbor{exact_sqdist(queries + static_cast<size_t>(b + i) * a,
+                                                                  data.attrs + r * a, a),
+                                                     data.id_base + static_cast<int>(r), data.labels[r]});
+    for (auto &h : heaps) h.finish();
+  }
+}
+
 void merge_topk(const Neighbor *x, const Neighbor *y, int k, Neighbor *out) {
   int i = 0, j = 0;
   for (int o = 0; o < k; ++o) {
@@ -206,14 +289,22 @@ void finalize_all(const QueryView &qv, const std::vector<int64_t> &off,
     finalize_query(lists.data() + off[i], static_cast<int>(off[i + 1] - off[i]), out);
 }
 
+namespace {
+// Lists of queries [b, e) into `lists` (CSR by `off`), through the blocked kernel.
+void topk_range(const DatasetView &data, const QueryView &qv, const std::vector<int64_t> &off, int64_t b, int64_t e,
+                Neighbor *lists) {
+  if (e <= b) return;
+  std::vector<Neighbor *> outs(static_cast<size_t>(e - b));
+  for (int64_t i = b; i < e; ++i) outs[static_cast<size_t>(i - b)] = lists + off[i];
+  local_topk_many(data, qv.attrs + b * qv.a, qv.k + b, static_cast<int>(e - b), outs.data());
+}
+}  // namespace
+
 // ---- strategy: serial / oracle -------------------------------------------
 void run_serial(const DatasetView &data, const QueryView &qv, int threads, ResultSet *out) {
   auto off = k_offsets(qv);
   std::vector<Neighbor> lists(static_cast<size_t>(off.back()));
-  parallel_for(qv.q, threads, [&](int64_t b, int64_t e, int) {
-    for (int64_t i = b; i < e; ++i)
-      local_topk(data, qv.attrs + i * qv.a, qv.k[i], lists.data() + off[i]);
-  });
+  parallel_for(qv.q, threads, [&](int64_t b, int64_t e, int) { topk_range(data, qv, off, b, e, lists.data()); });
   finalize_all(qv, off, lists, out);
 }
 
@@ -240,8 +331,7 @@ void run_grid(const DatasetView &data, const QueryView &qv, int rows, int cols, 
       ranks.emplace_back([&, r, c] {
         DatasetView shard = data_slice(data, dp.begin(r), dp.count(r));
         int64_t qb = qp.begin(c), qe = qb + qp.count(c);
-        for (int64_t i = qb; i < qe; ++i)
-          local_topk(shard, qv.attrs + i * qv.a, qv.k[i], mailbox[r].data() + off[i]);
+        topk_range(shard, qv, off, qb, qe, mailbox[r].data());
       });
   for (auto &t : ranks) t.join();
 
@@ -290,10 +380,10 @@ void run_farm(const DatasetView &data, const QueryView &qv, int workers, ResultS
   std::vector<std::thread> pool;
   for (int w = 0; w < workers; ++w)
     pool.emplace_back([&] {
-      for (;;) {
-        int64_t i = next.fetch_add(1, std::memory_order_relaxed);
+      for (;;) {  // a block of queries per request: they share one pass over the data
+        int64_t i = next.fetch_add(kQueryBlock, std::memory_order_relaxed);
         if (i >= qv.q) break;
-        local_topk(data, qv.attrs + i * qv.a, qv.k[i], lists.data() + off[i]);
+        topk_range(data, qv, off, i, std::min<int64_t>(i + kQueryBlock, qv.q), lists.data());
       }
     });
   for (auto &t : pool) t.join();
