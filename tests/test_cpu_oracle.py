@@ -173,3 +173,41 @@ def test_midsize_md5(tmp_path, repo_root):
     _, checksum, *_ = cpu.knn(data, labels, queries, k)
     lines = sorted(f"Query {i} checksum: {int(c)}\n" for i, c in enumerate(checksum))
     assert hashlib.md5("".join(lines).encode()).hexdigest() == "8cf1102ad3eb629255188098e0cfb4a1"
+
+
+def _numpy_lists(data, queries, k, kmax, id_base):
+    """Independent restatement of the spec: sequential fp64 sum per pair (vectorised over the
+    points only), order (distance ascending, larger id first), sentinel padding."""
+    q, n = queries.shape[0], data.shape[0]
+    dist = np.full((q, kmax), 1e18)
+    ids = np.full((q, kmax), -1, np.int32)
+    for i in range(q):
+        acc = np.zeros(n)
+        for c in range(data.shape[1]):
+            d = queries[i, c] - data[:, c]
+            acc = acc + d * d
+        order = np.lexsort((-np.arange(n), acc))[:k[i]]
+        dist[i, :len(order)] = acc[order]
+        ids[i, :len(order)] = order + id_base
+    return dist, ids
+
+
+@pytest.mark.parametrize("n,q,a,kmax,seed", [(37, 5, 3, 6, 0), (64, 16, 8, 4, 1), (203, 21, 17, 9, 2), (8, 1, 1, 8, 3),
+                                             (7, 19, 5, 3, 4), (1000, 33, 2, 12, 5), (129, 4, 64, 1, 6)])
+def test_blocked_simd_kernel_matches_a_numpy_restatement(n, q, a, kmax, seed):
+    """local_topk_many (eight points per SIMD register, 16 queries per pass, row counts that
+    are not multiples of either) against a numpy restatement; duplicated points force ties."""
+    rng = np.random.default_rng(seed)
+    data = np.round(rng.uniform(-3, 3, (n, a)), 2)
+    data[n // 2:] = data[:n - n // 2]          # duplicates: equal distances, the larger id must win
+    labels = rng.integers(0, 4, n).astype(np.int32)
+    queries = np.round(rng.uniform(-3, 3, (q, a)), 2)
+    k = rng.integers(1, kmax + 1, q).astype(np.int32)
+    k = np.minimum(k, n)
+    want_d, want_i = _numpy_lists(data, queries, k, kmax, 11)
+    for threads in (1, 3):
+        od, oi, ol = cpu.local_lists(data, labels, 11, queries, k, kmax, threads=threads)
+        assert np.array_equal(oi, want_i)
+        assert np.array_equal(od, want_d)      # bit for bit
+        real = oi >= 0
+        assert np.array_equal(ol[real], labels[oi[real] - 11])
