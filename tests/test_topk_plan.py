@@ -132,3 +132,31 @@ def test_env_overrides_are_respected(monkeypatch):
     monkeypatch.delenv("DMLP_TOPK_GMC")
     plan, _ = plan_and_items(65536, 65536, 8192, 16)
     assert plan["chunks"] == 2 and plan["group_m"] == 74 and plan["grid"] == 148
+
+
+def test_random_shapes_cover_the_work_exactly_once():
+    """300 random shapes (and SM counts: the planner is also used with fewer SMs, e.g. MIG slices):
+    same invariants as above, including the co-residency of re-alignment groups."""
+    rng = np.random.default_rng(2024)
+    for _ in range(300):
+        q = int(rng.choice([rng.integers(1, 300), rng.integers(300, 5000), rng.integers(5000, 70000)]))
+        n = int(rng.choice([rng.integers(1, 600), rng.integers(600, 20000), rng.integers(20000, 300000)]))
+        a_pad = 64 * int(rng.integers(1, 130))
+        kmax = int(rng.choice([1, 5, 16, 40, 96]))
+        sms = int(rng.choice([148, 148, 132, 64, 16, 2, 1]))
+        plan, items = plan_and_items(q, n, a_pad, kmax, sms)
+        mb, nt, chunks, cluster = plan["m_blocks"], plan["n_tiles"], plan["chunks"], plan["cluster"]
+        assert 1 <= plan["grid"] <= max(sms, cluster) and plan["grid"] % cluster == 0, (q, n, a_pad, kmax, sms, plan)
+        seen = np.zeros((mb, nt), dtype=np.int32)
+        lists = np.zeros((mb, chunks), dtype=np.int32)
+        groups = {}
+        for cl, rank, m, chunk, tb, te, group, rows in items:
+            if rank == 0:
+                groups.setdefault((int(group), int(chunk)), []).append((int(cl), int(rows)))
+            if m < mb:
+                seen[m, tb:te] += 1
+                lists[m, chunk] += 1
+        assert (seen == 1).all() and (lists == 1).all(), (q, n, a_pad, kmax, sms, plan)
+        for members in groups.values():
+            cls = [c for c, _ in members]
+            assert len(set(cls)) == len(cls) and all(r == len(members) for _, r in members), (q, n, a_pad, kmax, sms)
