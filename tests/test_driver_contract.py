@@ -114,3 +114,22 @@ def test_numa_binding_helpers(tmp_path, monkeypatch):
     assert numa.bind_to_gpu_node(0) is None           # off unless DMLP_NUMA_BIND=1
     monkeypatch.setenv("DMLP_NUMA_BIND", "1")
     assert numa.bind_to_gpu_node(0) is None           # no GPU here: nothing changes, nothing raises
+
+
+def test_python_module_cli_keeps_the_driver_contract(tmp_path, repo_root):
+    """`python -m dmlp_b200 < input` prints what ./engine (and, with --debug, ./engine.debug) prints."""
+    inp = tmp_path / "in.txt"
+    subprocess.run([sys.executable, os.path.join(repo_root, "tools", "generate_input.py"), "--num_data", "400", "--num_queries", "30",
+                    "--num_attrs", "6", "--min", "-5", "--max", "5", "--minK", "1", "--maxK", "7", "--num_labels", "3",
+                    "--output", str(inp)], check=True, capture_output=True)
+    env = dict(os.environ, PYTHONPATH=str(repo_root), DMLP_BACKEND="cpu")
+    text = inp.read_bytes()
+    for flag, binary in (([], "engine"), (["--debug"], "engine.debug")):
+        py = subprocess.run([sys.executable, "-m", "dmlp_b200", "--backend", "cpu"] + flag, input=text,
+                            capture_output=True, env=env, check=True)
+        ref = subprocess.run([os.path.join(repo_root, binary)], input=text, capture_output=True, env=env, check=True)
+        assert py.stdout == ref.stdout and len(py.stdout) > 0
+        assert b"Time taken:" in py.stderr
+    grid = subprocess.run([sys.executable, "-m", "dmlp_b200", "--backend", "cpu", "--strategy", "grid", "--ranks", "6"],
+                          input=text, capture_output=True, env=env, check=True)
+    assert grid.stdout == subprocess.run([os.path.join(repo_root, "engine")], input=text, capture_output=True, env=env).stdout
