@@ -116,7 +116,7 @@ def test_numa_binding_helpers(tmp_path, monkeypatch):
     assert numa.bind_to_gpu_node(0) is None           # no GPU here: nothing changes, nothing raises
 
 
-def test_python_module_cli_keeps_the_driver_contract(tmp_path, repo_root):
+def test_python_module_cli_keeps_the_driver_contract(tmp_path, repo_root, engine_bins):
     """`python -m dmlp_b200 < input` prints what ./engine (and, with --debug, ./engine.debug) prints."""
     inp = tmp_path / "in.txt"
     subprocess.run([sys.executable, os.path.join(repo_root, "tools", "generate_input.py"), "--num_data", "400", "--num_queries", "30",
