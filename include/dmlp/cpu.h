@@ -50,8 +50,8 @@ void local_topk(const DatasetView &data, const double *query, int k, Neighbor *o
 
 /// The same for `nq` queries at once (rows `queries + i * data.a`, lists `outs[i]` of `k[i]`
 /// entries): data rows are visited in groups of eight, transposed so that one SIMD register
-/// holds the same attribute of eight points, and every group is used by all queries of the
-/// block before the next one is touched.  Each (query, point) pair still sees the exact
+/// holds the same attribute of eight points, and every group is used by all queries of a
+/// block (64) before the next one is touched.  Each (query, point) pair still sees the exact
 /// sequential sub / mul / add sequence of exact_sqdist, so the lists are bit-identical to
 /// local_topk's; the dataset is streamed once per block instead of once per query.
 void local_topk_many(const DatasetView &data, const double *queries, const int *k, int nq, Neighbor *const *outs);

@@ -177,7 +177,7 @@ void local_topk(const DatasetView &data, const double *query, int k, Neighbor *o
 namespace {
 
 constexpr int kPointGroup = 8;   // points per transposed group (one AVX-512 register of doubles)
-constexpr int kQueryBlock = 16;  // queries that share one pass over the data
+constexpr int kQueryBlock = 64;  // queries that share one pass over the data
 
 // Distances of queries to eight points held attribute-major (`pt[i * 8 + j]` = attribute i of
 // point j).  The eight points are the SIMD dimension, written with GCC vector types so that the
@@ -236,10 +236,14 @@ void local_topk_many(const DatasetView &data, const double *queries, const int *
       for (; i + 4 <= nb; i += 4) {
         sqdist_group8_x4(qrow + static_cast<size_t>(i) * a, qrow + static_cast<size_t>(i + 1) * a,
                          qrow + static_cast<size_t>(i + 2) * a, qrow + static_cast<size_t>(i + 3) * a, pt.data(), a, d);
-        for (int u = 0; u < 4; ++u)
-          for (int j = 0; j < kPointGroup; ++j)
-            heaps[static_cast<size_t>(i + u)].offer(
-                Neighbor{d[u * kPointGroup + j], data.id_base + static_cast<int>(r + j), data.labels[r + j]});
+        for (int u = 0; u < 4; ++u) {
+          BoundedHeap &h = heaps[static_cast<size_t>(i + u)];
+          for (int j = 0; j < kPointGroup; ++j) {
+            const double dj = d[u * kPointGroup + j];
+            if (h.full() && dj > h.worst().dist) continue;  // (an equal distance can still win on the id)
+            h.offer(Neighbor{dj, data.id_base + static_cast<int>(r + j), data.labels[r + j]});
+          }
+        }
       }
       for (; i < nb; ++i) {
         sqdist_group8(qrow + static_cast<size_t>(i) * a, pt.data(), a, d);
@@ -377,13 +381,15 @@ void run_farm(const DatasetView &data, const QueryView &qv, int workers, ResultS
   std::vector<Neighbor> lists(static_cast<size_t>(off.back()));
   std::atomic<int64_t> next{0};
   if (workers < 1) workers = 1;
+  // requests small enough to balance (about four per worker), large enough to share data passes
+  const int64_t grain = std::max<int64_t>(1, std::min<int64_t>(kQueryBlock, qv.q / (4 * int64_t(workers))));
   std::vector<std::thread> pool;
   for (int w = 0; w < workers; ++w)
     pool.emplace_back([&] {
       for (;;) {  // a block of queries per request: they share one pass over the data
-        int64_t i = next.fetch_add(kQueryBlock, std::memory_order_relaxed);
+        int64_t i = next.fetch_add(grain, std::memory_order_relaxed);
         if (i >= qv.q) break;
-        topk_range(data, qv, off, i, std::min<int64_t>(i + kQueryBlock, qv.q), lists.data());
+        topk_range(data, qv, off, i, std::min<int64_t>(i + grain, qv.q), lists.data());
       }
     });
   for (auto &t : pool) t.join();
