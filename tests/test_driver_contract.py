@@ -90,6 +90,12 @@ def test_run_bench_harness_flow(repo_root, tmp_path):
     assert "=== Performance Comparison ===" in res.stdout and "Results:        identical (40 queries)" in res.stdout
     res = subprocess.run([sh, "1"], capture_output=True, text=True, env=env)
     assert "Output found in cache. Skipping..." in res.stdout
+    if os.path.exists(os.path.join(repo_root, "baseline", "_ref_build", "engine_ref")):
+        # the baseline on four ranks of the MPI stand-in (its 2 x 2 grid): same results again
+        for stale in ("outputs/test_1.err", "outputs/test_1.out"):
+            os.remove(os.path.join(repo_root, stale))
+        res = subprocess.run([sh, "1"], capture_output=True, text=True, env=dict(env, REF_RANKS="4"))
+        assert res.returncode == 0 and "Results:        identical (40 queries)" in res.stdout, res.stdout + res.stderr
     for stale in ("outputs/test_1.err", "outputs/test_1.out", "inputs/input1.in"):
         os.remove(os.path.join(repo_root, stale))
 
