@@ -96,6 +96,12 @@ int dmlp_debug_topk_wide(int q, int n, int a_pad, int num_sms, int kmax);
  * loads, scoring and appends, list compaction, list flush, 3 unused} in SM cycles; this copies the
  * counters of the last launch to host memory (16 values per CTA) and returns the number of CTAs. */
 int dmlp_debug_topk_prof(unsigned long long *host_out, int max_ctas);
+/* Watchdog of the filter kernel's re-alignment points (CTA pairs that sweep the same data
+ * tiles wait for each other so the tiles are shared through L2): a wait that gives up after
+ * 2e9 cycles is counted on the device; this reads the count (0 in a healthy run; results are
+ * correct either way).  Every dmlp_dist_topk* launch takes its own slice of the per-device
+ * counter array, so launches may overlap on different streams. */
+int dmlp_topk_sync_timeouts(unsigned *out);
 
 /* ---- exact fp64 brute force (reference: engine.cpp:233-257 as written) --------
  * Processes `count` queries: rows query_rows[0..count) or, with NULL, rows

@@ -240,7 +240,7 @@ void local_topk_many(const DatasetView &data, const double *queries, const int *
           BoundedHeap &h = heaps[static_cast<size_t>(i + u)];
           for (int j = 0; j < kPointGroup; ++j) {
             const double dj = d[u * kPointGroup + j];
-            if (h.full() && dj > h.worst().dist) continue;  // (an equal distance can still win on the id)
+            if (h.cap == 0 || (h.full() && dj > h.worst().dist)) continue;  // (an equal distance can still win on the id)
             h.offer(Neighbor{dj, data.id_base + static_cast<int>(r + j), data.labels[r + j]});
           }
         }

@@ -30,6 +30,7 @@
 // 256 x 512 per pair, both accumulator stages filled side by side).  The pair kernels
 // also carry the communication warp of the fused all-gathers (K4, data rows) and the
 // per-tile re-alignment of the pairs that sweep the same chunk.
+#include <atomic>
 #include <cstdlib>
 #include <limits>
 
@@ -52,6 +53,11 @@ constexpr int CAP = 64;   // list capacity between compactions
 constexpr int THREADS = 192;
 constexpr int EPI_THREADS = 128;
 
+
+// Re-alignment waits that gave up (see dist_topk_sync_timeouts): results stay correct, the
+// sweep only loses its L2 sharing, but a non-zero count means launches overlapped on one
+// slice of the counters or a CTA pair never arrived.
+__device__ unsigned g_sync_timeouts = 0;
 
 struct Item {
   int m;
@@ -809,7 +815,10 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
               const unsigned target = static_cast<unsigned>(it.group_rows) * sync_epoch;
               const long long t0 = clock64();
               while (static_cast<int>(ld_acquire_gpu(cnt) - target) < 0) {
-                if (clock64() - t0 > 2000000000LL) break;  // never hang on a lost peer
+                if (clock64() - t0 > 2000000000LL) {  // never hang on a lost peer, but say so
+                  atomicAdd(&g_sync_timeouts, 1u);
+                  break;
+                }
               }
               if (plan.prof) pw_sync += clock64() - t0;
             }
@@ -1069,8 +1078,13 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
 }
 
 namespace {
+// Re-alignment counters: one file-scope array per device, handed out in slices.  Every launch
+// takes the next `need` words (a host-side cursor that wraps), so launches that overlap on
+// different streams count on different words; only more than kSyncCounters words' worth of
+// launches in flight at once could meet on the same slice.
 constexpr int kSyncCounters = 16384;
 __device__ unsigned g_sync_counters[kSyncCounters];
+std::atomic<unsigned long long> g_sync_cursor{0};
 constexpr int kProfCtas = 256;
 __device__ unsigned long long g_prof[kProfCtas * 16];
 int g_prof_ctas = 0;
@@ -1096,6 +1110,11 @@ int enumerate_topk_items(const TopkPlan &plan, int *out, int max_items) {
   return n;
 }
 
+int dist_topk_sync_timeouts(unsigned *out) {
+  DMLP_CUDA_OK(cudaMemcpyFromSymbol(out, g_sync_timeouts, sizeof(unsigned)));
+  return 0;
+}
+
 int dist_topk_prof_read(unsigned long long *host_out, int max_ctas) {
   const int n = g_prof_ctas < max_ctas ? g_prof_ctas : max_ctas;
   if (n <= 0) return 0;
@@ -1119,8 +1138,16 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
     if (plan.sync && whole_wave && need <= kSyncCounters) {
       void *p = nullptr;
       DMLP_CUDA_OK(cudaGetSymbolAddress(&p, g_sync_counters));
-      DMLP_CUDA_OK(cudaMemsetAsync(p, 0, sizeof(unsigned) * need, s));
-      plan.sync_cnt = static_cast<unsigned *>(p);
+      // claim a slice [off, off + need) that does not straddle the end of the array
+      unsigned long long cur = g_sync_cursor.load(), off, next;
+      do {
+        off = cur % kSyncCounters;
+        if (off + need > kSyncCounters) off = 0;
+        next = off + need;
+      } while (!g_sync_cursor.compare_exchange_weak(cur, next));
+      unsigned *slice = static_cast<unsigned *>(p) + off;
+      DMLP_CUDA_OK(cudaMemsetAsync(slice, 0, sizeof(unsigned) * need, s));
+      plan.sync_cnt = slice;
     } else {
       plan.sync = 0;
     }

@@ -146,6 +146,9 @@ int enumerate_topk_items(const TopkPlan &plan, int *out, int max_items);
 ///  accumulator, epilogue total, epilogue norm staging, accumulator loads, scoring and appends,
 ///  list compaction, list flush, 3 unused} in SM cycles (16 values per CTA).  Returns the number of CTAs written.
 int dist_topk_prof_read(unsigned long long *host_out, int max_ctas);
+/// Number of re-alignment waits that timed out on the current device since the library was
+/// loaded (synchronises the device).  0 in a healthy run.
+int dist_topk_sync_timeouts(unsigned *out);
 
 // rerank.cu
 struct RerankArgs {

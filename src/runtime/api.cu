@@ -210,6 +210,7 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
 
 void dmlp_debug_rerank_w(int *w_out) { set_rerank_debug_w(w_out); }
 int dmlp_debug_topk_prof(unsigned long long *host_out, int max_ctas) { return dist_topk_prof_read(host_out, max_ctas); }
+int dmlp_topk_sync_timeouts(unsigned *out) { return dist_topk_sync_timeouts(out); }
 
 size_t dmlp_rerank_workspace_bytes(int q, int kmax) { return rerank_workspace_bytes(q, kmax); }
 
@@ -250,6 +251,17 @@ int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k,
 
 // ---- whole local pipeline ------------------------------------------------------
 namespace {
+// An empty shard has no neighbours to offer: every list is padding, no query is flagged.
+__global__ void __launch_bounds__(256) fill_empty_lists_kernel(double *dist, int *id, int *label, int *flags,
+                                                               long long slots, int q) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < slots; i += stride) {
+    dist[i] = 1e18;
+    id[i] = -1;
+    label[i] = -1;
+    if (i < q) flags[i] = 0;
+  }
+}
 struct LocalLayout {
   size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, rerank, rerank_bytes, total;
   int a_pad, chunks;
@@ -285,6 +297,7 @@ size_t dmlp_knn_local_workspace_bytes(int q, int n, int a, int num_sms, int kmax
 int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_attrs, const int *x_labels, int n,
                    int a, int id_base, int kmax, const void *range, void *workspace, size_t workspace_bytes,
                    double *out_dist, int *out_id, int *out_label, int *flags, int *num_flagged, void *stream) {
+  DMLP_REQUIRE(q >= 0 && n >= 0 && a >= 0 && kmax >= 1, "knn_local: negative size or kmax < 1");
   int sms = 0;
   if (int rc = current_sm_count(&sms)) return rc;
   LocalLayout L = local_layout(q, n, a, sms, kmax);
@@ -292,6 +305,17 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   DMLP_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "knn_local: workspace must be 256-byte aligned");
   unsigned char *w = static_cast<unsigned char *>(workspace);
   cudaStream_t s = st(stream);
+  if (num_flagged) DMLP_CUDA_OK(cudaMemsetAsync(num_flagged, 0, sizeof(int), s));
+  if (q <= 0) return 0;
+  if (n <= 0) {
+    // nothing to filter or re-rank (and the scratch may hold another call's candidates)
+    const long long slots = static_cast<long long>(q) * kmax;
+    long long blocks = (slots + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    fill_empty_lists_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(out_dist, out_id, out_label, flags, slots, q);
+    DMLP_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
   PackStats *stats = reinterpret_cast<PackStats *>(w + L.stats);
   PackStats *q_stats = reinterpret_cast<PackStats *>(w + L.q_stats);
   if (int rc = launch_stats_reset(stats, s)) return rc;
@@ -311,7 +335,6 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   if (int rc = launch_pack(q_attrs, q, a, L.a_pad, rng, qh, qn, qe, q_stats, s)) return rc;
   TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms, kmax);
   if (int rc = launch_dist_topk(qh, xh, xn, p, cand, nullptr, s)) return rc;
-  if (num_flagged) DMLP_CUDA_OK(cudaMemsetAsync(num_flagged, 0, sizeof(int), s));
   RerankArgs r;
   r.cand = cand; r.chunks = p.chunks; r.kp = 32;
   r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
