@@ -245,8 +245,11 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
  *  - Limit: problems whose dmlp_knn_local_workspace_bytes() exceeds
  *    DMLP_STATIC_SCRATCH_BYTES are refused (-3, message in dmlp_last_error()).
  *  - Every GPU that loads the library keeps the array reserved until exit.
- *  - The first call on each device looks up the array's device address; make
- *    that call at start-up, before any stream capture on that device.
+ *  - The first call in each CUDA context (by default: one per device; a host
+ *    application's own context counts separately) looks up that context's address
+ *    of the array; make that call at start-up, before any stream capture there.
+ *  - An empty data shard (n == 0) is answered with padding lists without touching
+ *    the scratch.
  *  - All calls share the one array, which keeps the previous call's contents;
  *    the call re-initialises what it accumulates into.  Calls that overlap on
  *    the same GPU (different streams or threads) race on it: serialise them. */

@@ -20,6 +20,17 @@ using namespace dmlp::k;
 
 static_assert(sizeof(PackStats) <= DMLP_STATS_BYTES, "stats block size");
 
+// An empty shard has no neighbours to offer: every list is padding, no query is flagged.
+static __global__ void __launch_bounds__(256) fill_empty_lists_kernel(double *dist, int *id, int *label, int *flags,
+                                                               long long slots, int q) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < slots; i += stride) {
+    dist[i] = 1e18;
+    id[i] = -1;
+    label[i] = -1;
+    if (i < q) flags[i] = 0;
+  }
+}
 namespace {
 inline cudaStream_t st(void *s) { return static_cast<cudaStream_t>(s); }
 inline size_t up256(size_t v) { return (v + 255) / 256 * 256; }
@@ -251,17 +262,6 @@ int dmlp_synth_k(int *dst, int64_t rows, int64_t row_base, int min_k, int max_k,
 
 // ---- whole local pipeline ------------------------------------------------------
 namespace {
-// An empty shard has no neighbours to offer: every list is padding, no query is flagged.
-__global__ void __launch_bounds__(256) fill_empty_lists_kernel(double *dist, int *id, int *label, int *flags,
-                                                               long long slots, int q) {
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < slots; i += stride) {
-    dist[i] = 1e18;
-    id[i] = -1;
-    label[i] = -1;
-    if (i < q) flags[i] = 0;
-  }
-}
 struct LocalLayout {
   size_t stats, q_stats, xh, qh, xn, xe, qn, qe, cand, rerank, rerank_bytes, total;
   int a_pad, chunks;

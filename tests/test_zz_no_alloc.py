@@ -7,7 +7,10 @@ drives it with ctypes, twice in a row on different problems (the second call see
 the first call's leftovers in the shared scratch), and requires exactly the
 results of the existing workspace-taking entry point dmlp_knn_local -- fp64
 distances compared with ==, like the other GPU tests.  It also checks that an
-oversized problem is refused with a clear message rather than run.
+oversized problem is refused with a clear message rather than run, that an empty
+data shard after a normal call yields padding (not the previous call's leftovers),
+and that a caller living in its own CUDA context (not the runtime's primary one)
+gets that context's copy of the scratch.
 
 Kept in a file that sorts last so a `pytest -x` run has already exercised every
 other test before this one can stop it.
@@ -78,6 +81,93 @@ def test_static_scratch_entry_matches_workspace_entry_twice():
     _run_both(lib, n=6000, q=700, a=96, kmax=12, seed=1, id_base=0)
     # second call: smaller, differently shaped problem on the same (now dirty) scratch
     _run_both(lib, n=1500, q=260, a=40, kmax=5, seed=2, id_base=1000)
+
+
+def test_static_scratch_entry_with_empty_shard_after_a_normal_call():
+    """n == 0 right after a real problem: the scratch is full of that problem's candidate keys,
+    none of which may leak into the answer."""
+    torch.cuda.set_device(0)
+    lib = _abi()
+    _run_both(lib, n=3000, q=300, a=64, kmax=8, seed=3, id_base=0)
+    q, a, kmax = 300, 64, 8
+    _, _, qq, k = _problem(16, q, a, kmax, seed=4)
+    x = torch.empty((0, a), dtype=torch.float64, device="cuda")
+    labels = torch.empty(0, dtype=torch.int32, device="cuda")
+    got = _outputs(q, kmax)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    rc = lib.dmlp_knn_local_static(p(qq), p(k), q, p(x), p(labels), 0, a, 0, kmax, *(p(t) for t in got), None)
+    assert rc == 0, lib.dmlp_last_error().decode()
+    torch.cuda.synchronize()
+    assert (got[0] == 1e18).all() and (got[1] == -1).all() and (got[2] == -1).all()
+    assert (got[3] == 0).all() and int(got[4].item()) == 0
+
+
+def test_static_scratch_entry_from_a_second_context():
+    """A plug-in inside another program's CUDA context: the `__device__` scratch exists once per
+    context, so the address looked up in the primary context must not be reused there.  The
+    second context is made with the driver API; all of its buffers are its own allocations."""
+    torch.cuda.set_device(0)
+    lib = _abi()
+    n, q, a, kmax, id_base = 2500, 260, 48, 6, 7
+    x, labels, qq, k = _problem(n, q, a, kmax, seed=11)
+    want = _outputs(q, kmax)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    rc = lib.dmlp_knn_local_static(p(qq), p(k), q, p(x), p(labels), n, a, id_base, kmax, *(p(t) for t in want), None)
+    assert rc == 0, lib.dmlp_last_error().decode()
+    torch.cuda.synchronize()
+    host_in = [t.cpu().contiguous() for t in (qq, k, x, labels)]
+    host_want = [t.cpu() for t in want]
+
+    cu = C.CDLL("libcuda.so.1")
+    cu.cuCtxCreate_v2.argtypes = [C.POINTER(_vp), C.c_uint, _i]
+    cu.cuMemAlloc_v2.argtypes = [C.POINTER(C.c_uint64), _sz]
+    cu.cuMemcpyHtoD_v2.argtypes = [C.c_uint64, _vp, _sz]
+    cu.cuMemcpyDtoH_v2.argtypes = [_vp, C.c_uint64, _sz]
+    cu.cuMemFree_v2.argtypes = [C.c_uint64]
+    cu.cuCtxPopCurrent_v2.argtypes = [C.POINTER(_vp)]
+    cu.cuCtxDestroy_v2.argtypes = [_vp]
+    assert cu.cuInit(0) == 0
+    dev = _i()
+    assert cu.cuDeviceGet(C.byref(dev), 0) == 0
+    ctx = _vp()
+    rc = cu.cuCtxCreate_v2(C.byref(ctx), 0, dev.value)   # becomes current on this thread
+    if rc != 0:
+        pytest.skip(f"cuCtxCreate failed with {rc} (exclusive-process compute mode?)")
+    bufs = []
+    try:
+        def dalloc(nbytes):
+            d = C.c_uint64()
+            assert cu.cuMemAlloc_v2(C.byref(d), max(nbytes, 256)) == 0
+            bufs.append(d)
+            return d
+
+        d_in = []
+        for t in host_in:
+            d = dalloc(t.numel() * t.element_size())
+            assert cu.cuMemcpyHtoD_v2(d, t.data_ptr(), t.numel() * t.element_size()) == 0
+            d_in.append(d)
+        d_out = [dalloc(t.numel() * t.element_size()) for t in host_want]
+        dq, dk, dx, dl = (C.c_void_p(d.value) for d in d_in)
+        rc = lib.dmlp_knn_local_static(dq, dk, q, dx, dl, n, a, id_base, kmax,
+                                       *(C.c_void_p(d.value) for d in d_out), None)
+        assert rc == 0, lib.dmlp_last_error().decode()
+        assert cu.cuCtxSynchronize() == 0
+        for name, w, d in zip(("dist", "id", "label", "flags", "num_flagged"), host_want, d_out):
+            got = torch.empty_like(w)
+            assert cu.cuMemcpyDtoH_v2(got.data_ptr(), d, w.numel() * w.element_size()) == 0
+            assert torch.equal(w, got), f"{name} differs between the primary and the second context"
+    finally:
+        for d in bufs:
+            cu.cuMemFree_v2(d)
+        old = _vp()
+        cu.cuCtxPopCurrent_v2(C.byref(old))
+        cu.cuCtxDestroy_v2(ctx)
+    # the primary context still works afterwards
+    again = _outputs(q, kmax)
+    rc = lib.dmlp_knn_local_static(p(qq), p(k), q, p(x), p(labels), n, a, id_base, kmax, *(p(t) for t in again), None)
+    assert rc == 0, lib.dmlp_last_error().decode()
+    torch.cuda.synchronize()
+    assert torch.equal(again[0], want[0]) and torch.equal(again[1], want[1])
 
 
 def test_static_scratch_entry_refuses_oversized_problem():
