@@ -108,57 +108,10 @@ class KNNClassifier:
                     label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
             else:
                 od, oi, ol = K.exact(qd, self.data, self.labels, kd, kmax, id_base)
-                if kmax <= 1024:
-                    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
-                else:
-                    label, checksum, ids, dist = _finalize_host(od, oi, ol, kd, self.device)
+                label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, self.want_lists)
             return KNNResult(label, checksum, ids, dist, flagged, path)
-
-
-def _finalize_host(od, oi, ol, kd, device):
-    """Vote + checksum on the host for k beyond the device merge capacity."""
-    from ..ops import cpu
-    ids, labels, kk = oi.cpu().numpy(), ol.cpu().numpy(), kd.cpu().numpy()
-    q = ids.shape[0]
-    out_label = np.empty(q, np.int32)
-    out_sum = np.empty(q, np.uint64)
-    for i in range(q):
-        kq = max(int(kk[i]), 0)
-        labs = labels[i, :kq][ids[i, :kq] >= 0]
-        if labs.size:
-            vals, counts = np.unique(labs, return_counts=True)
-            out_label[i] = vals[counts == counts.max()].max()
-        else:
-            out_label[i] = -1
-        out_sum[i] = cpu.result_checksum(int(out_label[i]), ids[i, :kq])
-    return (torch.from_numpy(out_label).to(device), torch.from_numpy(out_sum.view(np.int64)).to(device), oi, od)
 
 
 def knn(data, labels, queries, k, device=None, mode="auto", want_lists=False):
     """One-shot job, the call the reference driver makes (common.cpp:126)."""
     return KNNClassifier(device, mode, want_lists).fit(data, labels).classify(queries, k)
-
-
-def _finalize_host_merge(recv, k_slice, device):
-    """Host merge of [sources, q, kmax] lists for k beyond the device merge capacity."""
-    from ..ops import cpu
-    dist_, ids, labels = (t.cpu().numpy() for t in recv)
-    kk = k_slice.cpu().numpy()
-    q = ids.shape[1]
-    out_label = np.empty(q, np.int32)
-    out_sum = np.empty(q, np.uint64)
-    for i in range(q):
-        kq = max(int(kk[i]), 0)
-        d = dist_[:, i, :kq].reshape(-1)
-        idv = ids[:, i, :kq].reshape(-1)
-        lab = labels[:, i, :kq].reshape(-1)
-        order = np.lexsort((-idv, d))[:kq]
-        sel_ids, sel_lab = idv[order], lab[order]
-        labs = sel_lab[sel_ids >= 0]
-        if labs.size:
-            vals, counts = np.unique(labs, return_counts=True)
-            out_label[i] = vals[counts == counts.max()].max()
-        else:
-            out_label[i] = -1
-        out_sum[i] = cpu.result_checksum(int(out_label[i]), sel_ids.astype(np.int32))
-    return torch.from_numpy(out_label).to(device), torch.from_numpy(out_sum.view(np.int64)).to(device)

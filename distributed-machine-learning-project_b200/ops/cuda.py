@@ -33,10 +33,12 @@ def _lib():
                                     _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]
         lib.dmlp_rerank_workspace_bytes.argtypes = [_i, _i]
         lib.dmlp_rerank_workspace_bytes.restype = _sz
-        lib.dmlp_exact_workspace_bytes.argtypes = [_i, _i]
+        lib.dmlp_exact_workspace_bytes.argtypes = [_i, _i, _i]
         lib.dmlp_exact_workspace_bytes.restype = _sz
         lib.dmlp_exact.argtypes = [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]
-        lib.dmlp_finalize.argtypes = [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]
+        lib.dmlp_finalize.argtypes = [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]
+        lib.dmlp_finalize_workspace_bytes.argtypes = [_i, _i, _i]
+        lib.dmlp_finalize_workspace_bytes.restype = _sz
         lib.dmlp_synth_attrs.argtypes = [_vp, _i64, _i, _i64, _dbl, _dbl, _u64, _u64, _vp]
         lib.dmlp_synth_labels.argtypes = [_vp, _i64, _i64, _i, _u64, _vp]
         lib.dmlp_synth_k.argtypes = [_vp, _i64, _i64, _i, _i, _u64, _vp]
@@ -178,12 +180,13 @@ def rerank(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, 
     return od, oi, ol, flags, nflag
 
 
-def exact_workspace_bytes(n, batch):
-    return int(_lib().dmlp_exact_workspace_bytes(n, batch))
+def exact_workspace_bytes(n, count, kmax):
+    return int(_lib().dmlp_exact_workspace_bytes(n, count, kmax))
 
 
 def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=None, workspace=None):
-    """Direct fp64 brute force for all query rows, or the subset `query_rows` (int32)."""
+    """Direct fp64 brute force (streaming bounded lists, any k) for all query rows, or the subset
+    `query_rows` (int32)."""
     q, a = q_attrs.shape
     n = x_attrs.shape[0]
     dev = q_attrs.device
@@ -193,8 +196,7 @@ def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=N
                torch.empty((q, kmax), dtype=torch.int32, device=dev),
                torch.empty((q, kmax), dtype=torch.int32, device=dev))
     if workspace is None:
-        batch = max(1, min(count, (256 << 20) // max(1, 24 * n)))
-        workspace = torch.empty(exact_workspace_bytes(n, batch), dtype=torch.uint8, device=dev)
+        workspace = torch.empty(exact_workspace_bytes(n, count, kmax), dtype=torch.uint8, device=dev)
     od, oi, ol = out
     _check(_lib().dmlp_exact(_p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(query_rows), count, n, a, id_base,
                              kmax, _p(od), _p(oi), _p(ol), _p(workspace), workspace.numel(), _stream()))
@@ -209,8 +211,10 @@ def finalize(dist, ids, labels, k, want_lists=False):
     out_sum = torch.empty(q, dtype=torch.int64, device=dev)  # uint64 bit pattern
     out_id = torch.empty((q, kmax), dtype=torch.int32, device=dev) if want_lists else None
     out_dist = torch.empty((q, kmax), dtype=torch.float64, device=dev) if want_lists else None
-    _check(_lib().dmlp_finalize(_p(dist), _p(ids), _p(labels), q * kmax, sources, q, kmax, _p(k), _p(out_label),
-                                _p(out_sum), _p(out_id), _p(out_dist), _stream()))
+    wsb = int(_lib().dmlp_finalize_workspace_bytes(sources, q, kmax))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev) if wsb else None
+    _check(_lib().dmlp_finalize(_p(dist), _p(ids), _p(labels), dist.stride(0), sources, q, kmax, _p(k), _p(out_label),
+                                _p(out_sum), _p(out_id), _p(out_dist), _p(ws), wsb, _stream()))
     return out_label, out_sum, out_id, out_dist
 
 

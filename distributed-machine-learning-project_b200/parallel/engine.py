@@ -456,22 +456,14 @@ class DistributedKNN:
         """k-lists of every data shard -> owner of the query slice -> merge, vote, checksum."""
         R, qs, km = self.R, self.qs, self.kmax
         if R == 1:
-            if km <= 1024:
-                label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-                self.launch_count += 1
-            else:
-                from ..models.knn import _finalize_host_merge
-                label, checksum = _finalize_host_merge((od[None], oi[None], ol[None]), self.k_slice, self.device)
+            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+            self.launch_count += 1
             return label, checksum
         for src, dst in zip((od, oi, ol), self.recv):
             dist.all_to_all_single(dst.view(R * qs, km), src.view(R * qs, km), group=self.col_group)
         mine = self.k_all[self.r * qs:(self.r + 1) * qs]
-        if R * km <= 1024:
-            label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2], mine)
-            self.launch_count += 1
-        else:
-            from ..models.knn import _finalize_host_merge
-            label, checksum = _finalize_host_merge(self.recv, mine, self.device)
+        label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2], mine)
+        self.launch_count += 1
         return label[:self.nq], checksum[:self.nq]
 
     # ---------------------------------------------------------------- end to end

@@ -103,19 +103,30 @@ int dmlp_debug_topk_prof(unsigned long long *host_out, int max_ctas);
  * counter array, so launches may overlap on different streams. */
 int dmlp_topk_sync_timeouts(unsigned *out);
 
-/* ---- exact fp64 brute force (reference: engine.cpp:233-257 as written) --------
+/* ---- exact fp64 brute force (reference: engine.cpp:233-257; bounded per-query lists
+ * like the staff baselines' heaps) ---------------------------------
  * Processes `count` queries: rows query_rows[0..count) or, with NULL, rows
- * 0..count.  Scratch comes from the caller. */
-size_t dmlp_exact_workspace_bytes(int n, int batch);
+ * 0..count, for any k <= n.  Streaming: distances are selected on the fly into
+ * per-query lists in the workspace (O(count * kmax) memory, no distance matrix, no
+ * library sort).  Scratch comes from the caller, 256-byte aligned:
+ * dmlp_exact_workspace_bytes(n, count, kmax) is the recommended size (at most half
+ * a gigabyte unless a single query needs more); the launcher works in batches when
+ * given less, down to what one query needs. */
+size_t dmlp_exact_workspace_bytes(int n, int count, int kmax);
 int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels, const int *k,
                const int *query_rows, int count, int n, int a, int id_base, int kmax, double *out_dist,
                int *out_id, int *out_label, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- K5 owner merge + K6 vote/checksum (reference: engine.cpp:289-347) --------
- * dist/id/label: `sources` arrays of [q][kmax], source_stride elements apart. */
+ * dist/id/label: `sources` arrays of [q][kmax], source_stride elements apart, each list
+ * sorted by (distance asc, id desc) and padded with (1e18, -1, -1).  Entries are ranked
+ * against the other sources' lists by binary search, so any sources * kmax is merged on
+ * the device; only sources > 1 with kmax > 2048 needs scratch
+ * (dmlp_finalize_workspace_bytes, else 0 / NULL). */
+size_t dmlp_finalize_workspace_bytes(int sources, int q, int kmax);
 int dmlp_finalize(const double *dist, const int *id, const int *label, int64_t source_stride, int sources,
                   int q, int kmax, const int *k, int *out_label, uint64_t *out_checksum, int *out_id,
-                  double *out_dist, void *stream);
+                  double *out_dist, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- K8 synthetic_fill (reference: generate_input.py:13-21) -------------------
  * stream_id 0 = data attributes, 2 = query attributes. */

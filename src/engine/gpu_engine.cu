@@ -145,8 +145,7 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
                                 s.nflag.as<int>(), s.stream),
                  "knn_local");
       } else {
-        int batch = int(std::max<int64_t>(1, std::min<int64_t>(s.q, (256LL << 20) / std::max<int64_t>(1, 24 * s.n))));
-        size_t wsb = dmlp_exact_workspace_bytes(int(s.n), batch);
+        size_t wsb = dmlp_exact_workspace_bytes(int(s.n), int(s.q), kmax);
         s.ws.alloc(wsb);
         check_rc(dmlp_exact(s.qa.as<double>(), s.x.as<double>(), s.xl.as<int>(), s.qk.as<int>(), nullptr, int(s.q),
                             int(s.n), a, data.id_base + int(s.nb), kmax, s.od.as<double>(), s.oi.as<int>(),
@@ -171,8 +170,7 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
       for (int64_t i = 0; i < s.q; ++i) if (flags[size_t(i)]) rows.push_back(int(i));
       s.rows.alloc(sizeof(int) * rows.size());
       CK(cudaMemcpyAsync(s.rows.p, rows.data(), sizeof(int) * rows.size(), cudaMemcpyHostToDevice, s.stream));
-      int batch = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(rows.size()), (256LL << 20) / std::max<int64_t>(1, 24 * s.n))));
-      size_t wsb = dmlp_exact_workspace_bytes(int(s.n), batch);
+      size_t wsb = dmlp_exact_workspace_bytes(int(s.n), int(rows.size()), kmax);
       DeviceBuf ews; ews.alloc(wsb);
       check_rc(dmlp_exact(s.qa.as<double>(), s.x.as<double>(), s.xl.as<int>(), s.qk.as<int>(), s.rows.as<int>(),
                           int(rows.size()), int(s.n), a, data.id_base + int(s.nb), kmax, s.od.as<double>(),
@@ -210,7 +208,7 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
       own.fdist.alloc(sizeof(double) * per);
       check_rc(dmlp_finalize(own.gd.as<double>(), own.gi.as<int>(), own.gl.as<int>(), int64_t(per), R, int(own.q),
                              kmax, own.qk.as<int>(), own.label.as<int>(), own.checksum.as<uint64_t>(),
-                             own.fid.as<int>(), own.fdist.as<double>(), own.stream),
+                             own.fid.as<int>(), own.fdist.as<double>(), nullptr, 0, own.stream),
                "finalize");
       std::vector<int> ids(per);
       std::vector<double> dist(per);

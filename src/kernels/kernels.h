@@ -191,7 +191,10 @@ struct FinalizeArgs {
   unsigned long long *out_checksum;  // [q]
   int *out_id;          // [q][kmax] optional (nullptr to skip)
   double *out_dist;     // [q][kmax] optional
+  void *workspace = nullptr;   // >= finalize_workspace_bytes(); only needed when sources > 1 and kmax > 2048
+  size_t workspace_bytes = 0;
 };
+size_t finalize_workspace_bytes(int sources, int q, int kmax);
 int launch_finalize(const FinalizeArgs &args, cudaStream_t s);
 
 // exact.cu: brute-force fp64 path (any k), used for tiny problems, large k and
@@ -207,10 +210,10 @@ struct ExactArgs {
   double *out_dist;       // [q][kmax] (written at the query's own row)
   int *out_id;
   int *out_label;
-  void *workspace;        // >= exact_workspace_bytes()
-  size_t workspace_bytes;
+  void *workspace;        // 256-byte aligned; exact_workspace_bytes(n, count, kmax) holds every query at once,
+  size_t workspace_bytes; // anything down to exact_workspace_bytes(n, 1, kmax) works (smaller batches, fewer splits)
 };
-size_t exact_workspace_bytes(int n, int batch);
+size_t exact_workspace_bytes(int n, int batch, int kmax);
 int launch_exact(const ExactArgs &args, cudaStream_t s);
 
 // synth.cu

@@ -225,7 +225,13 @@ int dmlp_topk_sync_timeouts(unsigned *out) { return dist_topk_sync_timeouts(out)
 
 size_t dmlp_rerank_workspace_bytes(int q, int kmax) { return rerank_workspace_bytes(q, kmax); }
 
-size_t dmlp_exact_workspace_bytes(int n, int batch) { return exact_workspace_bytes(n, batch); }
+size_t dmlp_exact_workspace_bytes(int n, int count, int kmax) {
+  // everything at once if that stays modest, else half a gigabyte (the launcher then works in
+  // batches), and never less than one query needs
+  const size_t full = exact_workspace_bytes(n, count, kmax), one = exact_workspace_bytes(n, 1, kmax);
+  const size_t cap = size_t(512) << 20;
+  return full <= cap ? full : (one > cap ? one : cap);
+}
 
 int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels, const int *k,
                const int *query_rows, int count, int n, int a, int id_base, int kmax, double *out_dist,
@@ -238,10 +244,13 @@ int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels
   return launch_exact(e, st(stream));
 }
 
+size_t dmlp_finalize_workspace_bytes(int sources, int q, int kmax) { return finalize_workspace_bytes(sources, q, kmax); }
+
 int dmlp_finalize(const double *dist, const int *id, const int *label, int64_t source_stride, int sources, int q,
                   int kmax, const int *k, int *out_label, uint64_t *out_checksum, int *out_id, double *out_dist,
-                  void *stream) {
+                  void *workspace, size_t workspace_bytes, void *stream) {
   FinalizeArgs f;
+  f.workspace = workspace; f.workspace_bytes = workspace_bytes;
   f.dist = dist; f.id = id; f.label = label; f.source_stride = source_stride;
   f.sources = sources; f.q = q; f.kmax = kmax; f.k = k;
   f.out_label = out_label; f.out_checksum = reinterpret_cast<unsigned long long *>(out_checksum);

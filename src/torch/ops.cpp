@@ -27,7 +27,6 @@ namespace {
 using at::Tensor;
 
 constexpr int64_t kFusedMaxK = 96;      // keep in sync with ops/cuda.py FUSED_MAX_K
-constexpr int64_t kDeviceMergeMax = 1024;
 
 void ok(int rc, const char *what) { TORCH_CHECK(rc == 0, what, ": ", dmlp_last_error()); }
 
@@ -99,8 +98,7 @@ void exact_(const Tensor &queries, const Tensor &data, const Tensor &labels, con
   if (count == 0) return;
   c10::cuda::CUDAGuard guard(queries.device());
   auto stream = at::cuda::getCurrentCUDAStream();
-  const int64_t batch = std::max<int64_t>(1, std::min<int64_t>(count, (256LL << 20) / std::max<int64_t>(1, 24 * n)));
-  const size_t wsb = dmlp_exact_workspace_bytes(int(n), int(batch));
+  const size_t wsb = dmlp_exact_workspace_bytes(int(n), int(count), int(kmax));
   Tensor ws = at::empty({static_cast<int64_t>(wsb)}, queries.options().dtype(at::kByte));
   ok(dmlp_exact(queries.data_ptr<double>(), data.data_ptr<double>(), labels.data_ptr<int>(), k.data_ptr<int>(),
                 subset ? rows.data_ptr<int>() : nullptr, int(count), int(n), int(a), int(id_base), int(kmax),
@@ -119,28 +117,29 @@ std::tuple<Tensor, Tensor, std::optional<Tensor>, std::optional<Tensor>> finaliz
   TORCH_CHECK(ids.sizes() == dist.sizes() && labels.sizes() == dist.sizes(), "dist / ids / labels shapes differ");
   const int64_t sources = dist.size(0), q = dist.size(1), kmax = dist.size(2);
   TORCH_CHECK(k.size(0) == q, "k must have one entry per query");
-  TORCH_CHECK(sources * kmax <= kDeviceMergeMax, "finalize merges at most ", kDeviceMergeMax,
-              " candidates per query on the device");
   c10::cuda::CUDAGuard guard(dist.device());
   auto stream = at::cuda::getCurrentCUDAStream();
   Tensor label = at::empty({q}, k.options());
   Tensor checksum = at::empty({q}, k.options().dtype(at::kLong));  // uint64 bit pattern
   Tensor out_id = want_lists ? at::empty({q, kmax}, ids.options()) : Tensor();
   Tensor out_dist = want_lists ? at::empty({q, kmax}, dist.options()) : Tensor();
-  if (q > 0)
+  if (q > 0) {
+    const size_t wsb = dmlp_finalize_workspace_bytes(int(sources), int(q), int(kmax));
+    Tensor ws = wsb ? at::empty({static_cast<int64_t>(wsb)}, dist.options().dtype(at::kByte)) : Tensor();
     ok(dmlp_finalize(dist.data_ptr<double>(), ids.data_ptr<int>(), labels.data_ptr<int>(), q * kmax, int(sources),
                      int(q), int(kmax), k.data_ptr<int>(), label.data_ptr<int>(),
                      reinterpret_cast<uint64_t *>(checksum.data_ptr<int64_t>()),
                      want_lists ? out_id.data_ptr<int>() : nullptr, want_lists ? out_dist.data_ptr<double>() : nullptr,
-                     stream.stream()),
+                     wsb ? ws.data_ptr() : nullptr, wsb, stream.stream()),
        "finalize");
+  }
   if (!want_lists) return {label, checksum, std::nullopt, std::nullopt};
   return {label, checksum, out_id, out_dist};
 }
 
 std::tuple<Tensor, Tensor> classify(const Tensor &data, const Tensor &labels, const Tensor &queries, const Tensor &k,
                                     int64_t kmax, int64_t id_base) {
-  TORCH_CHECK(kmax >= 1 && kmax <= kDeviceMergeMax, "classify supports 1 <= kmax <= ", kDeviceMergeMax);
+  TORCH_CHECK(kmax >= 1, "classify needs kmax >= 1");
   const int64_t q = queries.size(0), n = data.size(0), a = queries.dim() == 2 ? queries.size(1) : 0;
   const bool fused = kmax <= kFusedMaxK && n > 0 && q > 0 &&
                      double(n) * double(q) * double(std::max<int64_t>(a, 1)) >= double(1 << 22);

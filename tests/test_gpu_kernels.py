@@ -165,6 +165,73 @@ def test_exact_path_matches_oracle(K, n, q, a, kmin, kmax):
     assert (label.cpu().numpy() == want_label).all()
 
 
+@pytest.mark.parametrize("n,q,a,k_lo,k_hi", [(20000, 64, 32, 250, 300), (9000, 40, 16, 900, 1000),
+                                             (3000, 5, 8, 2500, 3000), (70000, 3, 24, 4, 9)])
+def test_exact_streaming_large_k_and_splits(K, n, q, a, k_lo, k_hi):
+    """k = 300 / 1000 / 3000 and a handful of queries over many rows (data splits + rank merge):
+    the streaming kernel keeps bounded per-query lists, no distance matrix, no library sort."""
+    import time
+    data, labels, queries, k = cpu.synth(n, q, a, -100.0, 100.0, k_lo, k_hi, 6, seed=29)
+    want_label, want_sum, want_ids, want_dist, off = cpu.knn(data, labels, queries, k)
+    km = int(k.max())
+    xd, ld, qd, kd = _dev(data), _dev(labels), _dev(queries), _dev(k)
+    K.exact(qd, xd, ld, kd, km)                      # warm-up (module load)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    od, oi, ol = K.exact(qd, xd, ld, kd, km)
+    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, True)
+    torch.cuda.synchronize()
+    print(f"exact+finalize n={n} q={q} a={a} k<={km}: {(time.perf_counter() - t0) * 1e3:.2f} ms")
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+    assert (label.cpu().numpy() == want_label).all()
+    got_ids, got_dist = ids.cpu().numpy(), dist.cpu().numpy()
+    for i in range(q):
+        assert (got_ids[i, :k[i]] == want_ids[off[i]:off[i + 1]]).all()
+        assert (got_dist[i, :k[i]] == want_dist[off[i]:off[i + 1]]).all()
+
+
+def test_exact_subset_rows_and_small_workspace(K):
+    """query_rows subset written at the queries' own rows; a workspace sized for one query
+    forces the launcher into batches."""
+    data, labels, queries, k = cpu.synth(6000, 90, 12, -10.0, 10.0, 1, 40, 4, seed=33)
+    _, want_sum, want_ids, _, off = cpu.knn(data, labels, queries, k)
+    km = int(k.max())
+    xd, ld, qd, kd = _dev(data), _dev(labels), _dev(queries), _dev(k)
+    rows = torch.tensor([3, 77, 41, 0, 89], dtype=torch.int32, device="cuda")
+    od = torch.full((90, km), -5.0, dtype=torch.float64, device="cuda")
+    oi = torch.full((90, km), -5, dtype=torch.int32, device="cuda")
+    ol = torch.full((90, km), -5, dtype=torch.int32, device="cuda")
+    K.exact(qd, xd, ld, kd, km, 0, rows, out=(od, oi, ol))
+    torch.cuda.synchronize()
+    touched = set(rows.cpu().tolist())
+    for i in range(90):
+        if i in touched:
+            assert (oi[i, :k[i]].cpu().numpy() == want_ids[off[i]:off[i + 1]]).all()
+            assert (oi[i, k[i]:] == -1).all()
+        else:
+            assert (oi[i] == -5).all()
+    small = torch.empty(K.exact_workspace_bytes(6000, 1, km), dtype=torch.uint8, device="cuda")
+    od2, oi2, ol2 = K.exact(qd, xd, ld, kd, km, workspace=small)
+    _, checksum, _, _ = K.finalize(od2[None], oi2[None], ol2[None], kd)
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+
+
+@pytest.mark.parametrize("shards,kmin,kmax", [(8, 200, 300), (3, 2100, 2300)])
+def test_finalize_merges_long_lists(K, shards, kmin, kmax):
+    """sources * kmax far beyond the old 1024-candidate staging buffer (2400, 6900): the merge
+    ranks by binary search; lists longer than 2048 use the scratch workspace."""
+    n = 9000
+    data, labels, queries, k = cpu.synth(n, 24, 10, -100.0, 100.0, kmin, kmax, 5, seed=41)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    km = int(k.max())
+    qd, kd = _dev(queries), _dev(k)
+    bounds = [n * s // shards for s in range(shards + 1)]
+    parts = [K.exact(qd, _dev(data[lo:hi]), _dev(labels[lo:hi]), kd, km, lo) for lo, hi in zip(bounds, bounds[1:])]
+    dist, ids, labs = (torch.stack([p[j] for p in parts]) for j in range(3))
+    _, checksum, _, _ = K.finalize(dist, ids, labs, kd)
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+
+
 def test_duplicates_tie_break_on_gpu(K):
     rng = np.random.default_rng(0)
     base = rng.uniform(-1, 1, (50, 16))
