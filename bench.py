@@ -49,7 +49,11 @@ def parse_args():
     p.add_argument("--labels", type=int, default=10)
     p.add_argument("--seed", type=int, default=42)
     p.add_argument("--no-e2e", action="store_true")
-    p.add_argument("--verify", type=int, default=0, help="check this many queries against the CPU oracle")
+    p.add_argument("--verify", type=int, default=64,
+                   help="queries per rank checked after the timed region against the direct fp64 kernel (0 = off)")
+    p.add_argument("--verify-cpu", type=int, default=4, help="queries checked against the CPU oracle (rank 0's column)")
+    p.add_argument("--no-data-sharded", action="store_true",
+                   help="skip the second layout (N x 1, datapoints per GPU fixed) that is timed after the headline one")
     p.add_argument("--ref-queries", type=int, default=8, help="queries timed by --impl reference")
     return p.parse_args()
 
@@ -91,44 +95,62 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     from dmlp_b200.parallel import DistributedKNN
-    by_data = args.scale == "data"
-    grid = tuple(int(v) for v in args.grid.lower().split("x")) if args.grid else ((world, 1) if by_data else (1, world))
-    eng = DistributedKNN(device=dev, impl="fused" if args.impl == "ours" else "nccl_cublas", grid=grid)
+    impl = "fused" if args.impl == "ours" else "nccl_cublas"
     A = args.num_attrs
-    N = args.num_data * (world if by_data else 1)
-    Q = args.num_queries * (1 if by_data else world)
-    eng.synth_problem(n_total=N, q_total=Q, a=A, lo=-100.0, hi=100.0, min_k=args.min_k, max_k=args.max_k,
-                      num_labels=args.labels, seed=args.seed)
 
     def barrier():
         if world > 1:
             dist.barrier()
 
-    # ---- device-timed metric ---------------------------------------------------
-    def step_device():
-        eng.run_resident()
+    def max_over_ranks(sec):
+        t = torch.tensor([sec], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    for _ in range(args.warmup):
-        step_device()
-    torch.cuda.synchronize()
-    barrier()
-    torch.cuda.synchronize()
-    launches0 = eng.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    def device_timed(eng, with_clocks):
+        """W warm-up steps, then exactly K steps between CUDA events; max over ranks."""
+        for _ in range(args.warmup):
+            eng.run_resident()
+        torch.cuda.synchronize()
+        barrier()
+        torch.cuda.synchronize()
+        launches0 = eng.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(local_rank) if with_clocks else None
+        if sampler:
+            sampler.__enter__()
         ev0.record()
         for _ in range(args.steps):
-            step_device()
+            eng.run_resident()
         ev1.record()
         torch.cuda.synchronize()
-    barrier()
-    launches = eng.launch_count - launches0
-    sec = ev0.elapsed_time(ev1) / 1e3
-    t = torch.tensor([sec], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    sec = float(t.item())
-    flagged = eng.last_flagged
+        if sampler:
+            sampler.__exit__(None, None, None)
+        barrier()
+        return max_over_ranks(ev0.elapsed_time(ev1) / 1e3), eng.launch_count - launches0, sampler
+
+    def build(grid, n_total, q_total):
+        eng = DistributedKNN(device=dev, impl=impl, grid=grid)
+        eng.synth_problem(n_total=n_total, q_total=q_total, a=A, lo=-100.0, hi=100.0, min_k=args.min_k,
+                          max_k=args.max_k, num_labels=args.labels, seed=args.seed)
+        return eng
+
+    def verify(eng):
+        if args.verify <= 0:
+            return None
+        return eng.verify_sampled(n_exact=args.verify, n_cpu=args.verify_cpu)
+
+    # ---- headline: device-timed metric ---------------------------------------------
+    by_data = args.scale == "data"
+    grid = tuple(int(v) for v in args.grid.lower().split("x")) if args.grid else ((world, 1) if by_data else (1, world))
+    N = args.num_data * (world if by_data else 1)
+    Q = args.num_queries * (1 if by_data else world)
+    eng = build(grid, N, Q)
+    sec, launches, clocks = device_timed(eng, True)
+    flagged = eng.ensure_repaired()
+    verified = verify(eng)
+    timeouts = eng.check_watchdog()
 
     # ---- end-to-end through the public API --------------------------------------
     e2e = None
@@ -148,27 +170,55 @@ def main():
         torch.cuda.synchronize()
         wall = time.perf_counter() - wall0
         barrier()
-        te = torch.tensor([max(e0.elapsed_time(e1) / 1e3, wall)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": Q * args.steps / float(te.item()), "unit": "queries/s",
+        te = max_over_ranks(max(e0.elapsed_time(e1) / 1e3, wall))
+        e2e = {"value": Q * args.steps / te, "unit": "queries/s",
                "h2d_bytes_per_step": eng.h2d_bytes_per_step * world, "d2h_bytes_per_step": eng.d2h_bytes_per_step * world,
-               "ms_per_step": float(te.item()) * 1e3 / args.steps}
+               "ms_per_step": te * 1e3 / args.steps, "wire": eng.wire}
+        if args.verify > 0:   # the end-to-end answers must be the resident ones
+            lab, chk = eng.final[0][:eng.nq].cpu(), eng.final[1][:eng.nq].cpu()
+            assert torch.equal(res[0], lab) and torch.equal(res[1], chk), "end-to-end results differ from the resident run"
+    R0, C0 = eng.R, eng.C
+    shard_gb = (N / eng.R + Q / eng.C) * A * 8 / 1e9
 
-    verified = None
-    if args.verify > 0:
-        verified = eng.verify_against_oracle(args.verify)
+    # ---- the other layout: data sharded N x 1 (K4 query all-gather + K5 list reduce-scatter) -------
+    data_sharded = None
+    if not args.no_data_sharded and not by_data and not args.grid and world > 1:
+        eng.close()
+        del eng
+        torch.cuda.empty_cache()
+        Nd, Qd = args.num_data * world, args.num_queries
+        eng2 = build((world, 1), Nd, Qd)
+        sec2, launches2, _ = device_timed(eng2, False)
+        flagged2 = eng2.ensure_repaired()
+        verified2 = verify(eng2)
+        qp, km = eng2.qp, eng2.kmax
+        far = (world - 1) / world
+        data_sharded = {
+            "grid": "%dx1" % world, "num_data_total": Nd, "num_queries_total": Qd,
+            "value": Qd * args.steps / sec2, "unit": "queries/s", "ms_per_step": sec2 * 1e3 / args.steps,
+            "datapoint_query_pairs_per_sec": float(Nd) * Qd * args.steps / sec2,
+            "nvlink_bytes_per_step_per_gpu": int(far * qp * (eng2.a_pad * 2 + A * 8 + 12) + far * qp * km * 16),
+            "gpu_launches": launches2, "flagged_queries": flagged2, "verified_queries": verified2,
+            "watchdog": eng2.check_watchdog(),
+            "note": "weak scaling in the dataset: every GPU holds %d points, all %d queries meet every shard; "
+                    "the filter GEMM all-gathers the packed queries (K4), the re-rank stores its k-lists into the "
+                    "owners' buffers and signals from inside the kernel (K5); no NCCL call, no host sync in a step"
+                    % (args.num_data, Qd)}
+        eng2.close()
 
     if rank == 0:
         value = Q * args.steps / sec
         base = baseline_number()
         flops = 2.0 * Q * N * A * args.steps / sec
+        dtype = ("fp16 tensor-core filter (fp32 accumulate) + exact fp64 re-rank; results bit-identical to fp64"
+                 if args.impl == "ours" else
+                 "cuBLAS fp16 GEMM (fp32 out) + torch.topk + NCCL; pack / exact fp64 re-rank / finalize shared with 'ours'")
         line = {
             "metric": "queries_per_sec (samples/sec of the whole k-NN job)",
             "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": sec * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": (value / base) if base else None,
-            "dtype": "fp16 tensor-core filter (fp32 accumulate) + exact fp64 re-rank; results bit-identical to fp64",
+            "dtype": dtype,
             "data": "synthetic (generate_input.py distribution, uniform [-100,100] 6 decimals), on-device generator",
             "impl": args.impl,
             "config": {"model": "knn synthetic hidden(num_attrs)=%d batch(num_queries)=%d per GPU" % (A, args.num_queries),
@@ -176,18 +226,23 @@ def main():
                        "weak_scaling_axis": args.scale,
                        "host_numa_node": numa_node,
                        "k": [args.min_k, args.max_k],
-                       "parallelism": "grid R=%d (data shards) x C=%d (query shards)" % (eng.R, eng.C),
-                       "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed"
-                             % ((N / eng.R + Q / eng.C) * A * 8 / 1e9)},
+                       "parallelism": "grid R=%d (data shards) x C=%d (query shards)" % (R0, C0),
+                       "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed" % shard_gb,
+                       "step": "pack (fp64 -> fp16 + norms; the value range is a load-time property, like the "
+                               "loader's range on the end-to-end path), filter GEMM + fused top-k, exact re-rank "
+                               "with the vote and checksum folded in, device-side repair of uncertified queries"},
             "filter_gemm_tflops_per_gpu": flops / world / 1e12,
             "flagged_queries": flagged,
             "gpu_launches": launches,
+            "watchdog": timeouts,
             "clocks": clocks.summary(),
         }
         if e2e:
             line["e2e"] = e2e
         if verified is not None:
             line["verified_queries"] = verified
+        if data_sharded:
+            line["data_sharded"] = data_sharded
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -276,7 +276,7 @@ class DataGatherArgs(C.Structure):
     _fields_ = [("world", _i), ("rank", _i), ("a", _i), ("epoch", C.c_uint32), ("peer_base", _vp * 8),
                 ("off_xh", _u64), ("off_xn", _u64), ("off_xe", _u64), ("off_x64", _u64), ("off_labels", _u64),
                 ("off_pack_flags", _u64), ("part_begin", _i * 9), ("tile_count", _vp), ("status", _vp),
-                ("timeout_seconds", _dbl)]
+                ("timeout_seconds", _dbl), ("done_signal", _vp)]
 
 
 def dist_topk_rows(qh, n, cand, gather, kmax=0):
@@ -340,3 +340,158 @@ def knn_local(q_attrs, k, x_attrs, x_labels, kmax, id_base=0, rng=None, workspac
                                  _p(workspace), workspace.numel(), _p(od), _p(oi), _p(ol), _p(flags), _p(nflag),
                                  _stream()))
     return od, oi, ol, flags, nflag
+
+
+# ---- struct-based entry points: folded vote, device-side repair, in-kernel K5 signalling --------
+class SignalArgs(C.Structure):
+    _fields_ = [("peer_flags", _vp * 8), ("world", _i), ("rank", _i), ("value", C.c_uint32), ("done_counter", _vp)]
+
+
+class WaitArgs(C.Structure):
+    _fields_ = [("flags", _vp), ("world", _i), ("value", C.c_uint32), ("timeout_seconds", _dbl), ("status", _vp)]
+
+
+class RerankArgs(C.Structure):
+    _fields_ = [("cand", _vp), ("chunks", _i), ("kp", _i), ("q_attrs", _vp), ("x_attrs", _vp), ("x_labels", _vp),
+                ("k", _vp), ("q_norm2", _vp), ("q_errn", _vp), ("range", _vp), ("x_maxima", _vp), ("q", _i), ("n", _i),
+                ("a", _i), ("a_pad", _i), ("id_base", _i), ("kmax", _i), ("out_dist", _vp), ("out_id", _vp),
+                ("out_label", _vp), ("flags", _vp), ("num_flagged", _vp), ("flagged_rows", _vp), ("flagged_cap", _i),
+                ("final_label", _vp), ("final_checksum", _vp), ("scatter", C.POINTER(ScatterArgs)),
+                ("signal", C.POINTER(SignalArgs)), ("workspace", _vp), ("workspace_bytes", _sz)]
+
+
+class RepairArgs(C.Structure):
+    _fields_ = [("q_attrs", _vp), ("x_attrs", _vp), ("x_labels", _vp), ("k", _vp), ("flagged_rows", _vp),
+                ("num_flagged", _vp), ("cap", _i), ("q", _i), ("n", _i), ("a", _i), ("id_base", _i), ("kmax", _i),
+                ("out_dist", _vp), ("out_id", _vp), ("out_label", _vp), ("final_label", _vp), ("final_checksum", _vp),
+                ("scatter", C.POINTER(ScatterArgs)), ("signal", C.POINTER(SignalArgs)), ("workspace", _vp),
+                ("workspace_bytes", _sz)]
+
+
+class FinalizeArgs(C.Structure):
+    _fields_ = [("dist", _vp), ("id", _vp), ("label", _vp), ("source_stride", _i64), ("sources", _i), ("q", _i),
+                ("kmax", _i), ("k", _vp), ("out_label", _vp), ("out_checksum", _vp), ("out_id", _vp), ("out_dist", _vp),
+                ("query_rows", _vp), ("count", _i), ("count_dev", _vp), ("wait", C.POINTER(WaitArgs)),
+                ("workspace", _vp), ("workspace_bytes", _sz)]
+
+
+REPAIR_CAP = 64   # flagged queries a step repairs without asking the host (more: the caller's end-of-step check)
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def rerank_ex(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, id_base, kmax, flags, nflag,
+              out=None, final=None, flagged_rows=None, scatter=None, signal=None):
+    """dmlp_rerank_ex: re-rank with the optional folded vote (`final` = (label, checksum) tensors, single
+    data shard), flagged-row list, K5 scatter and in-kernel completion signal."""
+    lib = _lib()
+    lib.dmlp_rerank_ex.argtypes = [C.POINTER(RerankArgs), _vp]
+    q, chunks, kp = cand.shape
+    n, a = x_attrs.shape
+    ws = rerank_workspace(q, kmax, cand.device)
+    g = RerankArgs()
+    g.cand, g.chunks, g.kp = _ptr(cand), chunks, kp
+    g.q_attrs, g.x_attrs, g.x_labels, g.k = _ptr(q_attrs), _ptr(x_attrs), _ptr(x_labels), _ptr(k)
+    g.q_norm2, g.q_errn, g.range, g.x_maxima = _ptr(q_norm2), _ptr(q_errn), _ptr(rng), _ptr(x_maxima)
+    g.q, g.n, g.a, g.a_pad, g.id_base, g.kmax = q, n, a, pad64(a), id_base, kmax
+    if out is not None:
+        g.out_dist, g.out_id, g.out_label = _ptr(out[0]), _ptr(out[1]), _ptr(out[2])
+    g.flags, g.num_flagged = _ptr(flags), _ptr(nflag)
+    if flagged_rows is not None:
+        g.flagged_rows, g.flagged_cap = _ptr(flagged_rows), flagged_rows.numel()
+    if final is not None:
+        g.final_label, g.final_checksum = _ptr(final[0]), _ptr(final[1])
+    if scatter is not None:
+        g.scatter = C.pointer(scatter)
+    if signal is not None:
+        g.signal = C.pointer(signal)
+    g.workspace, g.workspace_bytes = _ptr(ws), ws.numel()
+    _check(lib.dmlp_rerank_ex(C.byref(g), _stream()))
+
+
+_repair_ws = {}
+
+
+def repair_flagged(q_attrs, x_attrs, x_labels, k, flagged_rows, nflag, id_base, kmax, out=None, final=None,
+                   scatter=None, signal=None):
+    """dmlp_repair_flagged: direct fp64 kernel over the first min(*nflag, cap) flagged rows; the count
+    stays on the device, so the call is enqueued unconditionally."""
+    lib = _lib()
+    lib.dmlp_repair_flagged.argtypes = [C.POINTER(RepairArgs), _vp]
+    q, a = q_attrs.shape
+    n = x_attrs.shape[0]
+    cap = flagged_rows.numel()
+    key = (str(q_attrs.device), n, cap, kmax)
+    if key not in _repair_ws:
+        _repair_ws[key] = torch.empty(exact_workspace_bytes(n, cap, kmax), dtype=torch.uint8, device=q_attrs.device)
+    ws = _repair_ws[key]
+    g = RepairArgs()
+    g.q_attrs, g.x_attrs, g.x_labels, g.k = _ptr(q_attrs), _ptr(x_attrs), _ptr(x_labels), _ptr(k)
+    g.flagged_rows, g.num_flagged, g.cap = _ptr(flagged_rows), _ptr(nflag), cap
+    g.q, g.n, g.a, g.id_base, g.kmax = q, n, a, id_base, kmax
+    if out is not None:
+        g.out_dist, g.out_id, g.out_label = _ptr(out[0]), _ptr(out[1]), _ptr(out[2])
+    if final is not None:
+        g.final_label, g.final_checksum = _ptr(final[0]), _ptr(final[1])
+    if scatter is not None:
+        g.scatter = C.pointer(scatter)
+    if signal is not None:
+        g.signal = C.pointer(signal)
+    g.workspace, g.workspace_bytes = _ptr(ws), ws.numel()
+    _check(lib.dmlp_repair_flagged(C.byref(g), _stream()))
+
+
+def finalize_ex(dist, ids, labels, k, out=None, query_rows=None, count_dev=None, wait=None):
+    """dmlp_finalize_ex: finalize with an in-kernel wait for the peers' lists and / or a row subset."""
+    lib = _lib()
+    lib.dmlp_finalize_ex.argtypes = [C.POINTER(FinalizeArgs), _vp]
+    sources, q, kmax = dist.shape
+    dev = dist.device
+    if out is None:
+        out = (torch.empty(q, dtype=torch.int32, device=dev), torch.empty(q, dtype=torch.int64, device=dev))
+    wsb = int(lib.dmlp_finalize_workspace_bytes(sources, q, kmax))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev) if wsb else None
+    g = FinalizeArgs()
+    g.dist, g.id, g.label, g.source_stride = _ptr(dist), _ptr(ids), _ptr(labels), dist.stride(0)
+    g.sources, g.q, g.kmax, g.k = sources, q, kmax, _ptr(k)
+    g.out_label, g.out_checksum = _ptr(out[0]), _ptr(out[1])
+    if query_rows is not None:
+        g.query_rows, g.count, g.count_dev = _ptr(query_rows), query_rows.numel(), _ptr(count_dev)
+    if wait is not None:
+        g.wait = C.pointer(wait)
+    g.workspace, g.workspace_bytes = _ptr(ws), wsb
+    _check(lib.dmlp_finalize_ex(C.byref(g), _stream()))
+    return out
+
+
+def pack_ex(src, rng, maxima=None, out=None, wait=None, signal=None):
+    """dmlp_pack_ex: pack that first waits for the peers to release the rows it overwrites (`wait`)
+    and whose last block announces the new rows (`signal`)."""
+    lib = _lib()
+    lib.dmlp_pack_ex.argtypes = [_vp, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(WaitArgs), C.POINTER(SignalArgs),
+                                 _vp]
+    rows, a = src.shape
+    h, n2, en = out
+    _check(lib.dmlp_pack_ex(_p(src), rows, a, pad64(a), _p(rng), _p(h), _p(n2), _p(en), _p(maxima),
+                            C.byref(wait) if wait is not None else None,
+                            C.byref(signal) if signal is not None else None, _stream()))
+    return h, n2, en
+
+
+def zero_(t):
+    """cudaMemsetAsync on the current stream (no library kernel)."""
+    lib = _lib()
+    lib.dmlp_zero.argtypes = [_vp, _sz, _vp]
+    _check(lib.dmlp_zero(_p(t), t.numel() * t.element_size(), _stream()))
+    return t
+
+
+def topk_sync_timeouts():
+    """Re-alignment waits of the filter kernel that timed out on the current device so far."""
+    lib = _lib()
+    lib.dmlp_topk_sync_timeouts.argtypes = [C.POINTER(C.c_uint)]
+    out = C.c_uint(0)
+    _check(lib.dmlp_topk_sync_timeouts(C.byref(out)))
+    return int(out.value)

@@ -25,7 +25,6 @@ def _keys_from_topk(vals, idx, base):
 
 def run_baseline(eng):
     q_all, k_all = eng._gather_queries_nccl()                       # NCCL all-gather of operands
-    eng._range_stats()
     K.pack(eng.x, eng.stats, eng.stats, out=(eng.xh, eng.xn, eng.xe))
     K.pack(q_all, eng.stats, eng.q_stats, out=(eng.qh, eng.qn, eng.qe_))
     eng.launch_count += 2

@@ -20,6 +20,8 @@ impl = "fused"        the above, hand-written sm_100a kernels, peer-mapped symme
 impl = "nccl_cublas"  baseline variant: NCCL all-gathers, cuBLAS GEMM (torch.mm),
                       torch.topk, NCCL all-to-all of the lists.
 """
+import ctypes as C
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -59,7 +61,7 @@ class DistributedKNN:
                 if r == self.r:
                     self.row_group = g
         self.launch_count = 0
-        self.last_flagged = 0
+        self._flagged_host = None
         self.epoch = 0
         self.host = None
         self.sym = self.row_sym = None
@@ -125,9 +127,25 @@ class DistributedKNN:
                 self._alloc_symmetric(q_slice, k_slice)
             else:
                 self._alloc_plain(q_slice, k_slice)
+            # the repair pass of a step works on at most REPAIR_CAP flagged queries without the host
+            self.flagged_rows = torch.zeros(K.REPAIR_CAP, dtype=torch.int32, device=dev)
+            self.final = (torch.empty(max(self.qs, 1), dtype=torch.int32, device=dev),
+                          torch.empty(max(self.qs, 1), dtype=torch.int64, device=dev))
+            self._load_range()
             torch.cuda.synchronize(dev)
         if self.world > 1:
             dist.barrier()
+
+    def _load_range(self):
+        """Value range of everything that is resident -> common centring / scaling of the packed
+        rows on every rank.  Part of loading (the end-to-end path gets the range from the
+        loader the same way), not of a step: a step starts at the pack kernels."""
+        K.stats_reset(self.stats)
+        K.stats_reset(self.q_stats)
+        K.stats_update(self.x_part, self.stats)
+        K.stats_update(self.q_slice, self.stats)
+        if self.world > 1:
+            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX)
 
     def _alloc_shard(self, x_part, labels_part):
         """The data shard of this row: local when C == 1, otherwise a row-symmetric buffer
@@ -276,6 +294,7 @@ class DistributedKNN:
         for the query slice this rank owns (device tensors)."""
         with torch.cuda.device(self.device):
             self.epoch += 1
+            self._flagged_host = None
             self.tracer.begin_step()
             if self.rows_fused:
                 return self._run_rows_fused()
@@ -310,99 +329,120 @@ class DistributedKNN:
                     b += sz
                 dist.all_gather(outs, part.contiguous(), group=self.row_group)
 
-    def _range_stats(self):
-        """Value range of the data shard and queries -> common centring / scaling for
-        the ranks that exchange packed rows (one column)."""
-        K.stats_reset(self.stats)
-        K.stats_reset(self.q_stats)
-        K.stats_update(self.x, self.stats)
-        K.stats_update(self.q_slice, self.stats)
-        self.launch_count += 4
-        if self.R > 1:
-            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.col_group)
-
     def _pack_part_and_signal(self):
-        """rows_fused: pack this rank's part of the data shard into the row-symmetric buffer and
-        tell the row it is ready; the GEMM's communication warps fetch the other parts."""
+        """rows_fused: pack this rank's part of the data shard into the row-symmetric buffer; the
+        kernel itself first waits until every peer has finished pulling the previous step's copy
+        and its last block tells the row that the new rows are ready."""
         b, e = self.part_rows
-        K.pack(self.x_part, self.stats, None, out=(self.xh[b:e], self.xn[b:e], self.xe[b:e]))
-        self.row_sym.signal(self.row_pack_table, self.epoch)
-        self.data_gather.epoch = self.epoch
-        self.launch_count += 2
+        sym, ep = self.row_sym, self.epoch
+        K.pack_ex(self.x_part, self.stats, None, out=(self.xh[b:e], self.xn[b:e], self.xe[b:e]),
+                  wait=sym.wait_args("done_flags", ep - 1, self.status), signal=sym.signal_args("pack_flags", ep))
+        self.data_gather.epoch = ep
+        self._done_signal = sym.signal_args("done_flags", ep)       # sent by the GEMM's last block
+        self.data_gather.done_signal = C.cast(C.pointer(self._done_signal), C.c_void_p)
+        self.launch_count += 1
 
     def _run_rows_fused(self):
         """Grid 1 x C on resident inputs: the row all-gather of the data shard runs inside the
-        filter GEMM (packed rows just ahead of the tiles that need them, fp64 rows after)."""
+        filter GEMM (packed rows just ahead of the tiles that need them, fp64 rows after).  Seven
+        launches, every flag handled inside them, no NCCL call and no host synchronisation."""
         tr = self.tracer
         od, oi, ol, flags, nflag = self.lists
-        with tr.phase("stats"):
-            K.stats_reset(self.stats)
-            K.stats_reset(self.q_stats)
-            K.stats_update(self.x_part, self.stats)
-            K.stats_update(self.q_slice, self.stats)
-            dist.all_reduce(self.stats[:2], op=dist.ReduceOp.MAX, group=self.row_group)
-            self.launch_count += 4
         with tr.phase("pack"):
-            self._wait_part_readers(self.epoch - 1)   # peers may still be pulling the previous step's copy
             self._pack_part_and_signal()
             K.pack(self.q_slice, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
         with tr.phase("dist_topk+row_allgather"):
             K.dist_topk_rows(self.qh, self.shard_rows, self.cand, self.data_gather, kmax=self.kmax)
-            self.row_sym.signal(self.done_table, self.epoch)     # "I have finished reading your parts"
             K.maxima_from_norms(self.xn, self.xe, self.stats)
-        nflag.zero_()
-        with tr.phase("rerank"):
-            K.rerank(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
-                     self.stats, self.id_base, self.kmax, out=self.lists)
-        self.launch_count += 7
-        flagged = int(nflag.item())
-        if flagged:
-            rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)
-            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows, out=(od, oi, ol))
-            self.launch_count += 3
-        self.last_flagged = flagged
-        with tr.phase("finalize"):
-            return self._reduce_and_finalize_nccl(od, oi, ol)
+        K.zero_(nflag)
+        with tr.phase("rerank+vote"):
+            K.rerank_ex(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
+                        self.stats, self.id_base, self.kmax, flags, nflag, out=(od, oi, ol), final=self.final,
+                        flagged_rows=self.flagged_rows)
+        with tr.phase("repair"):
+            K.repair_flagged(self.q_slice, self.x, self.labels, self.k_slice, self.flagged_rows, nflag, self.id_base,
+                             self.kmax, out=(od, oi, ol), final=self.final)
+        self.launch_count += 9   # pack, dist_topk, maxima, rerank x3, repair x3
+        return self.final[0][:self.nq], self.final[1][:self.nq]
 
     def _run_peer_fused(self):
-        r0, tr = self.r * self.qs, self.tracer
-        with tr.phase("stats"):
-            self._range_stats()
+        """R > 1: K4 (the GEMM all-gathers the packed queries) + K5 (k-lists stored into the owners'
+        receive buffers; the last kernel that writes them signals, the owner's finalize waits)."""
+        r0, tr, ep = self.r * self.qs, self.tracer, self.epoch
         with tr.phase("pack"):
             K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
-            K.pack(self.q_slice, self.stats, self.q_stats,
-                   out=(self.qh[r0:r0 + self.nq], self.qn[r0:r0 + self.nq], self.qe_[r0:r0 + self.nq]))
-            self.sym.signal(self.pack_table, self.epoch)          # "my packed slice is ready"
-        self.gather.epoch = self.epoch
+            K.pack_ex(self.q_slice, self.stats, self.q_stats,
+                      out=(self.qh[r0:r0 + self.nq], self.qn[r0:r0 + self.nq], self.qe_[r0:r0 + self.nq]),
+                      signal=self.sym.signal_args("pack_flags", ep))   # "my packed slice is ready"
+        self.gather.epoch = ep
         with tr.phase("dist_topk+allgather"):
             K.dist_topk_gather(self.xh, self.xn, self.cand, self.gather, kmax=self.kmax)   # K4
-        self.nflag.zero_()
+        K.zero_(self.nflag)
         with tr.phase("rerank+scatter"):
-            K.rerank_scatter(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
-                             self.stats, self.id_base, self.kmax, self.flags, self.nflag, self.scatter)   # K5
-        self.launch_count += 7   # pack x2, signal, dist_topk, rerank x3
-        flagged = int(self.nflag.item())
-        if flagged:
-            self._repair_flagged()
-        self.last_flagged = flagged
+            K.rerank_ex(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
+                        self.stats, self.id_base, self.kmax, self.flags, self.nflag, scatter=self.scatter,
+                        flagged_rows=self.flagged_rows)   # K5 store side
+        with tr.phase("repair+signal"):
+            K.repair_flagged(self.q_all, self.x, self.labels, self.k_all, self.flagged_rows, self.nflag,
+                             self.id_base, self.kmax, scatter=self.scatter,
+                             signal=self.sym.signal_args("list_flags", ep))   # "my k-lists have landed everywhere"
         with tr.phase("wait_lists+finalize"):
-            self.sym.signal(self.list_table, self.epoch)          # "my k-lists have landed everywhere"
-            self.sym.wait("list_flags", self.epoch, self.status)
-            label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2],
-                                               self.k_all[r0:r0 + self.qs])
-        self.launch_count += 3
-        return label[:self.nq], checksum[:self.nq]
+            K.finalize_ex(self.recv[0], self.recv[1], self.recv[2], self.k_all[r0:r0 + self.qs], out=self.final,
+                          wait=self.sym.wait_args("list_flags", ep, self.status))
+        self.launch_count += 9   # pack x2, dist_topk, rerank x3, repair x2, finalize
+        return self.final[0][:self.nq], self.final[1][:self.nq]
 
-    def _repair_flagged(self):
-        """Queries the filter could not certify: exact kernel, then store their lists
-        into the owners' receive buffers through the peer mappings."""
+    def _nflag_tensor(self):
+        return self.nflag if self.peer_fused else self.lists[4]
+
+    @property
+    def last_flagged(self):
+        """Queries of the last step the filter could not certify.  The fused steps keep the count
+        on the device (this reads it, which synchronises); the library-plumbed paths know it."""
+        if self._flagged_host is not None:
+            return self._flagged_host
+        if not getattr(self, "fused_ok", False):
+            return 0
+        return int(self._nflag_tensor().sum().item())
+
+    @last_flagged.setter
+    def last_flagged(self, value):
+        self._flagged_host = value
+
+    def ensure_repaired(self):
+        """End-of-step check: up to REPAIR_CAP flagged queries are repaired on the device by the step
+        itself; only beyond that (never seen on the generator's distributions) the host steps in,
+        re-runs every flagged query on the direct kernel and finalizes again.  Returns the count."""
+        flagged = self.last_flagged
+        worst = flagged
+        if self.peer_fused:   # the ranks of a column repair together or not at all
+            t = torch.tensor([flagged], dtype=torch.int32, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.col_group)
+            worst = int(t.item())
+        if worst <= K.REPAIR_CAP:
+            return flagged
+        if self.peer_fused:
+            self._repair_flagged_host()
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.col_group)
+            r0 = self.r * self.qs
+            K.finalize_ex(self.recv[0], self.recv[1], self.recv[2], self.k_all[r0:r0 + self.qs], out=self.final)
+        else:
+            od, oi, ol, flags, _ = self.lists
+            rows = torch.nonzero(flags[: self.nq], as_tuple=False).flatten().to(torch.int32)
+            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows, out=(od, oi, ol))
+            K.finalize_ex(od[None], oi[None], ol[None], self.k_slice, out=self.final)
+        return flagged
+
+    def _repair_flagged_host(self):
+        """More flagged queries than the step repairs by itself: exact kernel over all of them, then
+        their lists go into the owners' receive buffers through the peer mappings."""
         rows = torch.nonzero(self.flags, as_tuple=False).flatten()
         km = self.kmax
         tmp = (torch.empty((self.qp, km), dtype=torch.float64, device=self.device),
                torch.empty((self.qp, km), dtype=torch.int32, device=self.device),
                torch.empty((self.qp, km), dtype=torch.int32, device=self.device))
         K.exact(self.q_all, self.x, self.labels, self.k_all, km, self.id_base, rows.to(torch.int32), out=tmp)
-        self.launch_count += 3
         owners = rows // self.qs
         for o in torch.unique(owners).tolist():
             sel = rows[owners == o]
@@ -424,18 +464,34 @@ class DistributedKNN:
 
     def _run_local_or_nccl(self):
         tr = self.tracer
+        od, oi, ol, flags, nflag = self.lists
+        if self.fused_ok and self.R == 1:
+            # one data shard: pack, filter, re-rank with the vote folded in, device-side repair --
+            # eight launches, nothing for the host to wait on
+            with tr.phase("pack"):
+                K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+                K.pack(self.q_slice, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
+            with tr.phase("dist_topk"):
+                K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand, kmax=self.kmax)
+            K.zero_(nflag)
+            with tr.phase("rerank+vote"):
+                K.rerank_ex(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
+                            self.stats, self.id_base, self.kmax, flags, nflag, out=(od, oi, ol), final=self.final,
+                            flagged_rows=self.flagged_rows)
+            with tr.phase("repair"):
+                K.repair_flagged(self.q_slice, self.x, self.labels, self.k_slice, self.flagged_rows, nflag,
+                                 self.id_base, self.kmax, out=(od, oi, ol), final=self.final)
+            self.launch_count += 9   # pack x2, dist_topk, rerank x3, repair x3
+            return self.final[0][:self.nq], self.final[1][:self.nq]
         with tr.phase("query_gather"):
             q_all, k_all = self._gather_queries_nccl()
-        with tr.phase("stats"):
-            self._range_stats()
-        od, oi, ol, flags, nflag = self.lists
         if self.fused_ok:
             with tr.phase("pack"):
                 K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
                 K.pack(q_all, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
             with tr.phase("dist_topk"):
                 K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand, kmax=self.kmax)
-            nflag.zero_()
+            K.zero_(nflag)
             with tr.phase("rerank"):
                 K.rerank(self.cand, q_all, self.x, self.labels, k_all, self.qn, self.qe_, self.stats, self.stats,
                          self.id_base, self.kmax, out=self.lists)
@@ -444,11 +500,11 @@ class DistributedKNN:
             if flagged:
                 rows = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)
                 K.exact(q_all, self.x, self.labels, k_all, self.kmax, self.id_base, rows, out=(od, oi, ol))
-                self.launch_count += 3
+                self.launch_count += 2
             self.last_flagged = flagged
         else:
             K.exact(q_all, self.x, self.labels, k_all, self.kmax, self.id_base, out=(od, oi, ol))
-            self.launch_count += 3
+            self.launch_count += 2
         with tr.phase("reduce+finalize"):
             return self._reduce_and_finalize_nccl(od, oi, ol)
 
@@ -456,15 +512,15 @@ class DistributedKNN:
         """k-lists of every data shard -> owner of the query slice -> merge, vote, checksum."""
         R, qs, km = self.R, self.qs, self.kmax
         if R == 1:
-            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
+            K.finalize_ex(od[None], oi[None], ol[None], self.k_slice, out=self.final)
             self.launch_count += 1
-            return label, checksum
+            return self.final[0][:self.nq], self.final[1][:self.nq]
         for src, dst in zip((od, oi, ol), self.recv):
             dist.all_to_all_single(dst.view(R * qs, km), src.view(R * qs, km), group=self.col_group)
         mine = self.k_all[self.r * qs:(self.r + 1) * qs]
-        label, checksum, _, _ = K.finalize(self.recv[0], self.recv[1], self.recv[2], mine)
+        K.finalize_ex(self.recv[0], self.recv[1], self.recv[2], mine, out=self.final)
         self.launch_count += 1
-        return label[:self.nq], checksum[:self.nq]
+        return self.final[0][:self.nq], self.final[1][:self.nq]
 
     # ---------------------------------------------------------------- end to end
     E2E_CHUNK_ROWS = 18944   # 74 cluster rows of 256 queries: whole waves of the filter GEMM
@@ -514,6 +570,11 @@ class DistributedKNN:
             if use_dec:
                 self.x_wire = torch.empty(self.x_part.shape, dtype=torch.int32, device=dev)
                 self.q_wire = [torch.empty((rows, self.a), dtype=torch.int32, device=dev) for _ in range(2)]
+            nchunks = max(1, -(-max(self.nq, 1) // rows))
+            self.nflag_chunks = torch.zeros(nchunks, dtype=torch.int32, device=dev)
+            self.flagged_rows_chunks = torch.zeros((nchunks, K.REPAIR_CAP), dtype=torch.int32, device=dev)
+            self.host_nflag = torch.zeros(nchunks, dtype=torch.int32).pin_memory()
+            self.d2h_bytes_per_step += self.host_nflag.numel() * 4
             self._cand_by_rows = {}
             self.x_parts = max(1, int(os.environ.get("DMLP_E2E_XPARTS", "4")))
             if self.shard_rows < 4096 * self.x_parts:
@@ -526,6 +587,7 @@ class DistributedKNN:
         With a single-rank column the copy of the next query chunk overlaps the
         kernels of the current one (two streams)."""
         with torch.cuda.device(self.device):
+            self._flagged_host = None
             if getattr(self, "streamed", False) and self.world == 1 and self.x_parts > 1:
                 label, checksum = self._run_tiled()
             elif getattr(self, "streamed", False):
@@ -534,8 +596,35 @@ class DistributedKNN:
                 label, checksum = self._run_copy_then_compute()
             self.host_out[0].copy_(label, non_blocking=True)
             self.host_out[1].copy_(checksum, non_blocking=True)
+            streamed = getattr(self, "streamed", False)
+            counted = self._flagged_host is None and self.fused_ok and self.impl == "fused"
+            if counted and streamed:
+                self.host_nflag.copy_(self.nflag_chunks, non_blocking=True)
+            elif counted:
+                self.host_nflag[:1].copy_(self._nflag_tensor(), non_blocking=True)
             torch.cuda.current_stream().synchronize()
+            if counted:
+                worst = int(self.host_nflag.max()) if streamed else int(self.host_nflag[0])
+                self._flagged_host = int(self.host_nflag.sum()) if streamed else worst
+                if worst > K.REPAIR_CAP:   # beyond what the step repairs by itself (not seen in practice)
+                    self._flagged_host = None
+                    self.ensure_repaired()
+                    self.host_out[0].copy_(self.final[0][:self.nq])
+                    self.host_out[1].copy_(self.final[1][:self.nq])
             return self.host_out
+
+    def _rerank_chunk(self, i, b, e, cand):
+        """Re-rank + folded vote + device-side repair of query rows [b, e) (chunk i of a streamed step)."""
+        od, oi, ol, flags, _ = self.lists
+        nf, rows = self.nflag_chunks[i:i + 1], self.flagged_rows_chunks[i]
+        out = (od[b:e], oi[b:e], ol[b:e])
+        fin = (self.final[0][b:e], self.final[1][b:e])
+        K.rerank_ex(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], self.qn[b:e], self.qe_[b:e],
+                    self.stats, self.stats, self.id_base, self.kmax, flags[b:e], nf, out=out, final=fin,
+                    flagged_rows=rows)
+        K.repair_flagged(self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], rows, nf, self.id_base, self.kmax,
+                         out=out, final=fin)
+        self.launch_count += 6
 
     def _wait_part_readers(self, upto=None):
         """Before this rank's part of the data shard is overwritten: every rank of the row
@@ -607,7 +696,7 @@ class DistributedKNN:
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
-        nflag.zero_()
+        K.zero_(self.nflag_chunks)
         self.launch_count += 2
         have_x, have_q = set(), set()
         done, reranked = set(), set()
@@ -656,21 +745,9 @@ class DistributedKNN:
                     self.launch_count += 1
                 if i not in reranked and all((i, p_) in done for p_ in range(len(xparts))):
                     main.wait_event(e_small)
-                    K.rerank(cands[i], self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], self.qn[b:e],
-                             self.qe_[b:e], self.stats, self.stats, self.id_base, self.kmax,
-                             out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
+                    self._rerank_chunk(i, b, e, cands[i])
                     reranked.add(i)
-                    self.launch_count += 3
-        label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-        self.launch_count += 1
-        flagged = int(nflag.item())
-        if flagged:
-            rows_f = torch.nonzero(flags[: self.nq], as_tuple=False).flatten().to(torch.int32)
-            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows_f, out=(od, oi, ol))
-            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-            self.launch_count += 4
-        self.last_flagged = flagged
-        return label, checksum
+        return self.final[0][:self.nq], self.final[1][:self.nq]
 
     def _run_streamed(self):
         h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream
@@ -701,8 +778,7 @@ class DistributedKNN:
         else:
             self._gather_shard()
             K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
-        od, oi, ol, flags, nflag = self.lists
-        nflag.zero_()
+        K.zero_(self.nflag_chunks)
         self.launch_count += 4 + (1 if dec else 0)
         for i, (b, e) in enumerate(chunks):
             with torch.cuda.stream(cs):
@@ -728,29 +804,21 @@ class DistributedKNN:
             cand = self._cand_by_rows[key]
             if gather_pending:      # the first GEMM of the step also gathers the data shard
                 K.dist_topk_rows(qh, self.shard_rows, cand, self.data_gather, kmax=self.kmax)
-                self.row_sym.signal(self.done_table, self.epoch)
                 K.maxima_from_norms(self.xn, self.xe, self.stats)
                 gather_pending = False
-                self.launch_count += 2
+                self.launch_count += 1
             else:
                 K.dist_topk(qh, self.xh, self.xn, cand=cand, kmax=self.kmax)
-            K.rerank(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], qn, qe, self.stats, self.stats,
-                     self.id_base, self.kmax, out=(od[b:e], oi[b:e], ol[b:e], flags[b:e], nflag))
-            self.launch_count += 5 + (1 if dec else 0)
-        label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-        self.launch_count += 1
-        flagged = int(nflag.item())
-        if flagged:
-            rows_f = torch.nonzero(flags[:nq], as_tuple=False).flatten().to(torch.int32)
-            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows_f, out=(od, oi, ol))
-            label, checksum, _, _ = K.finalize(od[None], oi[None], ol[None], self.k_slice)
-            self.launch_count += 4
-        self.last_flagged = flagged
-        return label, checksum
+            self._rerank_chunk(i, b, e, cand)
+            self.launch_count += 2 + (1 if dec else 0)
+        return self.final[0][:self.nq], self.final[1][:self.nq]
 
     def check_watchdog(self):
-        """Non-zero means a peer signal timed out somewhere."""
-        return int(self.status.item())
+        """Non-zero means a device-side wait gave up somewhere: a positive code names
+        the peer signal that never came, a negative one counts re-alignment waits of the filter
+        kernel that timed out (results stay correct, the sweep lost its L2 sharing)."""
+        st = int(self.status.item())
+        return st if st else -K.topk_sync_timeouts()
 
     def close(self):
         for s in (self.sym, self.row_sym):
@@ -759,11 +827,96 @@ class DistributedKNN:
         self.sym = self.row_sym = None
 
     # -------------------------------------------------------------- verification
+    def verify_sampled(self, n_exact=64, n_cpu=4, seed=1234):
+        """Check the results of the last run_resident() on sampled queries, at any problem size.
+
+        * `n_exact` queries per rank against the independent direct fp64 kernel (exact.cu) on this
+          rank's data shard; with several data shards the sampled queries' local lists are
+          all-gathered along the column (a few KB) and merged, and each owner compares its own.
+        * `n_cpu` queries against the CPU oracle, driven from rank 0's column only: every rank
+          of that column runs the CPU twin on its own shard (one device-to-host copy of the
+          shard it already holds), rank 0 merges, votes and compares.  Nothing gathers the
+          whole dataset anywhere.
+        Raises AssertionError on any mismatch; returns the number of (query, check) pairs that
+        passed, summed over all ranks."""
+        from ..ops import cpu
+        self.ensure_repaired()
+        torch.cuda.synchronize(self.device)
+        dev, R, km = self.device, self.R, self.kmax
+        fin_label, fin_sum = self.final[0][:self.nq].cpu().numpy(), self.final[1][:self.nq].cpu().numpy()
+        gen = np.random.default_rng(seed + 7919 * self.c)            # the ranks of a column draw the same sample
+        counts = [even_slice(self.q_col, R, r)[1] - even_slice(self.q_col, R, r)[0] for r in range(R)]
+
+        def sample(count):
+            owners = gen.choice([r for r in range(R) if counts[r] > 0], size=count)
+            local = np.array([gen.integers(0, counts[o]) for o in owners], dtype=np.int64)
+            return owners, local
+
+        passed = 0
+        if self.q_col > 0 and n_exact > 0:
+            owners, local = sample(n_exact)
+            if R == 1:
+                q_rows, k_rows = self.q_slice, self.k_slice
+                rows = torch.from_numpy(local.astype(np.int32)).to(dev)
+            else:   # padded column index space: owner * qs + local row
+                q_rows, k_rows = self.q_all, self.k_all
+                rows = torch.from_numpy((owners * self.qs + local).astype(np.int32)).to(dev)
+            kk = k_rows[rows.long()].contiguous()
+            qsel = q_rows[rows.long()].contiguous()
+            od, oi, ol = K.exact(qsel, self.x, self.labels, kk, km, self.id_base)
+            if R > 1:
+                parts = [[torch.empty_like(t) for _ in range(R)] for t in (od, oi, ol)]
+                for t, outs in zip((od, oi, ol), parts):
+                    dist.all_gather(outs, t, group=self.col_group)
+                od, oi, ol = (torch.stack(p) for p in parts)
+            else:
+                od, oi, ol = od[None], oi[None], ol[None]
+            label, checksum, _, _ = K.finalize(od, oi, ol, kk)
+            label, checksum = label.cpu().numpy(), checksum.cpu().numpy()
+            for j in range(len(local)):
+                if owners[j] != self.r:
+                    continue
+                if label[j] != fin_label[local[j]] or checksum[j] != fin_sum[local[j]]:
+                    raise AssertionError(f"rank {self.rank}: query {local[j]} of this rank differs from the direct "
+                                         f"fp64 kernel (label {fin_label[local[j]]} vs {label[j]})")
+                passed += 1
+        if self.c == 0 and self.q_col > 0 and n_cpu > 0:
+            owners, local = sample(n_cpu)
+            if R == 1:
+                qsel, ksel = self.q_slice[local].cpu().numpy(), self.k_slice[local].cpu().numpy()
+            else:
+                idx = torch.from_numpy(owners * self.qs + local).to(dev)
+                qsel, ksel = self.q_all[idx].cpu().numpy(), self.k_all[idx].cpu().numpy()
+            lists = cpu.local_lists(self.x.cpu().numpy(), self.labels.cpu().numpy(), self.id_base, qsel, ksel, km)
+            mine = {int(j): (int(fin_label[local[j]]), int(fin_sum[local[j]])) for j in range(n_cpu)
+                    if owners[j] == self.r}
+            if R > 1:
+                gathered = [None] * R if self.r == 0 else None
+                dist.gather_object((lists, mine), gathered, dst=self.grid.column_ranks(0)[0], group=self.col_group)
+            else:
+                gathered = [(lists, mine)]
+            if self.r == 0:
+                d, i, l = (np.stack([g[0][t] for g in gathered]) for t in range(3))
+                want_label, want_sum = cpu.finalize_lists(d, i, l, ksel)
+                got = {}
+                for g in gathered:
+                    got.update(g[1])
+                for j in range(n_cpu):
+                    if got[j] != (int(want_label[j]), int(want_sum[j].view(np.int64))):
+                        raise AssertionError(f"query {local[j]} of row {owners[j]} differs from the CPU oracle: "
+                                             f"{got[j]} vs {(int(want_label[j]), int(want_sum[j].view(np.int64)))}")
+                    passed += 1
+        t = torch.tensor([passed], dtype=torch.int64, device=dev)
+        if self.world > 1:
+            dist.all_reduce(t)
+        return int(t.item())
+
     def verify_against_oracle(self, count):
         """Re-derive the first `count` owned queries on the CPU oracle (gathers the whole
         dataset on the host: only sensible for small problems)."""
         from ..ops import cpu
         label, checksum = self.run_resident()
+        self.ensure_repaired()
         torch.cuda.synchronize(self.device)
         if self.world > 1:
             parts = [None] * self.world     # parts differ in size: exchange as objects

@@ -104,6 +104,32 @@ class SymmetricBuffer:
                                      C.c_void_p(status.data_ptr() if status is not None else 0),
                                      C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
+    # -- in-kernel signalling: argument blocks for the kernels that carry the flag protocol themselves
+    def signal_args(self, name, value):
+        """`signal` block for a kernel launch: when the launch has finished, its last block stores
+        `value` into this rank's word of region `name` (a flag array) in every rank's buffer."""
+        from ..ops.cuda import SignalArgs
+        if not hasattr(self, "_done_counters"):
+            self._done_counters, self._next_counter = torch.zeros(64, dtype=torch.int32, device=self.device), {}
+        slot = self._next_counter.setdefault(name, len(self._next_counter))   # one counter per flag array
+        sg = SignalArgs()
+        off = self.layout.off[name]
+        for r, ptr in enumerate(self.peer_ptrs):
+            sg.peer_flags[r] = ptr + off
+        sg.world, sg.rank, sg.value = self.world, self.rank, value
+        sg.done_counter = self._done_counters.data_ptr() + 4 * slot
+        return sg
+
+    def wait_args(self, name, value, status=None, timeout=20.0):
+        """`wait` block for a kernel launch: every block first spins until all words of the local
+        flag array `name` have reached `value`."""
+        from ..ops.cuda import WaitArgs
+        wa = WaitArgs()
+        wa.flags = self.local_ptr + self.layout.off[name]
+        wa.world, wa.value, wa.timeout_seconds = self.world, value, timeout
+        wa.status = status.data_ptr() if status is not None else 0
+        return wa
+
     def close(self):
         lib = _lib()
         torch.cuda.synchronize(self.device)

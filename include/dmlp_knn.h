@@ -222,6 +222,8 @@ typedef struct dmlp_data_gather_args {
   uint32_t *tile_count;
   int *status;
   double timeout_seconds;
+  const struct dmlp_signal_args *done_signal;  /* optional: "I have finished reading your parts", stored by
+                                                  the kernel's last block (see dmlp_signal_args below) */
 } dmlp_data_gather_args;
 int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms, int kmax, uint64_t *cand,
                         const dmlp_data_gather_args *g, void *stream);
@@ -243,6 +245,113 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
                         const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
                         int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *workspace,
                         size_t workspace_bytes, void *stream);
+
+/* ---- struct-based forms of the re-rank and of the repair pass -----------------------
+ * dmlp_rerank_ex is dmlp_rerank / dmlp_rerank_scatter with the optional extras:
+ *   final_label / final_checksum  (single data shard only, scatter == NULL): the emit kernel
+ *       also votes and folds the checksum, so no dmlp_finalize launch is needed (K6 fused
+ *       into K2; reference: engine.cpp:320-347, common.cpp:59-68);
+ *   flagged_rows / flagged_cap    the indices of the queries the filter could not certify,
+ *       in the order they bumped *num_flagged (entries beyond flagged_cap are dropped);
+ *   signal                        K5: when the whole launch has finished, store `value` into
+ *       this rank's word of every peer's flag array (release at system scope), from inside
+ *       the kernel -- no separate signal launch.
+ * dmlp_repair_flagged re-runs the first min(*num_flagged, cap) of those rows on the direct
+ * fp64 kernel and overwrites their lists (locally or, with scatter, in the owners' receive
+ * buffers); with final_label set it also re-finalizes those rows.  The count stays on the
+ * device: the pass is enqueued unconditionally and does nothing when no query was flagged,
+ * so a step needs no host synchronisation in the middle.  If *num_flagged > cap the caller
+ * must handle the rest (check the counter once the step is over).
+ * Workspace: dmlp_exact_workspace_bytes(n, cap, kmax). */
+/* dmlp_pack with the two ends of a flag protocol folded in: the kernel first waits (wait, may be
+ * NULL) until every peer has finished reading the rows it is about to overwrite, and its last
+ * block announces the new rows (signal, may be NULL).  rows == 0 still signals. */
+struct dmlp_signal_args;
+struct dmlp_wait_args;
+int dmlp_pack_ex(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
+                 float *errn, void *maxima, const struct dmlp_wait_args *wait, const struct dmlp_signal_args *signal,
+                 void *stream);
+/* cudaMemsetAsync(ptr, 0, bytes) on the stream (counters, flags) without a library kernel. */
+int dmlp_zero(void *ptr, size_t bytes, void *stream);
+
+typedef struct dmlp_signal_args {
+  void *peer_flags[8];     /* every rank's flag array as mapped here; word `rank` is written */
+  int world, rank;
+  uint32_t value;
+  uint32_t *done_counter;  /* local device word, zero at set-up; counts finished blocks and resets itself */
+} dmlp_signal_args;
+
+/* The receiving side of `signal`: the kernel spins (acquire, system scope) until every one of the
+ * `world` words of the local flag array has reached `value` before it touches what the peers
+ * wrote; after timeout_seconds it writes 600 + the late rank to *status and carries on. */
+typedef struct dmlp_wait_args {
+  const uint32_t *flags;
+  int world;
+  uint32_t value;
+  double timeout_seconds;
+  int *status;
+} dmlp_wait_args;
+
+typedef struct dmlp_rerank_args {
+  const uint64_t *cand;
+  int chunks, kp;
+  const double *q_attrs, *x_attrs;
+  const int *x_labels, *k;
+  const float *q_norm2, *q_errn;
+  const void *range, *x_maxima;
+  int q, n, a, a_pad, id_base, kmax;
+  double *out_dist;
+  int *out_id, *out_label;
+  int *flags, *num_flagged;
+  int *flagged_rows;
+  int flagged_cap;
+  int *final_label;
+  uint64_t *final_checksum;
+  const dmlp_scatter_args *scatter;
+  const dmlp_signal_args *signal;
+  void *workspace;
+  size_t workspace_bytes;
+} dmlp_rerank_args;
+int dmlp_rerank_ex(const dmlp_rerank_args *r, void *stream);
+
+typedef struct dmlp_repair_args {
+  const double *q_attrs, *x_attrs;
+  const int *x_labels, *k;
+  const int *flagged_rows, *num_flagged;
+  int cap;
+  int q, n, a, id_base, kmax;
+  double *out_dist;
+  int *out_id, *out_label;
+  int *final_label;
+  uint64_t *final_checksum;
+  const dmlp_scatter_args *scatter;
+  const dmlp_signal_args *signal;
+  void *workspace;
+  size_t workspace_bytes;
+} dmlp_repair_args;
+int dmlp_repair_flagged(const dmlp_repair_args *r, void *stream);
+
+/* dmlp_finalize with the extras: `wait` (K5 owner side: the lists come from the peers, see
+ * dmlp_signal_args; no separate wait launch), and a row subset whose length may live on the
+ * device (query_rows / count / count_dev, e.g. the repaired rows of this step). */
+typedef struct dmlp_finalize_args {
+  const double *dist;
+  const int *id, *label;
+  int64_t source_stride;
+  int sources, q, kmax;
+  const int *k;
+  int *out_label;
+  uint64_t *out_checksum;
+  int *out_id;
+  double *out_dist;
+  const int *query_rows;
+  int count;
+  const int *count_dev;
+  const dmlp_wait_args *wait;
+  void *workspace;
+  size_t workspace_bytes;
+} dmlp_finalize_args;
+int dmlp_finalize_ex(const dmlp_finalize_args *f, void *stream);
 
 /* ---- the same pipeline for callers that cannot allocate -------------------------
  * (No counterpart in the reference: it has no GPU code and no scratch buffers.)

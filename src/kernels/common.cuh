@@ -231,6 +231,45 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
          | (static_cast<uint32_t>(m >> 4) << 24);  // M / 16
 }
 
+// ---------------------------------------------------------------------------
+// Cross-GPU signalling from inside a kernel (see SignalArgs / WaitArgs in kernels.h).
+// Both helpers contain a block-wide barrier: every thread of the block must call them.
+// ---------------------------------------------------------------------------
+template <class SignalT>
+__device__ __forceinline__ void signal_peers_when_grid_done(const SignalT &sg) {
+  if (sg.world <= 0) return;
+  __threadfence_system();  // this thread's stores (peer memory included) precede the arrival below
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned blocks = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned prev = atomicAdd(sg.done_counter, 1u);
+    if (prev == blocks - 1) {  // the last block of the launch
+      *sg.done_counter = 0;    // ready for the next launch on this stream
+      __threadfence_system();
+      for (int d = 0; d < sg.world; ++d)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sg.peer_flags[d] + sg.rank), "r"(sg.value) : "memory");
+    }
+  }
+}
+template <class WaitT>
+__device__ __forceinline__ void wait_for_peers(const WaitT &wa) {
+  if (wa.world <= 0) return;
+  if (static_cast<int>(threadIdx.x) < wa.world) {
+    const long long t0 = clock64();
+    for (;;) {
+      unsigned v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(wa.flags + threadIdx.x) : "memory");
+      if (static_cast<int>(v - wa.value) >= 0) break;
+      if (clock64() - t0 > wa.timeout_cycles) {  // watchdog: a lost signal must not hang the GPU
+        if (wa.status) atomicExch(wa.status, 600 + static_cast<int>(threadIdx.x));
+        break;
+      }
+      __nanosleep(200);
+    }
+  }
+  __syncthreads();
+}
+
 __device__ __forceinline__ void named_barrier_sync(uint32_t id, uint32_t threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }

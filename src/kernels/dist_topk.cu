@@ -944,6 +944,9 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
   }
+  // fused row all-gather: once every CTA's communication warp is through, tell the row's peers
+  // that their parts may be overwritten ("done reading")
+  signal_peers_when_grid_done(dg.done);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,

@@ -41,7 +41,7 @@ __host__ __device__ inline int list_stride(int kmax) { return pow2_at_least(2 * 
 
 struct ScanArgs {
   const double *q_attrs, *x_attrs;
-  const int *k, *query_rows;
+  const int *k, *query_rows, *count_dev;
   int qbase, count, n, a, kmax, splits, stride;
   double *l_dist;  // [count][splits][stride]
   int *l_id;       // same shape
@@ -99,6 +99,12 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
   const int tid = threadIdx.x;
   const int b0 = blockIdx.x * EX_QB;
   const int split = blockIdx.y;
+  int count = a.count;
+  if (a.count_dev != nullptr) {
+    const int c = *a.count_dev - a.qbase;
+    count = c < count ? (c > 0 ? c : 0) : count;
+  }
+  if (b0 >= count) return;  // (uniform over the CTA)
   const int r_begin = static_cast<int>(static_cast<long long>(split) * a.n / a.splits);
   const int r_end = static_cast<int>(static_cast<long long>(split + 1) * a.n / a.splits);
   const int xr = tid % EX_XR;
@@ -107,7 +113,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
   if (tid < EX_QB) {
     const int b = b0 + tid;
     int kq = 0, row = 0;
-    if (b < a.count) {
+    if (b < count) {
       row = a.query_rows ? a.query_rows[a.qbase + b] : a.qbase + b;
       kq = a.k[row];
       kq = kq < 0 ? 0 : (kq > a.kmax ? a.kmax : kq);
@@ -152,7 +158,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
       for (int i = tid; i < EX_QB * EX_CH; i += EX_THREADS) {
         const int r = i / EX_CH, c = i - r * EX_CH;
         const int col = c0 + c;
-        qs[r][c] = (b0 + r < a.count && col < a.a) ? a.q_attrs[static_cast<long long>(s_row[r]) * a.a + col] : 0.0;
+        qs[r][c] = (b0 + r < count && col < a.a) ? a.q_attrs[static_cast<long long>(s_row[r]) * a.a + col] : 0.0;
       }
       __syncthreads();
 #pragma unroll 4
@@ -172,7 +178,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
       for (int j = 0; j < 4; ++j) {
         const int qi = qg * 4 + j;
         // "<=": an equal distance with a larger id still beats the current k-th best
-        if (b0 + qi < a.count && acc[j] <= s_thr[qi]) {
+        if (b0 + qi < count && acc[j] <= s_thr[qi]) {
           const int slot = atomicAdd(&s_cnt[qi], 1);
           list_d(qi)[slot] = acc[j];
           list_i(qi)[slot] = row;
@@ -183,7 +189,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
   }
   // leave every list sorted and cut to k
   for (int qi = 0; qi < EX_QB; ++qi) {
-    if (b0 + qi >= a.count) break;
+    if (b0 + qi >= count) break;
     compact(qi);
     if (tid == 0) a.l_cnt[static_cast<long long>(b0 + qi) * a.splits + split] = s_cnt[qi];
   }
@@ -192,20 +198,28 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
 struct MergeArgs {
   const double *l_dist;
   const int *l_id, *l_cnt;
-  const int *x_labels, *k, *query_rows;
+  const int *x_labels, *k, *query_rows, *count_dev;
+  ScatterArgs scatter;
+  SignalArgs signal;
   int qbase, count, splits, stride, id_base, kmax;
   double *out_dist;
   int *out_id, *out_label;
 };
 
-__global__ void __launch_bounds__(128) exact_merge_kernel(const MergeArgs a) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * 4 + warp;
-  if (b >= a.count) return;
+__device__ __forceinline__ void merge_query(const MergeArgs &a, int b, int lane) {
   const int qrow = a.query_rows ? a.query_rows[a.qbase + b] : a.qbase + b;
   int kq = a.k[qrow];
   kq = kq < 0 ? 0 : (kq > a.kmax ? a.kmax : kq);
-  const long long o = static_cast<long long>(qrow) * a.kmax;
+  long long o = static_cast<long long>(qrow) * a.kmax;
+  double *out_dist = a.out_dist;
+  int *out_id = a.out_id, *out_label = a.out_label;
+  if (a.scatter.world > 1) {  // K5: straight into the owner's receive buffer
+    const int owner = qrow / a.scatter.slice_rows;
+    o = (static_cast<long long>(a.scatter.rank) * a.scatter.slice_rows + (qrow - owner * a.scatter.slice_rows)) * a.kmax;
+    out_dist = reinterpret_cast<double *>(a.scatter.peer_base[owner] + a.scatter.off_dist);
+    out_id = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_id);
+    out_label = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_label);
+  }
   const double *ld = a.l_dist + static_cast<long long>(b) * a.splits * a.stride;
   const int *li = a.l_id + static_cast<long long>(b) * a.splits * a.stride;
   const int *lc = a.l_cnt + static_cast<long long>(b) * a.splits;
@@ -213,9 +227,9 @@ __global__ void __launch_bounds__(128) exact_merge_kernel(const MergeArgs a) {
   for (int s = 0; s < a.splits; ++s) total += lc[s];
   const int filled = total < kq ? total : kq;
   for (int i = filled + lane; i < a.kmax; i += 32) {
-    a.out_dist[o + i] = 1e18;
-    a.out_id[o + i] = -1;
-    a.out_label[o + i] = -1;
+    out_dist[o + i] = 1e18;
+    out_id[o + i] = -1;
+    out_label[o + i] = -1;
   }
   for (int s = 0; s < a.splits; ++s) {
     const int len = lc[s];
@@ -228,12 +242,24 @@ __global__ void __launch_bounds__(128) exact_merge_kernel(const MergeArgs a) {
           rank += entries_before(ld + static_cast<long long>(t) * a.stride, li + static_cast<long long>(t) * a.stride,
                                  lc[t], d, id);
       if (rank < kq) {
-        a.out_dist[o + rank] = d;
-        a.out_id[o + rank] = a.id_base + id;
-        a.out_label[o + rank] = a.x_labels[id];
+        out_dist[o + rank] = d;
+        out_id[o + rank] = a.id_base + id;
+        out_label[o + rank] = a.x_labels[id];
       }
     }
   }
+}
+
+__global__ void __launch_bounds__(128) exact_merge_kernel(const MergeArgs a) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 4 + warp;
+  int count = a.count;
+  if (a.count_dev != nullptr) {
+    const int c = *a.count_dev - a.qbase;
+    count = c < count ? (c > 0 ? c : 0) : count;
+  }
+  if (b < count) merge_query(a, b, lane);
+  signal_peers_when_grid_done(a.signal);  // (K5) the repaired lists have been stored as well
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -293,6 +319,7 @@ int launch_exact(const ExactArgs &args, cudaStream_t s) {
     const int cnt = args.count - base < batch ? args.count - base : batch;
     ScanArgs sa;
     sa.q_attrs = args.q_attrs; sa.x_attrs = args.x_attrs; sa.k = args.k; sa.query_rows = args.query_rows;
+    sa.count_dev = args.count_dev;
     sa.qbase = base; sa.count = cnt; sa.n = args.n; sa.a = args.a; sa.kmax = args.kmax;
     sa.splits = splits; sa.stride = stride;
     sa.l_dist = l_dist; sa.l_id = l_id; sa.l_cnt = l_cnt;
@@ -302,6 +329,8 @@ int launch_exact(const ExactArgs &args, cudaStream_t s) {
     MergeArgs ma;
     ma.l_dist = l_dist; ma.l_id = l_id; ma.l_cnt = l_cnt;
     ma.x_labels = args.x_labels; ma.k = args.k; ma.query_rows = args.query_rows;
+    ma.count_dev = args.count_dev; ma.scatter = args.scatter;
+    if (base + cnt >= args.count) ma.signal = args.signal;  // only the last batch announces completion
     ma.qbase = base; ma.count = cnt; ma.splits = splits; ma.stride = stride;
     ma.id_base = args.id_base; ma.kmax = args.kmax;
     ma.out_dist = args.out_dist; ma.out_id = args.out_id; ma.out_label = args.out_label;

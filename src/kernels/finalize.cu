@@ -25,8 +25,15 @@ constexpr int FIN_SMEM_K = 2048;  // merged lists up to this k are staged in sha
 __global__ void __launch_bounds__(FIN_WARPS * 32) finalize_kernel(const FinalizeArgs a) {
   extern __shared__ __align__(16) unsigned char fin_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * FIN_WARPS + warp;
-  if (q >= a.q) return;
+  wait_for_peers(a.wait);  // (K5) the lists of the other data shards land through NVLink
+  int q = blockIdx.x * FIN_WARPS + warp;
+  if (a.query_rows != nullptr) {  // a subset of the rows, possibly of a length only the device knows
+    int count = a.count;
+    if (a.count_dev != nullptr) count = *a.count_dev < count ? *a.count_dev : count;
+    if (q >= count) return;
+    q = a.query_rows[q];
+  }
+  if (q >= a.q || q < 0) return;
   int kq = a.k[q];
   kq = kq < 0 ? 0 : (kq > a.kmax ? a.kmax : kq);
   const long long qoff = static_cast<long long>(q) * a.kmax;
@@ -132,7 +139,9 @@ int launch_finalize(const FinalizeArgs &args, cudaStream_t s) {
   }
   if (smem > 48 * 1024)
     DMLP_CUDA_OK(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  const int blocks = (args.q + FIN_WARPS - 1) / FIN_WARPS;
+  const int rows = args.query_rows != nullptr ? args.count : args.q;
+  if (rows <= 0) return 0;
+  const int blocks = (rows + FIN_WARPS - 1) / FIN_WARPS;
   finalize_kernel<<<blocks, FIN_WARPS * 32, smem, s>>>(args);
   DMLP_CUDA_OK(cudaGetLastError());
   return 0;

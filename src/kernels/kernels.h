@@ -73,18 +73,40 @@ struct TopkPlan {
 /// every chunk contributes at most 32 candidates per query.
 TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax = 0);
 
+constexpr int kMaxPeers = 8;
+/// "When this launch has finished, tell the peers" (K5 signalling from inside the kernels):
+/// every block bumps `done_counter` as it finishes; the last one stores `value` into word
+/// `rank` of every peer's flag array with release semantics at system scope and resets the
+/// counter.  world == 0: no signal.
+struct SignalArgs {
+  unsigned *peer_flags[kMaxPeers] = {};
+  int world = 0, rank = 0;
+  unsigned value = 0;
+  unsigned *done_counter = nullptr;
+};
+/// "Do not start before the peers have told us": every block spins (acquire, system scope) until
+/// each of the `world` words of the local flag array has reached `value`; a wait that exceeds
+/// timeout_cycles writes 600 + the late rank to *status and carries on.  world == 0: no wait.
+struct WaitArgs {
+  const unsigned *flags = nullptr;
+  int world = 0;
+  unsigned value = 0;
+  long long timeout_cycles = 0;
+  int *status = nullptr;
+};
+
 // pack.cu
 int launch_stats_reset(PackStats *st, cudaStream_t s);
 int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t s);
 int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
-                float *norm2, float *errn, PackStats *maxima, cudaStream_t s);
+                float *norm2, float *errn, PackStats *maxima, cudaStream_t s, const WaitArgs *wait = nullptr,
+                const SignalArgs *signal = nullptr);
 
 /// Cross-GPU operand gather fused into the filter GEMM (K4).  Every rank owns
 /// `slice_rows` query rows and has packed them into its own symmetric buffer;
 /// a communication warp in each GEMM CTA pulls the other ranks' packed rows over
 /// NVLink into the local copy just ahead of the tiles that consume them, then
 /// pulls the fp64 rows, norms and k for the re-rank kernel that follows.
-constexpr int kMaxPeers = 8;
 struct GatherArgs {
   int world = 1, rank = 0;
   int slice_rows = 0;          ///< padded rows per owner (multiple of 256)
@@ -112,6 +134,7 @@ struct DataGatherArgs {
   unsigned *tile_count = nullptr;      ///< local, one counter per 256-row data tile, monotonically increasing
   int *status = nullptr;
   long long timeout_cycles = 0;
+  SignalArgs done;                     ///< optional: "I have finished reading your parts", sent when the launch ends
 };
 
 /// Where the exact k-lists go (K5): straight into the owner rank's receive
@@ -172,6 +195,11 @@ struct RerankArgs {
   int *num_flagged;                // device counter
   ScatterArgs scatter;             // world > 1: lists go to the owners' receive buffers
   int *w_out = nullptr;            // optional [q]: survivors recomputed per query (diagnostics)
+  int *final_label = nullptr;      // optional [q] (single data shard only): predicted label, and
+  unsigned long long *final_checksum = nullptr;  //   [q] checksum -- the vote + checksum tail folded into the emit kernel
+  int *flagged_rows = nullptr;     // optional [flagged_cap]: indices of flagged queries, slot = their order in num_flagged
+  int flagged_cap = 0;
+  SignalArgs signal;               // optional: the emit kernel tells the peers when the whole launch is done
   void *workspace = nullptr;       // >= rerank_workspace_bytes(q), 256-byte aligned
   size_t workspace_bytes = 0;
 };
@@ -193,6 +221,10 @@ struct FinalizeArgs {
   double *out_dist;     // [q][kmax] optional
   void *workspace = nullptr;   // >= finalize_workspace_bytes(); only needed when sources > 1 and kmax > 2048
   size_t workspace_bytes = 0;
+  const int *query_rows = nullptr;  // optional: only these rows are finalized (`count` entries at most,
+  int count = 0;                    //   the first min(count, *count_dev) when count_dev is set: a count
+  const int *count_dev = nullptr;   //   that only the device knows, e.g. the flagged queries of this step)
+  WaitArgs wait;                    // optional: the lists come from peers; wait for their signals first
 };
 size_t finalize_workspace_bytes(int sources, int q, int kmax);
 int launch_finalize(const FinalizeArgs &args, cudaStream_t s);
@@ -205,7 +237,11 @@ struct ExactArgs {
   const int *x_labels;
   const int *k;           // [q]
   const int *query_rows;  // optional [count] subset of query rows (nullptr = all q rows)
-  int count;              // number of queries to process
+  int count;              // number of queries to process (an upper bound when count_dev is set)
+  const int *count_dev = nullptr;  // optional device int: process min(count, *count_dev) queries -- lets a
+                                   // repair pass be enqueued before anyone knows how many queries need it
+  ScatterArgs scatter;    // world > 1: lists go to the owners' receive buffers (like RerankArgs)
+  SignalArgs signal;      // optional: the merge kernel tells the peers when the whole launch is done
   int n, a, id_base, kmax;
   double *out_dist;       // [q][kmax] (written at the query's own row)
   int *out_id;

@@ -61,7 +61,10 @@ __global__ void __launch_bounds__(256) stats_kernel(const double *__restrict__ s
 __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ src, long long rows, int a,
                                                    int a_pad, const PackStats *__restrict__ range,
                                                    __half *__restrict__ dst, float *__restrict__ norm2,
-                                                   float *__restrict__ errn, PackStats *maxima) {
+                                                   float *__restrict__ errn, PackStats *maxima, const WaitArgs wait,
+                                                   const SignalArgs signal) {
+  // (fused all-gathers) peers may still be reading the previous step's copy of these rows
+  wait_for_peers(wait);
   const ScaleParams sp = derive_scale(range->neg_lo, range->hi);
   const int lane = threadIdx.x & 31;
   const long long warp_global = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -115,6 +118,7 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
     atomicMax(reinterpret_cast<int *>(&maxima->max_norm), __float_as_int(my_max_norm));
     atomicMax(reinterpret_cast<int *>(&maxima->max_err), __float_as_int(my_max_err));
   }
+  signal_peers_when_grid_done(signal);  // "my packed rows are in place"
 }
 
 // Wire format "decimal6": the text grammar carries six decimals, so a value whose
@@ -211,12 +215,18 @@ int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t
 }
 
 int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
-                float *norm2, float *errn, PackStats *maxima, cudaStream_t s) {
-  if (rows <= 0) return 0;
+                float *norm2, float *errn, PackStats *maxima, cudaStream_t s, const WaitArgs *wait,
+                const SignalArgs *signal) {
+  const WaitArgs wa = wait ? *wait : WaitArgs();
+  const SignalArgs sg = signal ? *signal : SignalArgs();
+  if (rows <= 0 && sg.world <= 0) return 0;
+  if (rows < 0) rows = 0;
   DMLP_REQUIRE(a_pad >= a && (a_pad % 8) == 0, "pack: a_pad must be a multiple of 8 and >= a");
   long long blocks = (rows + 7) / 8;  // 8 warps per block
   if (blocks > 148 * 8) blocks = 148 * 8;
-  pack_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn, maxima);
+  if (blocks < 1) blocks = 1;
+  pack_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn, maxima, wa,
+                                                           sg);
   DMLP_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -363,26 +363,28 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
 }
 
 // -------------------------------------------------------------------- emit
-__global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc) {
-  __shared__ double s_dist[RR_THREADS / 32][WMAX];
-  __shared__ int s_id[RR_THREADS / 32][WMAX];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * (RR_THREADS / 32) + warp;
-  if (q >= a.q) return;
+// With `final_label` set (single data shard: the local list is the final one) the warp also
+// votes and folds the checksum right here -- the K6 tail (reference: engine.cpp:320-347,
+// common.cpp:59-68) without a second kernel or a second pass over the lists.
+__device__ __forceinline__ void emit_query(const RerankArgs &a, const Scratch &sc, int q, int lane, double *s_dist,
+                                           int *s_id, int *s_fid, int *s_flab) {
   int kq = a.k[q];
   kq = kq < 0 ? 0 : (kq > a.kmax ? a.kmax : kq);
   const int w = sc.q_w[q], base = sc.q_base[q];
   const QMeta m = sc.meta[q];
+  const bool fold = a.final_label != nullptr && a.scatter.world <= 1;
   int bad = 0;
   for (int i = lane; i < w; i += 32) {
     const double d = sc.pair_dist[base + i];
-    s_dist[warp][i] = d;
-    s_id[warp][i] = sc.pair_id[base + i];
+    s_dist[i] = d;
+    s_id[i] = sc.pair_id[base + i];
     // a-posteriori check of the error model on every recomputed pair
     const double dhat = fmax(m.qn2 + static_cast<double>(sc.pair_score[base + i]), 0.0);
     const double bound = (2.0 * sqrt(dhat) * m.delta + m.delta * m.delta + m.E) * (1.0 + 1e-6) + 1e-9 * dhat;
     if (fabs(d * m.s2 - dhat) > bound) bad = 1;
   }
+  if (fold)
+    for (int i = lane; i < kq; i += 32) { s_fid[i] = -1; s_flab[i] = -1; }
   bad = __any_sync(0xFFFFFFFFu, bad);
   __syncwarp();
 
@@ -398,17 +400,19 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArg
     o_label = reinterpret_cast<int *>(a.scatter.peer_base[owner] + a.scatter.off_label);
   }
   for (int i = lane; i < w; i += 32) {
-    const double d = s_dist[warp][i];
-    const int id = s_id[warp][i];
+    const double d = s_dist[i];
+    const int id = s_id[i];
     int rank = 0;
     for (int j = 0; j < w; ++j) {
-      const double dj = s_dist[warp][j];
-      rank += (dj < d || (dj == d && s_id[warp][j] > id)) ? 1 : 0;
+      const double dj = s_dist[j];
+      rank += (dj < d || (dj == d && s_id[j] > id)) ? 1 : 0;
     }
     if (rank < kq) {
+      const int lab = a.x_labels[id];
       o_dist[obase + rank] = d;
       o_id[obase + rank] = a.id_base + id;
-      o_label[obase + rank] = a.x_labels[id];
+      o_label[obase + rank] = lab;
+      if (fold) { s_fid[rank] = a.id_base + id; s_flab[rank] = lab; }
     }
   }
   for (int i = (w < kq ? w : kq) + lane; i < a.kmax; i += 32) {
@@ -419,8 +423,52 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArg
   if (lane == 0) {
     const int f = a.flags[q] | (bad ? kFlagModel : 0);
     a.flags[q] = f;
-    if (f != 0 && a.num_flagged != nullptr) atomicAdd(a.num_flagged, 1);
+    if (f != 0 && a.num_flagged != nullptr) {
+      const int slot = atomicAdd(a.num_flagged, 1);
+      if (a.flagged_rows != nullptr && slot < a.flagged_cap) a.flagged_rows[slot] = q;
+    }
   }
+  if (!fold) return;
+  __syncwarp();
+  // majority vote, ties to the larger label, -1 when nothing voted
+  unsigned long long best = 0;
+  for (int i = lane; i < kq; i += 32) {
+    if (s_fid[i] < 0) continue;
+    const int lab = s_flab[i];
+    int count = 0;
+    for (int j = 0; j < kq; ++j) count += (s_fid[j] >= 0 && s_flab[j] == lab) ? 1 : 0;
+    const unsigned long long key =
+        (static_cast<unsigned long long>(count) << 32) | (static_cast<uint32_t>(lab) ^ 0x80000000u);
+    best = key > best ? key : best;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+    best = other > best ? other : best;
+  }
+  if (lane == 0) {
+    const int label = best == 0 ? -1 : static_cast<int>(static_cast<uint32_t>(best & 0xFFFFFFFFu) ^ 0x80000000u);
+    unsigned long long h = 1469598103934665603ULL;
+    h ^= static_cast<unsigned long long>(static_cast<long long>(label));
+    h *= 1099511628211ULL;
+    for (int i = 0; i < kq; ++i) {
+      h ^= static_cast<unsigned long long>(static_cast<long long>(s_fid[i] + 1));
+      h *= 1099511628211ULL;
+    }
+    a.final_label[q] = label;
+    a.final_checksum[q] = h;
+  }
+}
+
+
+__global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc) {
+  __shared__ double s_dist[RR_THREADS / 32][WMAX];
+  __shared__ int s_id[RR_THREADS / 32][WMAX];
+  __shared__ int s_fid[RR_THREADS / 32][WMAX];
+  __shared__ int s_flab[RR_THREADS / 32][WMAX];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * (RR_THREADS / 32) + warp;
+  if (q < a.q) emit_query(a, sc, q, lane, s_dist[warp], s_id[warp], s_fid[warp], s_flab[warp]);
+  signal_peers_when_grid_done(a.signal);  // (K5) all of this rank's lists have been stored
 }
 
 int *g_debug_w = nullptr;

@@ -36,6 +36,30 @@ inline cudaStream_t st(void *s) { return static_cast<cudaStream_t>(s); }
 inline size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 inline int pad64(int a) { return (a + 63) / 64 * 64; }
 
+int fill_scatter(const dmlp_scatter_args *sc, ScatterArgs *out) {
+  DMLP_REQUIRE(sc->world >= 1 && sc->world <= kMaxPeers && sc->slice_rows > 0, "scatter: world must be in [1, 8]");
+  out->world = sc->world; out->rank = sc->rank; out->slice_rows = sc->slice_rows;
+  for (int i = 0; i < sc->world; ++i) out->peer_base[i] = static_cast<unsigned char *>(sc->peer_base[i]);
+  out->off_dist = sc->off_dist; out->off_id = sc->off_id; out->off_label = sc->off_label;
+  return 0;
+}
+
+int fill_signal(const dmlp_signal_args *sg, SignalArgs *out) {
+  if (sg == nullptr || sg->world <= 0) return 0;
+  DMLP_REQUIRE(sg->world <= kMaxPeers && sg->done_counter != nullptr, "signal: world must be in [1, 8] and done_counter set");
+  out->world = sg->world; out->rank = sg->rank; out->value = sg->value; out->done_counter = sg->done_counter;
+  for (int i = 0; i < sg->world; ++i) out->peer_flags[i] = static_cast<unsigned *>(sg->peer_flags[i]);
+  return 0;
+}
+
+int fill_wait(const dmlp_wait_args *w, WaitArgs *out) {
+  if (w == nullptr || w->world <= 0) return 0;
+  DMLP_REQUIRE(w->world <= kMaxPeers && w->flags != nullptr, "wait: world must be in [1, 8] and flags set");
+  out->flags = w->flags; out->world = w->world; out->value = w->value; out->status = w->status;
+  out->timeout_cycles = static_cast<long long>((w->timeout_seconds > 0 ? w->timeout_seconds : 20.0) * 1.5e9);
+  return 0;
+}
+
 int current_sm_count(int *out) {
   int dev = 0;
   DMLP_CUDA_OK(cudaGetDevice(&dev));
@@ -70,6 +94,22 @@ int dmlp_pack(const double *src, int64_t rows, int a, int a_pad, const void *ran
   DMLP_REQUIRE(a_pad % 64 == 0, "pack: a_pad must be a multiple of 64");
   return launch_pack(src, rows, a, a_pad, static_cast<const PackStats *>(range), static_cast<__half *>(dst_fp16),
                      norm2, errn, static_cast<PackStats *>(maxima), st(stream));
+}
+
+int dmlp_pack_ex(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
+                 float *errn, void *maxima, const dmlp_wait_args *wait, const dmlp_signal_args *signal, void *stream) {
+  DMLP_REQUIRE(a_pad % 64 == 0, "pack: a_pad must be a multiple of 64");
+  WaitArgs wa;
+  SignalArgs sg;
+  if (int rc = fill_wait(wait, &wa)) return rc;
+  if (int rc = fill_signal(signal, &sg)) return rc;
+  return launch_pack(src, rows, a, a_pad, static_cast<const PackStats *>(range), static_cast<__half *>(dst_fp16),
+                     norm2, errn, static_cast<PackStats *>(maxima), st(stream), &wa, &sg);
+}
+
+int dmlp_zero(void *ptr, size_t bytes, void *stream) {
+  DMLP_CUDA_OK(cudaMemsetAsync(ptr, 0, bytes, st(stream)));
+  return 0;
 }
 
 int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *stream) {
@@ -111,23 +151,49 @@ int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2,
                           reinterpret_cast<unsigned long long *>(cand), nullptr, st(stream));
 }
 
+int dmlp_rerank_ex(const dmlp_rerank_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr, "rerank: null arguments");
+  RerankArgs r;
+  r.workspace = g->workspace; r.workspace_bytes = g->workspace_bytes;
+  r.cand = reinterpret_cast<const unsigned long long *>(g->cand);
+  r.chunks = g->chunks; r.kp = g->kp;
+  r.q_attrs = g->q_attrs; r.x_attrs = g->x_attrs; r.x_labels = g->x_labels; r.k = g->k;
+  r.q_norm2 = g->q_norm2; r.q_errn = g->q_errn;
+  r.range = static_cast<const PackStats *>(g->range);
+  r.x_maxima = static_cast<const PackStats *>(g->x_maxima);
+  r.q = g->q; r.n = g->n; r.a = g->a; r.a_pad = g->a_pad; r.id_base = g->id_base; r.kmax = g->kmax;
+  r.out_dist = g->out_dist; r.out_id = g->out_id; r.out_label = g->out_label;
+  r.flags = g->flags; r.num_flagged = g->num_flagged;
+  r.flagged_rows = g->flagged_rows; r.flagged_cap = g->flagged_rows ? g->flagged_cap : 0;
+  r.final_label = g->final_label;
+  r.final_checksum = reinterpret_cast<unsigned long long *>(g->final_checksum);
+  if (g->scatter != nullptr) {
+    const dmlp_scatter_args *sc = g->scatter;
+    DMLP_REQUIRE(sc->world >= 2 && sc->world <= kMaxPeers, "rerank: scatter world must be in [2, 8]");
+    DMLP_REQUIRE(g->q == sc->world * sc->slice_rows, "rerank: with scatter, q must equal world * slice_rows");
+    DMLP_REQUIRE(g->final_label == nullptr, "rerank: the folded vote needs a single data shard (no scatter)");
+    if (int rc = fill_scatter(sc, &r.scatter)) return rc;
+  } else {
+    DMLP_REQUIRE(g->out_dist && g->out_id && g->out_label, "rerank: output lists missing");
+  }
+  DMLP_REQUIRE((g->final_label == nullptr) == (g->final_checksum == nullptr),
+               "rerank: final_label and final_checksum come together");
+  if (int rc = fill_signal(g->signal, &r.signal)) return rc;
+  return launch_rerank(r, st(stream));
+}
+
 int dmlp_rerank(const uint64_t *cand, int chunks, int kp, const double *q_attrs, const double *x_attrs,
                 const int *x_labels, const int *k, const float *q_norm2, const float *q_errn, const void *range,
                 const void *x_maxima, int q, int n, int a, int a_pad, int id_base, int kmax, double *out_dist,
                 int *out_id, int *out_label, int *flags, int *num_flagged, void *workspace, size_t workspace_bytes,
                 void *stream) {
-  RerankArgs r;
-  r.workspace = workspace; r.workspace_bytes = workspace_bytes;
-  r.cand = reinterpret_cast<const unsigned long long *>(cand);
-  r.chunks = chunks; r.kp = kp;
-  r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
-  r.q_norm2 = q_norm2; r.q_errn = q_errn;
-  r.range = static_cast<const PackStats *>(range);
-  r.x_maxima = static_cast<const PackStats *>(x_maxima);
-  r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
-  r.out_dist = out_dist; r.out_id = out_id; r.out_label = out_label;
-  r.flags = flags; r.num_flagged = num_flagged;
-  return launch_rerank(r, st(stream));
+  dmlp_rerank_args g = {};
+  g.cand = cand; g.chunks = chunks; g.kp = kp; g.q_attrs = q_attrs; g.x_attrs = x_attrs; g.x_labels = x_labels;
+  g.k = k; g.q_norm2 = q_norm2; g.q_errn = q_errn; g.range = range; g.x_maxima = x_maxima;
+  g.q = q; g.n = n; g.a = a; g.a_pad = a_pad; g.id_base = id_base; g.kmax = kmax;
+  g.out_dist = out_dist; g.out_id = out_id; g.out_label = out_label; g.flags = flags; g.num_flagged = num_flagged;
+  g.workspace = workspace; g.workspace_bytes = workspace_bytes;
+  return dmlp_rerank_ex(&g, stream);
 }
 
 int dmlp_dist_topk_gather(const void *x_fp16, const float *x_norm2, int n, int a_pad, int num_sms, int kmax,
@@ -185,6 +251,7 @@ int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms
   dg.off_labels = g->off_labels; dg.off_pack_flags = g->off_pack_flags;
   dg.tile_count = g->tile_count; dg.status = g->status;
   dg.timeout_cycles = static_cast<long long>((g->timeout_seconds > 0 ? g->timeout_seconds : 20.0) * 1.5e9);
+  if (int rc = fill_signal(g->done_signal, &dg.done)) return rc;
   const __half *xh = reinterpret_cast<const __half *>(dg.peer_base[dg.rank] + dg.off_xh);
   const float *xn = reinterpret_cast<const float *>(dg.peer_base[dg.rank] + dg.off_xn);
   return launch_dist_topk(static_cast<const __half *>(q_fp16), xh, xn, p,
@@ -200,23 +267,44 @@ int dmlp_rerank_scatter(const uint64_t *cand, int chunks, int kp, const double *
                         const void *range, const void *x_maxima, int q, int n, int a, int a_pad, int id_base,
                         int kmax, int *flags, int *num_flagged, const dmlp_scatter_args *sc, void *workspace,
                         size_t workspace_bytes, void *stream) {
-  DMLP_REQUIRE(sc != nullptr && sc->world >= 2 && sc->world <= kMaxPeers, "rerank_scatter: world must be in [2, 8]");
-  DMLP_REQUIRE(q == sc->world * sc->slice_rows, "rerank_scatter: q must equal world * slice_rows");
-  RerankArgs r;
-  r.cand = reinterpret_cast<const unsigned long long *>(cand);
-  r.chunks = chunks; r.kp = kp;
-  r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
-  r.q_norm2 = q_norm2; r.q_errn = q_errn;
-  r.range = static_cast<const PackStats *>(range);
-  r.x_maxima = static_cast<const PackStats *>(x_maxima);
-  r.q = q; r.n = n; r.a = a; r.a_pad = a_pad; r.id_base = id_base; r.kmax = kmax;
-  r.out_dist = nullptr; r.out_id = nullptr; r.out_label = nullptr;
-  r.flags = flags; r.num_flagged = num_flagged;
-  r.workspace = workspace; r.workspace_bytes = workspace_bytes;
-  r.scatter.world = sc->world; r.scatter.rank = sc->rank; r.scatter.slice_rows = sc->slice_rows;
-  for (int i = 0; i < sc->world; ++i) r.scatter.peer_base[i] = static_cast<unsigned char *>(sc->peer_base[i]);
-  r.scatter.off_dist = sc->off_dist; r.scatter.off_id = sc->off_id; r.scatter.off_label = sc->off_label;
-  return launch_rerank(r, st(stream));
+  DMLP_REQUIRE(sc != nullptr, "rerank_scatter: scatter arguments missing");
+  dmlp_rerank_args g = {};
+  g.cand = cand; g.chunks = chunks; g.kp = kp; g.q_attrs = q_attrs; g.x_attrs = x_attrs; g.x_labels = x_labels;
+  g.k = k; g.q_norm2 = q_norm2; g.q_errn = q_errn; g.range = range; g.x_maxima = x_maxima;
+  g.q = q; g.n = n; g.a = a; g.a_pad = a_pad; g.id_base = id_base; g.kmax = kmax;
+  g.flags = flags; g.num_flagged = num_flagged; g.scatter = sc;
+  g.workspace = workspace; g.workspace_bytes = workspace_bytes;
+  return dmlp_rerank_ex(&g, stream);
+}
+
+int dmlp_repair_flagged(const dmlp_repair_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr && g->cap > 0 && g->flagged_rows != nullptr && g->num_flagged != nullptr,
+               "repair_flagged: needs the flagged-row list, its device counter and cap > 0");
+  ExactArgs e;
+  e.q_attrs = g->q_attrs; e.x_attrs = g->x_attrs; e.x_labels = g->x_labels; e.k = g->k;
+  e.query_rows = g->flagged_rows; e.count = g->cap; e.count_dev = g->num_flagged;
+  e.n = g->n; e.a = g->a; e.id_base = g->id_base; e.kmax = g->kmax;
+  e.out_dist = g->out_dist; e.out_id = g->out_id; e.out_label = g->out_label;
+  e.workspace = g->workspace; e.workspace_bytes = g->workspace_bytes;
+  if (g->scatter != nullptr) {
+    DMLP_REQUIRE(g->final_label == nullptr, "repair_flagged: re-finalizing needs a single data shard (no scatter)");
+    if (int rc = fill_scatter(g->scatter, &e.scatter)) return rc;
+  } else {
+    DMLP_REQUIRE(g->out_dist && g->out_id && g->out_label, "repair_flagged: output lists missing");
+  }
+  if (int rc = fill_signal(g->signal, &e.signal)) return rc;
+  if (int rc = launch_exact(e, st(stream))) return rc;
+  if (g->final_label != nullptr) {
+    FinalizeArgs f;
+    f.dist = g->out_dist; f.id = g->out_id; f.label = g->out_label;
+    f.source_stride = static_cast<long long>(g->q) * g->kmax;
+    f.sources = 1; f.q = g->q; f.kmax = g->kmax; f.k = g->k;
+    f.out_label = g->final_label; f.out_checksum = reinterpret_cast<unsigned long long *>(g->final_checksum);
+    f.out_id = nullptr; f.out_dist = nullptr;
+    f.query_rows = g->flagged_rows; f.count = g->cap; f.count_dev = g->num_flagged;
+    return launch_finalize(f, st(stream));
+  }
+  return 0;
 }
 
 void dmlp_debug_rerank_w(int *w_out) { set_rerank_debug_w(w_out); }
@@ -245,6 +333,19 @@ int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels
 }
 
 size_t dmlp_finalize_workspace_bytes(int sources, int q, int kmax) { return finalize_workspace_bytes(sources, q, kmax); }
+
+int dmlp_finalize_ex(const dmlp_finalize_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr, "finalize: null arguments");
+  FinalizeArgs f;
+  f.dist = g->dist; f.id = g->id; f.label = g->label; f.source_stride = g->source_stride;
+  f.sources = g->sources; f.q = g->q; f.kmax = g->kmax; f.k = g->k;
+  f.out_label = g->out_label; f.out_checksum = reinterpret_cast<unsigned long long *>(g->out_checksum);
+  f.out_id = g->out_id; f.out_dist = g->out_dist;
+  f.workspace = g->workspace; f.workspace_bytes = g->workspace_bytes;
+  f.query_rows = g->query_rows; f.count = g->count; f.count_dev = g->count_dev;
+  if (int rc = fill_wait(g->wait, &f.wait)) return rc;
+  return launch_finalize(f, st(stream));
+}
 
 int dmlp_finalize(const double *dist, const int *id, const int *label, int64_t source_stride, int sources, int q,
                   int kmax, const int *k, int *out_label, uint64_t *out_checksum, int *out_id, double *out_dist,
