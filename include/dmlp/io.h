@@ -111,6 +111,10 @@ inline double synth_attr(uint64_t h, double lo, double hi) {
   return static_cast<double>(i) / 1e6;
 }
 
+/// Smallest and largest attribute value over data and queries (threads <= 0: hardware
+/// concurrency); 0, 0 for an empty problem.
+void value_range(const Problem &p, int threads, double *lo, double *hi);
+
 /// Write a Problem in the reference's text grammar (six decimals).
 void write_problem_text(const Problem &p, std::FILE *f);
 

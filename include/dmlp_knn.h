@@ -331,6 +331,22 @@ typedef struct dmlp_repair_args {
 } dmlp_repair_args;
 int dmlp_repair_flagged(const dmlp_repair_args *r, void *stream);
 
+/* dmlp_exact with the K5 extras: `scatter` sends the lists into the owners' receive buffers (the
+ * query rows are then indices in the padded column space, owner = row / slice_rows), `signal`
+ * announces them from the kernel's last block. */
+typedef struct dmlp_exact_args {
+  const double *q_attrs, *x_attrs;
+  const int *x_labels, *k, *query_rows;
+  int count, n, a, id_base, kmax;
+  double *out_dist;
+  int *out_id, *out_label;
+  const dmlp_scatter_args *scatter;
+  const dmlp_signal_args *signal;
+  void *workspace;
+  size_t workspace_bytes;
+} dmlp_exact_args;
+int dmlp_exact_ex(const dmlp_exact_args *g, void *stream);
+
 /* dmlp_finalize with the extras: `wait` (K5 owner side: the lists come from the peers, see
  * dmlp_signal_args; no separate wait launch), and a row subset whose length may live on the
  * device (query_rows / count / count_dev, e.g. the repaired rows of this step). */

@@ -190,6 +190,35 @@ void read_problem(std::FILE *f, int threads, Problem *out) {
   parse_problem(buf.data(), used, threads, out);
 }
 
+void value_range(const Problem &p, int threads, double *lo, double *hi) {
+  if (threads <= 0) threads = int(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  const int64_t nd = p.num_data * p.num_attrs, nq = p.num_queries * p.num_attrs;
+  std::vector<double> los(size_t(threads), 1e300), his(size_t(threads), -1e300);
+  auto scan = [&](int t) {
+    double l = 1e300, h = -1e300;
+    for (int pass = 0; pass < 2; ++pass) {
+      const double *v = pass == 0 ? p.data_attrs : p.query_attrs;
+      const int64_t n = pass == 0 ? nd : nq;
+      for (int64_t i = n * t / threads, e = n * (t + 1) / threads; i < e; ++i) {
+        l = v[i] < l ? v[i] : l;
+        h = v[i] > h ? v[i] : h;
+      }
+    }
+    los[size_t(t)] = l;
+    his[size_t(t)] = h;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; ++t) pool.emplace_back(scan, t);
+  scan(0);
+  for (auto &th : pool) th.join();
+  double l = 1e300, h = -1e300;
+  for (int t = 0; t < threads; ++t) { l = los[size_t(t)] < l ? los[size_t(t)] : l; h = his[size_t(t)] > h ? his[size_t(t)] : h; }
+  if (l > h) l = h = 0.0;
+  *lo = l;
+  *hi = h;
+}
+
 void synth_problem(const SynthSpec &s, Problem *out) {
   out->resize(s.n, s.q, s.a);
   int threads = int(std::thread::hardware_concurrency());

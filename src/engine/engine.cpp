@@ -74,6 +74,9 @@ void Engine::KNNFlat(const DatasetView &data, const QueryView &queries, ResultSe
     go.cols = config.grid_cols;
     go.exact_only = (be == Backend::kGpuExact);
     go.trace = config.trace;
+    go.have_range = config.have_range;
+    go.range_lo = config.range_lo;
+    go.range_hi = config.range_hi;
     gpu::knn_gpu(data, queries, go, rs, &last_backend);
   }
 
@@ -91,6 +94,18 @@ void Engine::KNNFlat(const DatasetView &data, const QueryView &queries, ResultSe
       reportResult(shell, pairs, rs->label[i]);
     }
   }
+}
+
+void Engine::Prepare(const Params &p, int kmax) {
+  if (config.backend == Backend::kCpu) return;
+  const int ndev = gpu::device_count();
+  if (ndev == 0) return;
+  gpu::GpuOptions go;
+  go.ngpu = config.ngpu > 0 ? (config.ngpu < ndev ? config.ngpu : ndev) : ndev;
+  go.rows = config.grid_rows;
+  go.cols = config.grid_cols;
+  go.exact_only = (config.backend == Backend::kGpuExact);
+  gpu::prepare(p.num_data, p.num_queries, p.num_attrs, kmax, go);
 }
 
 void Engine::KNN(Params &p, std::vector<DataPoint> &dataset, std::vector<Query> &queries) {

@@ -697,7 +697,16 @@ __device__ void data_gather_warp(const TopkPlan &plan, const DataGatherArgs &dg,
   }
 }
 
-template <bool WIDE>
+// Skewed wide schedule (MODE 2): which k-step an item is at decides what is in flight.  Tile j
+// of the item runs on accumulator j & 1 during steps [j * H, j * H + K); H = (K + gap) / 2, so
+// the two accumulators are half a period apart, each has `gap` steps between the end of one
+// tile and the start of its next one (its drain), and at most two tiles are active at a step.
+__device__ __forceinline__ int skew_first_tile(int s, int K, int H) {
+  const int j = (s - K + H) / H;  // ceil((s - K + 1) / H) for s >= K - H, else <= 0
+  return s - K + 1 <= 0 ? 0 : j;
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(THREADS2, 1)
 dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
                       const float *__restrict__ xnorm2, const TopkPlan plan,
@@ -707,6 +716,13 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   // operand then crosses L2 -> SM once per two data tiles: 48 instead of 64 bytes per SM and
   // clock at full tensor rate, against an L2 that delivers ~43 (measured 8.7 TB/s at 72 %).
   // The price is that the two stages drain while the MMA waits.
+  // SKEW (MODE 2) keeps the wide tile's operand sharing but never lets the tensor pipe wait for a
+  // drain: the two accumulators run half a period apart, each tile walks the k-blocks
+  // cyclically from wherever the (continuous) query stream is when it starts, and a tile's
+  // accumulator rests for `gap` steps -- while the other one keeps the MMA busy -- before its
+  // next tile begins.  The query tile of a step is still shared by both active data tiles.
+  constexpr bool WIDE = MODE >= 1;
+  constexpr bool SKEW = MODE == 2;
   constexpr int NST = WIDE ? STAGES : STAGES2;
   constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of one data tile
   constexpr int BS_BYTES = WIDE ? B_BYTES : BH_BYTES;  // data bytes per stage
@@ -783,6 +799,56 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           }
           asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
         }
+        if constexpr (SKEW) {
+          const int K = plan.k_blocks, H = (K + plan.gap) >> 1, T = it.tile_end - it.tile_begin;
+          const int steps = (T - 1) * H + K;
+          for (int st = 0; st < steps; ++st) {
+            const int j0 = skew_first_tile(st, K, H);
+            int j1 = st / H;
+            if (j1 > T - 1) j1 = T - 1;
+            const int kb = st % K;
+            if (dg.world > 1 && j1 * H == st) {
+              // a tile starts: its packed rows (and norms) may still be on their way
+              const int tile = it.tile_begin + j1;
+              const int rows_in_tile = min(BN, plan.n - tile * BN);
+              const unsigned target = dg.epoch * static_cast<unsigned>(rows_in_tile);
+              const long long t0 = clock64();
+              while (static_cast<int>(ld_acquire_gpu(dg.tile_count + tile) - target) < 0) {
+                if (clock64() - t0 > dg.timeout_cycles) {
+                  if (dg.status) atomicExch(dg.status, 500);
+                  break;
+                }
+                __nanosleep(64);
+              }
+              asm volatile("fence.proxy.async;" ::: "memory");
+            }
+            if (plan.sync && cta_rank == 0 && it.group_rows > 1 && (st % (K * plan.sync)) == 0) {
+              // re-align the pairs that sweep this chunk (see the tile-ordered loop below)
+              unsigned *cnt = plan.sync_cnt + (it.group * plan.chunks + it.chunk);
+              atomicAdd(cnt, 1u);
+              ++sync_epoch;
+              const unsigned target = static_cast<unsigned>(it.group_rows) * sync_epoch;
+              const long long t0 = clock64();
+              while (static_cast<int>(ld_acquire_gpu(cnt) - target) < 0) {
+                if (clock64() - t0 > 2000000000LL) {
+                  atomicAdd(&g_sync_timeouts, 1u);
+                  break;
+                }
+              }
+              if (plan.prof) pw_sync += clock64() - t0;
+            }
+            const long long pe0 = plan.prof ? clock64() : 0;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (plan.prof) pw_empty += clock64() - pe0;
+            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + (j1 - j0 + 1) * BH_BYTES));
+            tma_load_2d_pair(smem + L::kOffA + stage * A_BYTES, &tm_q, &full_bar[stage], kb * BK, it.m * BM, pol_q);
+            for (int j = j0; j <= j1; ++j)   // slot = accumulator = parity of the tile within the item
+              tma_load_2d_pair(smem + L::kOffB + stage * BS_BYTES + (j & 1) * BH_BYTES, &tm_x, &full_bar[stage], kb * BK,
+                               (it.tile_begin + j) * BN + cta_rank * (BN / 2), pol_x);
+            if (++stage == NST) { stage = 0; phase ^= 1; }
+          }
+          continue;
+        }
         constexpr int TSTEP = WIDE ? 2 : 1;
         for (int tile = it.tile_begin; tile < it.tile_end; tile += TSTEP) {
           const bool two = WIDE && tile + 1 < it.tile_end;
@@ -855,7 +921,40 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       for (int t = cluster_id; t < total_items; t += num_clusters) {
         Item it;
         if (!get_item(plan, t, cta_rank, &it)) continue;
-        if constexpr (WIDE) {
+        if constexpr (SKEW) {
+          const int K = plan.k_blocks, H = (K + plan.gap) >> 1, T = it.tile_end - it.tile_begin;
+          const int steps = (T - 1) * H + K;
+          for (int st = 0; st < steps; ++st) {
+            const int j0 = skew_first_tile(st, K, H);
+            int j1 = st / H;
+            if (j1 > T - 1) j1 = T - 1;
+            const long long w1 = plan.prof ? clock64() : 0;
+            mbar_wait(&full_bar[stage], phase);
+            if (plan.prof) mw_full += clock64() - w1;
+            tc_fence_after();
+            const uint64_t da = make_smem_desc_sw128(smem_u32(smem + L::kOffA + stage * A_BYTES));
+            for (int j = j0; j <= j1; ++j) {   // the older tile first: it never has to wait for a drain
+              const int acc = j & 1;
+              const int first = j * H;
+              if (st == first) {   // this accumulator's previous tile must have been drained
+                const long long w0 = plan.prof ? clock64() : 0;
+                mbar_wait(&tempty_bar[acc], ((acc ? uses[1] : uses[0]) & 1) ^ 1);
+                if (plan.prof) mw_tempty += clock64() - w0;
+                tc_fence_after();
+              }
+              const uint64_t db = make_smem_desc_sw128(smem_u32(smem + L::kOffB + stage * BS_BYTES + acc * BH_BYTES));
+#pragma unroll
+              for (int kk = 0; kk < BK / 16; ++kk)
+                umma_f16_pair(tmem_base + acc * BN, da + 2 * kk, db + 2 * kk, idesc, (st > first || kk > 0) ? 1u : 0u);
+              if (st == first + K - 1) {   // every k-block seen once (cyclically): hand the tile to the epilogue
+                umma_commit_pair(&tfull_bar[acc]);
+                if (acc) ++uses[1]; else ++uses[0];
+              }
+            }
+            umma_commit_pair(&empty_bar[stage]);  // frees this stage in both CTAs
+            if (++stage == NST) { stage = 0; phase ^= 1; }
+          }
+        } else if constexpr (WIDE) {
           for (int tile = it.tile_begin; tile < it.tile_end; tile += 2) {
             const bool two = tile + 1 < it.tile_end;
             const long long w0 = plan.prof ? clock64() : 0;
@@ -1009,6 +1108,15 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   p.prof = nullptr;
   if (const char *e = getenv("DMLP_TOPK_WIDE")) p.wide = atoi(e) != 0;
   if (!p.pair) p.wide = 0;
+  // skewed wide schedule: steps an accumulator rests between two tiles (its drain; the other
+  // accumulator keeps the tensor pipe busy meanwhile).  DMLP_TOPK_GAP=<steps>, -1 = the lock-step
+  // wide tile (both accumulators fill side by side and drain while the MMA waits)
+  p.gap = 12;
+  if (const char *e = getenv("DMLP_TOPK_GAP")) p.gap = atoi(e);
+  if (p.gap > p.k_blocks - 2) p.gap = p.k_blocks - 2;
+  if (p.gap >= 0 && ((p.k_blocks + p.gap) & 1)) ++p.gap;   // the half period must be whole
+  if (p.gap > p.k_blocks - 2) p.gap -= 2;
+  if (p.gap < 0 || !p.wide) p.gap = -1;
   p.rot = 0;
   p.cand_chunks = 0;  // filled in once the chunk count is known
   p.chunk_base = 0;
@@ -1170,10 +1278,13 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   if (int rc = make_fp16_tile_map(&tm_x, xh, plan.n, plan.a_pad, plan.pair ? BN / 2 : BN / plan.cluster)) return rc;
   if (!plan.pair) plan.wide = 0;
   const int smem_bytes = plan.pair ? (plan.wide ? Layout1::kBytes : Layout2::kBytes) : Layout1::kBytes;
-  if (plan.pair && plan.wide)
-    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  if (!plan.wide) plan.gap = -1;
+  if (plan.pair && plan.wide && plan.gap >= 0)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  else if (plan.pair && plan.wide)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   else if (plan.pair)
-    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   else
     DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg = {};
@@ -1196,10 +1307,12 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (plan.pair && plan.wide)
-    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<true>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+  if (plan.pair && plan.wide && plan.gap >= 0)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<2>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+  else if (plan.pair && plan.wide)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<1>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
   else if (plan.pair)
-    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<false>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<0>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
   else
     DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_kernel, tm_q, tm_x, xnorm2, plan, cand));
   return 0;

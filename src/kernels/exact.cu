@@ -29,7 +29,7 @@ constexpr int EX_QB = 16;    // queries per block tile
 constexpr int EX_CH = 32;    // columns per step
 constexpr int EX_THREADS = 256;
 constexpr int EX_SORT_SMEM = 2048;  // entries sorted in shared memory; longer lists sort in place in global memory
-constexpr int EX_MAX_SPLITS = 64;
+constexpr int EX_MAX_SPLITS = 128;
 
 __host__ __device__ inline int pow2_at_least(int v) {
   int p = 1;
@@ -273,7 +273,7 @@ size_t bytes_for(int batch, int splits, int kmax) {
 int pick_splits(int count, int n, int num_sms) {
   const int qblocks = (count + EX_QB - 1) / EX_QB;
   int s = (4 * num_sms + qblocks - 1) / qblocks;
-  const int by_rows = n / 2048 > 0 ? n / 2048 : 1;
+  const int by_rows = n / 512 > 0 ? n / 512 : 1;
   if (s > by_rows) s = by_rows;
   if (s > EX_MAX_SPLITS) s = EX_MAX_SPLITS;
   return s < 1 ? 1 : s;

@@ -332,6 +332,22 @@ int dmlp_exact(const double *q_attrs, const double *x_attrs, const int *x_labels
   return launch_exact(e, st(stream));
 }
 
+int dmlp_exact_ex(const dmlp_exact_args *g, void *stream) {
+  DMLP_REQUIRE(g != nullptr, "exact: null arguments");
+  ExactArgs e;
+  e.q_attrs = g->q_attrs; e.x_attrs = g->x_attrs; e.x_labels = g->x_labels; e.k = g->k; e.query_rows = g->query_rows;
+  e.count = g->count; e.n = g->n; e.a = g->a; e.id_base = g->id_base; e.kmax = g->kmax;
+  e.out_dist = g->out_dist; e.out_id = g->out_id; e.out_label = g->out_label;
+  e.workspace = g->workspace; e.workspace_bytes = g->workspace_bytes;
+  if (g->scatter != nullptr) {
+    if (int rc = fill_scatter(g->scatter, &e.scatter)) return rc;
+  } else {
+    DMLP_REQUIRE(g->out_dist && g->out_id && g->out_label, "exact: output lists missing");
+  }
+  if (int rc = fill_signal(g->signal, &e.signal)) return rc;
+  return launch_exact(e, st(stream));
+}
+
 size_t dmlp_finalize_workspace_bytes(int sources, int q, int kmax) { return finalize_workspace_bytes(sources, q, kmax); }
 
 int dmlp_finalize_ex(const dmlp_finalize_args *g, void *stream) {

@@ -115,11 +115,32 @@ def test_dist_topk_wide_tile_equals_narrow(K, q, n, a, chunks, gmc, sync, monkey
     xh, xn, _ = K.pack(x, st, st)
     qh, _, _ = K.pack(qq, st)
     got = {}
-    for wide in ("0", "1"):
+    # narrow; wide in lock step (gap -1); wide skewed (the default gap, and a short one)
+    for name, wide, gap in (("narrow", "0", None), ("lockstep", "1", "-1"), ("skew", "1", None), ("skew4", "1", "4")):
         monkeypatch.setenv("DMLP_TOPK_WIDE", wide)
-        got[wide] = K.dist_topk(qh, xh, xn).clone()
+        if gap is None:
+            monkeypatch.delenv("DMLP_TOPK_GAP", raising=False)
+        else:
+            monkeypatch.setenv("DMLP_TOPK_GAP", gap)
+        got[name] = K.dist_topk(qh, xh, xn).clone()
         torch.cuda.synchronize()
-    assert got["0"].shape == got["1"].shape and torch.equal(got["0"], got["1"])
+    assert got["narrow"].shape == got["lockstep"].shape and torch.equal(got["narrow"], got["lockstep"])
+    # the skewed schedule walks the k-blocks cyclically from a tile-dependent start, so fp32
+    # accumulation order -- and the last bits of a score -- differ: compare what matters, the
+    # certified exact lists the re-rank derives from the candidates
+    kk = torch.full((q,), 9, dtype=torch.int32, device="cuda")
+    labels = torch.zeros(n, dtype=torch.int32, device="cuda")
+    qst = K.new_stats()
+    _, qn, qe = K.pack(qq, st, qst)
+    ref = None
+    for name in ("narrow", "skew", "skew4"):
+        od, oi, ol, flags, nflag = K.rerank(got[name], qq, x, labels, kk, qn, qe, st, st, 0, 9)
+        torch.cuda.synchronize()
+        assert int(nflag.item()) == 0, name
+        if ref is None:
+            ref = (od.clone(), oi.clone())
+        else:
+            assert torch.equal(ref[0], od) and torch.equal(ref[1], oi), name
 
 
 def test_knn_local_long_rows_take_the_wide_tile(K):
