@@ -24,6 +24,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <stdexcept>
@@ -237,7 +238,7 @@ Plan make_plan(int64_t N, int64_t Q, int a, int kmax, const GpuOptions &opt) {
   s.R = R; s.C = C; s.a = a; s.a_pad = pad64(a); s.kmax = std::max(kmax, 1);
   s.n_max = BlockPartition{N, R}.count(0);
   s.q_max = BlockPartition{Q, C}.count(0);
-  s.fused = !opt.exact_only && kmax <= kFusedMaxK && N > 0 && Q > 0 &&
+  s.fused = !opt.exact_only && kmax <= kFusedMaxK && N >= R && Q > 0 &&   // (no empty data shard on the fused path)
             double(N) * double(Q) * double(std::max(a, 1)) >= double(1 << 22);
   // slices of a column: one per data shard; padded to whole 256-row tiles for the fused gather
   const int64_t per = BlockPartition{s.q_max, R}.count(0);
@@ -360,7 +361,9 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
   for (int d = 0; d < R * C; ++d) base[size_t(d)] = rt.dev(d).arena;
   auto dev_of = [&](int r, int c) { return r * C + c; };
   // rows_fused: one data shard whose parts are spread over the row and gathered inside the GEMM
-  const bool rows_fused = S.fused && R == 1 && C > 1 && qp.count(C - 1) >= 256 && N >= C;
+  const char *rf_env = std::getenv("DMLP_ROWS_FUSED");   // 0: every device loads the whole shard from the host
+  const bool rows_fused = S.fused && R == 1 && C > 1 && qp.count(C - 1) >= 256 && N >= C &&
+                          !(rf_env && std::atoi(rf_env) == 0);
   const int km = S.kmax;
 
   std::vector<std::vector<int>> h_nflag(size_t(R) * C, std::vector<int>(1, 0));
@@ -368,6 +371,8 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
   std::vector<std::vector<double>> h_dist(size_t(R) * C);
   std::vector<Owner> owned(size_t(R) * C);
   std::vector<int> h_status(size_t(R) * C, 0);
+  struct Readback { bool folded = false; int64_t qb = 0, q = 0; };
+  std::vector<Readback> readback(size_t(R) * C);
   // ---- enqueue everything, device by device; nothing here waits for the GPU ----------------
   for (int r = 0; r < R; ++r)
     for (int c = 0; c < C; ++c) {
@@ -539,22 +544,38 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
           if (R > 1) f.wait = &w_lists;
           check_rc(dmlp_finalize_ex(&f, st), "finalize");
         }
-        const int64_t gq = qcb + own_b;
-        const int *ids_src = folded ? at<int>(B, L.oi) : at<int>(B, L.fid);
-        const double *dist_src = folded ? at<double>(B, L.od) : at<double>(B, L.fdist);
-        CK(cudaMemcpyAsync(out->label.data() + gq, f_label, sizeof(int) * size_t(own_q), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(out->checksum.data() + gq, f_sum, sizeof(uint64_t) * size_t(own_q), cudaMemcpyDeviceToHost, st));
-        // lists come back dense [own_q][kmax]; the CSR result is filled after the sync below
-        h_ids[size_t(d)].resize(size_t(own_q) * km);
-        h_dist[size_t(d)].resize(size_t(own_q) * km);
-        CK(cudaMemcpyAsync(h_ids[size_t(d)].data(), ids_src, sizeof(int) * size_t(own_q) * km, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_dist[size_t(d)].data(), dist_src, sizeof(double) * size_t(own_q) * km, cudaMemcpyDeviceToHost, st));
-        owned[size_t(d)].qb = gq;
-        owned[size_t(d)].q = own_q;
+        Readback &rb = readback[size_t(d)];
+        rb.folded = folded;
+        rb.qb = qcb + own_b;
+        rb.q = own_q;
       }
-      CK(cudaMemcpyAsync(&h_status[size_t(d)], at<int>(B, L.status), sizeof(int), cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(h_nflag[size_t(d)].data(), nflag, sizeof(int), cudaMemcpyDeviceToHost, st));
     }
+  // ---- read-backs, once every device has all of its work (a copy into pageable host memory
+  // blocks the host until the device gets there, and an owner's finalize waits for lists that
+  // the other devices' kernels -- all enqueued above -- produce)
+  for (int d = 0; d < R * C; ++d) {
+    Device &dv = rt.dev(d);
+    const Layout &L = plan.layout[size_t(d)];
+    unsigned char *B = base[size_t(d)];
+    cudaStream_t st = dv.stream;
+    CK(cudaSetDevice(dv.id));
+    const Readback &rb = readback[size_t(d)];
+    if (rb.q > 0) {
+      const int *ids_src = rb.folded ? at<int>(B, L.oi) : at<int>(B, L.fid);
+      const double *dist_src = rb.folded ? at<double>(B, L.od) : at<double>(B, L.fdist);
+      CK(cudaMemcpyAsync(out->label.data() + rb.qb, at<int>(B, L.final_label), sizeof(int) * size_t(rb.q), cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(out->checksum.data() + rb.qb, at<uint64_t>(B, L.final_sum), sizeof(uint64_t) * size_t(rb.q), cudaMemcpyDeviceToHost, st));
+      // lists come back dense [q][kmax]; the CSR result is filled after the sync below
+      h_ids[size_t(d)].resize(size_t(rb.q) * km);
+      h_dist[size_t(d)].resize(size_t(rb.q) * km);
+      CK(cudaMemcpyAsync(h_ids[size_t(d)].data(), ids_src, sizeof(int) * size_t(rb.q) * km, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(h_dist[size_t(d)].data(), dist_src, sizeof(double) * size_t(rb.q) * km, cudaMemcpyDeviceToHost, st));
+      owned[size_t(d)].qb = rb.qb;
+      owned[size_t(d)].q = rb.q;
+    }
+    CK(cudaMemcpyAsync(&h_status[size_t(d)], at<int>(B, L.status), sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_nflag[size_t(d)].data(), at<int>(B, L.nflag), sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
 
   // ---- the one wait of the call: every device's read-back ------------------------------------
   long long total_flagged = 0;
@@ -571,6 +592,17 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
   if (worst > kRepairCap) {
     // More uncertified queries on one shard than the call repairs by itself (not seen on the
     // generator's distributions): answer the whole job on the direct fp64 kernels instead.
+    if (opt.trace)
+      for (int d = 0; d < R * C; ++d) {
+        std::vector<int> f(size_t(std::min<int64_t>(S.qp, 4096)));
+        CK(cudaSetDevice(rt.dev(d).id));
+        CK(cudaMemcpy(f.data(), base[size_t(d)] + plan.layout[size_t(d)].flags, f.size() * sizeof(int), cudaMemcpyDeviceToHost));
+        int hist[8] = {0};
+        for (int v : f) ++hist[v & 7];
+        std::fprintf(stderr, "[dmlp] device %d: %d flagged; reason bits (1 cutoff, 2 overflow, 4 model) over the first %zu "
+                     "queries: 0:%d 1:%d 2:%d 3:%d 4:%d 5:%d 6:%d 7:%d\n", d, h_nflag[size_t(d)][0], f.size(), hist[0], hist[1],
+                     hist[2], hist[3], hist[4], hist[5], hist[6], hist[7]);
+      }
     GpuOptions again = opt;
     again.exact_only = true;
     knn_gpu(data, queries, again, out, nullptr);

@@ -198,16 +198,29 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
       const uint32_t acc_phase = (acc ? uses[1] : uses[0]) & 1;
       if (acc) ++uses[1]; else ++uses[0];
       float *xn = xn_all + (acc_it & 1) * BN;  // (not `acc`: two tiles in a row can share a stage across items)
+      // The data norms of the tile are staged while its MMAs still run -- unless the rows (and their
+      // norms) are being gathered from peer GPUs by this very kernel: then they are only known to be
+      // in place once the tile's MMAs have completed (the TMA producer waited for the tile's arrival
+      // counter), so the staging follows the accumulator wait.
       const long long ps0 = prof ? clock64() : 0;
-      for (int i = e_tid; i < BN; i += EPI_THREADS) {
-        const int col = tile * BN + i;
-        xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
+      if (!plan.late_norms) {
+        for (int i = e_tid; i < BN; i += EPI_THREADS) {
+          const int col = tile * BN + i;
+          xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
+        }
+        named_barrier_sync(1, EPI_THREADS);
       }
-      named_barrier_sync(1, EPI_THREADS);
       const long long pw0 = prof ? clock64() : 0;
       if (prof) prof_stage += pw0 - ps0;
       mbar_wait(&tfull_bar[acc], acc_phase);
       if (prof) prof_wait += clock64() - pw0;
+      if (plan.late_norms) {
+        for (int i = e_tid; i < BN; i += EPI_THREADS) {
+          const int col = tile * BN + i;
+          xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
+        }
+        named_barrier_sync(1, EPI_THREADS);
+      }
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       // (one tcgen05.ld in flight at a time: overlapping the load of the next 32 columns with
@@ -1108,10 +1121,11 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   p.prof = nullptr;
   if (const char *e = getenv("DMLP_TOPK_WIDE")) p.wide = atoi(e) != 0;
   if (!p.pair) p.wide = 0;
-  // skewed wide schedule: steps an accumulator rests between two tiles (its drain; the other
-  // accumulator keeps the tensor pipe busy meanwhile).  DMLP_TOPK_GAP=<steps>, -1 = the lock-step
-  // wide tile (both accumulators fill side by side and drain while the MMA waits)
-  p.gap = 12;
+  // skewed wide schedule (opt-in): steps an accumulator rests between two tiles (its drain; the
+  // other accumulator keeps the tensor pipe busy meanwhile).  DMLP_TOPK_GAP=<steps>; the default
+  // -1 is the lock-step wide tile (both accumulators fill side by side and drain while the MMA waits)
+  p.late_norms = 0;
+  p.gap = -1;   // measured on B200: the skewed schedule is slower (65.9 vs 57 ms on the headline shape), see DESIGN.md
   if (const char *e = getenv("DMLP_TOPK_GAP")) p.gap = atoi(e);
   if (p.gap > p.k_blocks - 2) p.gap = p.k_blocks - 2;
   if (p.gap >= 0 && ((p.k_blocks + p.gap) & 1)) ++p.gap;   // the half period must be whole
@@ -1271,6 +1285,15 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
     plan.prof = static_cast<unsigned long long *>(p);
     g_prof_ctas = plan.grid;
   }
+  if (!plan.pair && plan.cluster > 1) {
+    // TMA multicast loads here read only this GPU's memory
+    int dev = -1;
+    DMLP_CUDA_OK(cudaGetDevice(&dev));
+    cudaPointerAttributes at_x;
+    DMLP_CUDA_OK(cudaPointerGetAttributes(&at_x, xh));
+    DMLP_REQUIRE(at_x.type == cudaMemoryTypeDevice && at_x.device == dev,
+                 "dist_topk: the multicast tile loads need the data operand in this GPU's own memory");
+  }
   DMLP_REQUIRE(plan.kp == KP, "dist_topk: this build keeps 32 keys per (query, chunk)");
   DMLP_REQUIRE(plan.a_pad % BK == 0 && plan.a_pad > 0, "dist_topk: a_pad must be a positive multiple of 64");
   CUtensorMap tm_q, tm_x;
@@ -1297,6 +1320,7 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   DMLP_REQUIRE(ga.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
   DataGatherArgs dg;
   if (data_gather != nullptr) dg = *data_gather;
+  plan.late_norms = dg.world > 1 ? 1 : 0;
   DMLP_REQUIRE(dg.world == 1 || plan.pair, "dist_topk: the fused data gather needs the CTA-pair kernel");
   DMLP_REQUIRE(dg.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
   cfg.stream = s;

@@ -301,8 +301,8 @@ int launch_exact(const ExactArgs &args, cudaStream_t s) {
   int splits = pick_splits(batch, args.n, sms);
   while (bytes_for(batch, splits, args.kmax) > args.workspace_bytes) {
     if (splits > 1) { splits = (splits + 1) / 2; continue; }
-    if (batch <= EX_QB) break;
-    batch = ((batch + 1) / 2 + EX_QB - 1) / EX_QB * EX_QB;
+    if (batch <= 1) break;
+    batch = batch > 2 * EX_QB ? ((batch + 1) / 2 + EX_QB - 1) / EX_QB * EX_QB : (batch + 1) / 2;
   }
   DMLP_REQUIRE(bytes_for(batch, splits, args.kmax) <= args.workspace_bytes,
                "exact: workspace smaller than exact_workspace_bytes(n, batch >= 1, kmax)");

@@ -115,8 +115,8 @@ def test_dist_topk_wide_tile_equals_narrow(K, q, n, a, chunks, gmc, sync, monkey
     xh, xn, _ = K.pack(x, st, st)
     qh, _, _ = K.pack(qq, st)
     got = {}
-    # narrow; wide in lock step (gap -1); wide skewed (the default gap, and a short one)
-    for name, wide, gap in (("narrow", "0", None), ("lockstep", "1", "-1"), ("skew", "1", None), ("skew4", "1", "4")):
+    # narrow; wide in lock step (the default); wide skewed (opt-in, two gaps)
+    for name, wide, gap in (("narrow", "0", None), ("lockstep", "1", None), ("skew", "1", "12"), ("skew4", "1", "4")):
         monkeypatch.setenv("DMLP_TOPK_WIDE", wide)
         if gap is None:
             monkeypatch.delenv("DMLP_TOPK_GAP", raising=False)
