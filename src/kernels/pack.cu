@@ -76,17 +76,7 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
     const double *in = src + r * a;
     __half2 *out = reinterpret_cast<__half2 *>(dst + r * a_pad);
     double nsum = 0.0, esum = 0.0, xsum = 0.0;
-#pragma unroll 4
-    for (int c = lane * 2; c < a_pad; c += 64) {
-      double v0 = 0.0, v1 = 0.0;
-      bool in0 = c < a, in1 = c + 1 < a;
-      if (vec_ok && in1) {
-        double2 t = *reinterpret_cast<const double2 *>(in + c);
-        v0 = t.x; v1 = t.y;
-      } else {
-        if (in0) v0 = in[c];
-        if (in1) v1 = in[c + 1];
-      }
+    auto one = [&](double v0, double v1, bool in0, bool in1, int c) {
       double x0 = in0 ? __dmul_rn(__dsub_rn(v0, sp.center), sp.scale) : 0.0;
       double x1 = in1 ? __dmul_rn(__dsub_rn(v1, sp.center), sp.scale) : 0.0;
       __half h0 = __double2half(x0), h1 = __double2half(x1);
@@ -96,6 +86,31 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
       esum += d0 * d0 + d1 * d1;
       xsum += x0 * x0 + x1 * x1;
       out[c >> 1] = __halves2half2(h0, h1);
+    };
+    int c0 = 0;
+    if (vec_ok) {
+      // whole 512-column blocks: eight independent 16-byte loads per lane are issued before any of
+      // them is used (8 KB in flight per warp), each a fully coalesced 512-byte warp access
+      for (; c0 + 512 <= a; c0 += 512) {
+        double2 t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = __ldcs(reinterpret_cast<const double2 *>(in + c0 + j * 64 + lane * 2));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) one(t[j].x, t[j].y, true, true, c0 + j * 64 + lane * 2);
+      }
+    }
+#pragma unroll 2
+    for (int c = c0 + lane * 2; c < a_pad; c += 64) {
+      double v0 = 0.0, v1 = 0.0;
+      bool in0 = c < a, in1 = c + 1 < a;
+      if (vec_ok && in1) {
+        double2 t = *reinterpret_cast<const double2 *>(in + c);
+        v0 = t.x; v1 = t.y;
+      } else {
+        if (in0) v0 = in[c];
+        if (in1) v1 = in[c + 1];
+      }
+      one(v0, v1, in0, in1, c);
     }
     for (int o = 16; o > 0; o >>= 1) {
       nsum += __shfl_xor_sync(0xFFFFFFFFu, nsum, o);
