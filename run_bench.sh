@@ -36,7 +36,7 @@ INPUT_ARGS_1=${INPUT_ARGS_1:-"--num_data 20000 --num_queries 2000 --num_attrs 32
 INPUT_ARGS_2=${INPUT_ARGS_2:-"--num_data 50000 --num_queries 4000 --num_attrs 64 --min -100 --max 100 --minK 16 --maxK 16 --num_labels 10"}
 INPUT_ARGS_3=${INPUT_ARGS_3:-"--num_data 30000 --num_queries 8000 --num_attrs 128 --min 0 --max 10 --minK 5 --maxK 5 --num_labels 4"}
 
-ngpu=$(nvidia-smi -L 2>/dev/null | wc -l)
+ngpu=${DMLP_NGPU:-$(nvidia-smi -L 2>/dev/null | wc -l)}   # DMLP_NGPU=<n> uses fewer GPUs than are visible
 grid_for() {  # layout per configuration on the GPUs that are visible
   local g=${ngpu:-0}; [ "$g" -lt 1 ] && g=1
   case "$1" in
@@ -87,7 +87,8 @@ run_config() {
     # come out once per rank and iteration, hence the sort -u
     tools/dmlp-mpirun -n "${REF_RANKS:-1}" baseline/_ref_build/engine_ref < "$inp" 2> "outputs/test_$n.err" | sort -u > "outputs/test_$n.out"
   else DMLP_BACKEND=cpu ./engine < "$inp" 2> "outputs/test_$n.err" > "outputs/test_$n.out"; fi
-  DMLP_GRID=${DMLP_GRID:-$(grid_for "$n")} ./engine < "$inp" 2> outputs/tmp.err > outputs/tmp.out || cat outputs/tmp.err
+  DMLP_GRID=${DMLP_GRID:-$(grid_for "$n")} ./engine --json < "$inp" 2> outputs/tmp.err > outputs/tmp.out || cat outputs/tmp.err
+  grep -o '"backend": "[^"]*"\|"time_ms": [0-9.]*' outputs/tmp.err | tr '\n' ' '; echo
   compare_times "outputs/test_$n.err" outputs/tmp.err
   compare_outputs "outputs/test_$n.out" outputs/tmp.out
 }
