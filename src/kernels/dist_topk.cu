@@ -523,78 +523,66 @@ __device__ void gather_warp(const TopkPlan &plan, const GatherArgs &ga, int lane
     }
     ready_mask |= 1u << owner;
   };
-  const int a_pad = plan.a_pad;
-  const int vec_per_row = a_pad / 8;  // int4 = 8 halves
-  const long long total_rows = static_cast<long long>(plan.mc_blocks) * plan.cluster * BM;
-  for (long long seq = b; seq < total_rows; seq += G) {
-    const int o = static_cast<int>(seq / BM), i = static_cast<int>(seq - static_cast<long long>(o) * BM);
+  const int vec_per_row = plan.a_pad / 8;  // int4 = 8 halves
+  // rows travel in groups of RB consecutive rows (one owner: slices are whole 256-row tiles), so
+  // that 32 lanes x 8 independent 16-byte loads = 4 KB are in flight per round trip for short rows too
+  int RB = 1;
+  while (RB < 8 && 2 * RB * vec_per_row <= 256) RB <<= 1;
+  const int gpb = BM / RB;  // groups per 128-row block
+  auto copy_vec = [&](const int4 *src, int4 *dst, int count) {  // contiguous, 16-byte units
+    for (int v0 = 0; v0 < count; v0 += 32 * 8) {
+      int4 tmp[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < count) tmp[u] = src[v];
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < count) dst[v] = tmp[u];
+      }
+    }
+  };
+  unsigned char *own = ga.peer_base[ga.rank];
+  const long long total_groups = static_cast<long long>(plan.mc_blocks) * plan.cluster * gpb;
+  for (long long seq = b; seq < total_groups; seq += G) {
+    const int o = static_cast<int>(seq / gpb), g = static_cast<int>(seq - static_cast<long long>(o) * gpb);
     const int cr = o / plan.cluster, j = o - cr * plan.cluster;
     const int m = ((cr + plan.rot) % plan.mc_blocks) * plan.cluster + j;
-    const long long grow = static_cast<long long>(m) * BM + i;
+    const long long grow = static_cast<long long>(m) * BM + g * RB;
     const int owner = static_cast<int>(grow / ga.slice_rows);
     if (owner != ga.rank && owner < ga.world) {
       wait_peer(owner);
-      if (!dead) {
-        const int4 *src = reinterpret_cast<const int4 *>(ga.peer_base[owner] + ga.off_qh) + grow * vec_per_row;
-        int4 *dst = reinterpret_cast<int4 *>(ga.peer_base[ga.rank] + ga.off_qh) + grow * vec_per_row;
-        for (int v0 = 0; v0 < vec_per_row; v0 += 32 * 8) {
-          int4 tmp[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < vec_per_row) tmp[u] = src[v];
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < vec_per_row) dst[v] = tmp[u];
-          }
-        }
-      }
+      if (!dead)
+        copy_vec(reinterpret_cast<const int4 *>(ga.peer_base[owner] + ga.off_qh) + grow * vec_per_row,
+                 reinterpret_cast<int4 *>(own + ga.off_qh) + grow * vec_per_row, RB * vec_per_row);
     }
     __syncwarp();
     if (lane == 0) {
       __threadfence();
-      atomicAdd(ga.rb_count + m, 1u);
+      atomicAdd(ga.rb_count + m, static_cast<unsigned>(RB));
     }
   }
-  // fp64 rows + per-query scalars of the remote slices, for the re-rank kernel
-  const long long qp = static_cast<long long>(ga.world) * ga.slice_rows;
-  const bool vec_ok = (ga.a % 2) == 0;
-  for (long long grow = b; grow < qp; grow += G) {
-    const int owner = static_cast<int>(grow / ga.slice_rows);
-    if (owner == ga.rank) continue;
+  // fp64 rows + per-query scalars of the remote slices, for the re-rank kernel: every slice is one
+  // contiguous span (slice_rows is a multiple of 256), copied in 4 KB pieces by all communication warps
+  for (int pj = 1; pj < ga.world && !dead; ++pj) {
+    const int owner = (ga.rank + pj) % ga.world;
     wait_peer(owner);
     if (dead) break;
-    const double *src = reinterpret_cast<const double *>(ga.peer_base[owner] + ga.off_q64) + grow * ga.a;
-    double *dst = reinterpret_cast<double *>(ga.peer_base[ga.rank] + ga.off_q64) + grow * ga.a;
-    if (vec_ok) {
-      const int n2 = ga.a / 2;
-      const double2 *s2 = reinterpret_cast<const double2 *>(src);
-      double2 *d2 = reinterpret_cast<double2 *>(dst);
-      for (int v0 = 0; v0 < n2; v0 += 32 * 8) {
-        double2 tmp[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int v = v0 + u * 32 + lane;
-          if (v < n2) tmp[u] = s2[v];
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int v = v0 + u * 32 + lane;
-          if (v < n2) d2[v] = tmp[u];
-        }
-      }
-    } else {
-      for (int v = lane; v < ga.a; v += 32) dst[v] = src[v];
+    const unsigned char *peer = ga.peer_base[owner];
+    const long long r0 = static_cast<long long>(owner) * ga.slice_rows;
+    const long long nvec = static_cast<long long>(ga.slice_rows) * ga.a / 2;   // slice_rows is even
+    const int4 *s4 = reinterpret_cast<const int4 *>(reinterpret_cast<const double *>(peer + ga.off_q64) + r0 * ga.a);
+    int4 *d4 = reinterpret_cast<int4 *>(reinterpret_cast<double *>(own + ga.off_q64) + r0 * ga.a);
+    for (long long v0 = static_cast<long long>(b) * 256; v0 < nvec; v0 += static_cast<long long>(G) * 256) {
+      const long long left = nvec - v0;
+      copy_vec(s4 + v0, d4 + v0, left < 256 ? static_cast<int>(left) : 256);
     }
-    if (lane == 0) {
-      reinterpret_cast<float *>(ga.peer_base[ga.rank] + ga.off_qn)[grow] =
-          reinterpret_cast<const float *>(ga.peer_base[owner] + ga.off_qn)[grow];
-      reinterpret_cast<float *>(ga.peer_base[ga.rank] + ga.off_qe)[grow] =
-          reinterpret_cast<const float *>(ga.peer_base[owner] + ga.off_qe)[grow];
-      reinterpret_cast<int *>(ga.peer_base[ga.rank] + ga.off_k)[grow] =
-          reinterpret_cast<const int *>(ga.peer_base[owner] + ga.off_k)[grow];
+    for (long long i = r0 + static_cast<long long>(b) * 32 + lane; i < r0 + ga.slice_rows; i += static_cast<long long>(G) * 32) {
+      reinterpret_cast<float *>(own + ga.off_qn)[i] = reinterpret_cast<const float *>(peer + ga.off_qn)[i];
+      reinterpret_cast<float *>(own + ga.off_qe)[i] = reinterpret_cast<const float *>(peer + ga.off_qe)[i];
+      reinterpret_cast<int *>(own + ga.off_k)[i] = reinterpret_cast<const int *>(peer + ga.off_k)[i];
     }
   }
 }
@@ -627,86 +615,92 @@ __device__ void data_gather_warp(const TopkPlan &plan, const DataGatherArgs &dg,
     return o;
   };
   const int vec_per_row = plan.a_pad / 8;  // int4 = 8 halves
+  // 32 lanes x 8 independent 16-byte loads = 4 KB in flight per warp and round trip: rows are
+  // taken in groups of RB consecutive rows so that short rows fill that window too (one row of
+  // a = 256 is only 512 bytes; a round trip over NVLink costs microseconds whatever its size)
+  int RB = 1;
+  while (RB < 8 && 2 * RB * vec_per_row <= 256) RB <<= 1;
+  const int gpt = BN / RB;  // groups per tile
+  auto copy_vec = [&](const int4 *src, int4 *dst, int count) {  // contiguous, 16-byte units
+    for (int v0 = 0; v0 < count; v0 += 32 * 8) {
+      int4 tmp[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < count) tmp[u] = src[v];
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < count) dst[v] = tmp[u];
+      }
+    }
+  };
   const int per_chunk = (plan.n_tiles + plan.chunks - 1) / plan.chunks;
-  const long long total = static_cast<long long>(per_chunk) * plan.chunks * BN;
+  const long long total = static_cast<long long>(per_chunk) * plan.chunks * gpt;
+  unsigned char *own = dg.peer_base[dg.rank];
   for (long long seq = b; seq < total; seq += G) {
-    const int i = static_cast<int>(seq % BN);
-    const long long ts = seq / BN;
+    const int g = static_cast<int>(seq % gpt);
+    const long long ts = seq / gpt;
     const int c = static_cast<int>(ts % plan.chunks), j = static_cast<int>(ts / plan.chunks);
     const int tb = static_cast<int>(static_cast<long long>(c) * plan.n_tiles / plan.chunks);
     const int te = static_cast<int>(static_cast<long long>(c + 1) * plan.n_tiles / plan.chunks);
     const int tile = tb + j;
     if (tile >= te) continue;
-    const int row = tile * BN + i;
-    if (row >= plan.n) continue;
-    const int owner = owner_of(row);
-    if (owner != dg.rank) {
-      wait_peer(owner);
-      if (!dead) {
-        const int4 *src = reinterpret_cast<const int4 *>(dg.peer_base[owner] + dg.off_xh) +
-                          static_cast<long long>(row) * vec_per_row;
-        int4 *dst = reinterpret_cast<int4 *>(dg.peer_base[dg.rank] + dg.off_xh) + static_cast<long long>(row) * vec_per_row;
-        for (int v0 = 0; v0 < vec_per_row; v0 += 32 * 8) {
-          int4 tmp[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < vec_per_row) tmp[u] = src[v];
+    const int row0 = tile * BN + g * RB;
+    const int rows = min(RB, plan.n - row0);
+    if (rows <= 0) continue;
+    // a group never straddles more than two parts; copy it part by part (usually in one piece)
+    for (int r = row0; r < row0 + rows;) {
+      const int owner = owner_of(r);
+      const int r_end = min(row0 + rows, dg.part_begin[owner + 1]);
+      if (owner != dg.rank) {
+        wait_peer(owner);
+        if (!dead) {
+          const unsigned char *peer = dg.peer_base[owner];
+          copy_vec(reinterpret_cast<const int4 *>(peer + dg.off_xh) + static_cast<long long>(r) * vec_per_row,
+                   reinterpret_cast<int4 *>(own + dg.off_xh) + static_cast<long long>(r) * vec_per_row,
+                   (r_end - r) * vec_per_row);
+          if (lane < r_end - r) {
+            reinterpret_cast<float *>(own + dg.off_xn)[r + lane] = reinterpret_cast<const float *>(peer + dg.off_xn)[r + lane];
+            reinterpret_cast<float *>(own + dg.off_xe)[r + lane] = reinterpret_cast<const float *>(peer + dg.off_xe)[r + lane];
           }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < vec_per_row) dst[v] = tmp[u];
-          }
-        }
-        if (lane == 0) {
-          reinterpret_cast<float *>(dg.peer_base[dg.rank] + dg.off_xn)[row] =
-              reinterpret_cast<const float *>(dg.peer_base[owner] + dg.off_xn)[row];
-          reinterpret_cast<float *>(dg.peer_base[dg.rank] + dg.off_xe)[row] =
-              reinterpret_cast<const float *>(dg.peer_base[owner] + dg.off_xe)[row];
         }
       }
+      r = r_end;
     }
     __syncwarp();
     if (lane == 0) {
       __threadfence();
-      atomicAdd(dg.tile_count + tile, 1u);
+      atomicAdd(dg.tile_count + tile, static_cast<unsigned>(rows));
     }
   }
-  // fp64 rows + labels of the other parts, for the re-rank kernel that follows
-  const bool vec_ok = (dg.a % 2) == 0;
+  // fp64 rows + labels of the other parts, for the re-rank kernel that follows: each part is one
+  // contiguous span, copied in 4 KB pieces spread over all communication warps
   for (int pj = 1; pj < dg.world && !dead; ++pj) {
     const int owner = (dg.rank + pj) % dg.world;
     wait_peer(owner);
     if (dead) break;
-    for (int row = dg.part_begin[owner] + b; row < dg.part_begin[owner + 1]; row += G) {
-      const double *src = reinterpret_cast<const double *>(dg.peer_base[owner] + dg.off_x64) +
-                          static_cast<long long>(row) * dg.a;
-      double *dst = reinterpret_cast<double *>(dg.peer_base[dg.rank] + dg.off_x64) + static_cast<long long>(row) * dg.a;
-      if (vec_ok) {
-        const int n2 = dg.a / 2;
-        const double2 *s2 = reinterpret_cast<const double2 *>(src);
-        double2 *d2 = reinterpret_cast<double2 *>(dst);
-        for (int v0 = 0; v0 < n2; v0 += 32 * 8) {
-          double2 tmp[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < n2) tmp[u] = s2[v];
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int v = v0 + u * 32 + lane;
-            if (v < n2) d2[v] = tmp[u];
-          }
-        }
-      } else {
-        for (int v = lane; v < dg.a; v += 32) dst[v] = src[v];
-      }
-      if (lane == 0)
-        reinterpret_cast<int *>(dg.peer_base[dg.rank] + dg.off_labels)[row] =
-            reinterpret_cast<const int *>(dg.peer_base[owner] + dg.off_labels)[row];
+    const unsigned char *peer = dg.peer_base[owner];
+    const long long e0 = static_cast<long long>(dg.part_begin[owner]) * dg.a;       // first double of the part
+    const long long e1 = static_cast<long long>(dg.part_begin[owner + 1]) * dg.a;   // one past its last
+    const double *src = reinterpret_cast<const double *>(peer + dg.off_x64);
+    double *dst = reinterpret_cast<double *>(own + dg.off_x64);
+    long long lo = e0, hi = e1;
+    if (lo & 1) { if (b == 0 && lane == 0 && lo < hi) dst[lo] = src[lo]; ++lo; }      // 16-byte alignment of the bulk
+    if ((hi & 1) && hi > lo) { --hi; if (b == 0 && lane == 1) dst[hi] = src[hi]; }
+    const long long nvec = hi > lo ? (hi - lo) / 2 : 0;
+    const int4 *s4 = reinterpret_cast<const int4 *>(src + lo);
+    int4 *d4 = reinterpret_cast<int4 *>(dst + lo);
+    for (long long v0 = static_cast<long long>(b) * 256; v0 < nvec; v0 += static_cast<long long>(G) * 256) {
+      const long long left = nvec - v0;
+      copy_vec(s4 + v0, d4 + v0, left < 256 ? static_cast<int>(left) : 256);
     }
+    const int *sl = reinterpret_cast<const int *>(peer + dg.off_labels);
+    int *dl = reinterpret_cast<int *>(own + dg.off_labels);
+    for (long long i = dg.part_begin[owner] + static_cast<long long>(b) * 32 + lane; i < dg.part_begin[owner + 1];
+         i += static_cast<long long>(G) * 32)
+      dl[i] = sl[i];
   }
 }
 
