@@ -38,6 +38,69 @@ def _round_up(v, m):
     return (v + m - 1) // m * m
 
 
+def simulate_copy_order(order, q_rows, x_rows, a, bytes_per_value=4, pcie_gbs=52.0, gemm_pflops=1.2, hbm_tbs=5.5,
+                        pairs_per_query=16.0):
+    """Makespan (ms) of one end-to-end step for a given copy order of query chunks and data parts.
+
+    One copy stream moves the pieces back to back; the compute stream runs, in the order the
+    step enqueues them, the expand + pack of an arrived piece, the filter GEMM of every (query
+    chunk, data part) pair as soon as both are there, and a chunk's re-rank once its last pair
+    is done.  Costs are first-order: bytes over PCIe, 2 q x a flops at the sustained GEMM rate,
+    HBM bytes for pack and for the re-rank's row fetches."""
+    t_copy = t_gpu = 0.0
+    have_q, have_x, done, reranked = [], [], set(), set()
+    for kind, idx in order:
+        rows = q_rows[idx] if kind == "q" else x_rows[idx]
+        t_copy += rows * a * bytes_per_value / (pcie_gbs * 1e6)
+        # expand (decimal6 only) + pack: read wire, write + read fp64, write fp16
+        t_gpu = max(t_gpu, t_copy) + rows * a * (bytes_per_value + 8 + 8 + 2) / (hbm_tbs * 1e9)
+        (have_q if kind == "q" else have_x).append(idx)
+        for i in sorted(have_q):
+            for p_ in sorted(have_x):
+                if (i, p_) not in done:
+                    done.add((i, p_))
+                    t_gpu += 2.0 * q_rows[i] * x_rows[p_] * a / (gemm_pflops * 1e12)
+            if i not in reranked and all((i, p_) in done for p_ in range(len(x_rows))):
+                reranked.add(i)
+                t_gpu += q_rows[i] * pairs_per_query * a * 8 / (hbm_tbs * 1e9)
+    return t_gpu
+
+
+def best_copy_order(q_rows, x_rows, a, bytes_per_value=4, limit=40000, **model):
+    """The interleaving of query chunks and data parts (each kind in index order) with the
+    smallest simulated makespan; exhaustive while the number of interleavings stays small."""
+    from itertools import combinations
+    from math import comb
+    nq, nx = len(q_rows), len(x_rows)
+
+    def alternate():
+        order, xi, qi = [("q", 0), ("x", 0)], 1, 1
+        while xi < nx or qi < nq:
+            if xi < nx:
+                order.append(("x", xi))
+                xi += 1
+            if qi < nq:
+                order.append(("q", qi))
+                qi += 1
+        return order
+    if nq == 0 or nx == 0 or comb(nq + nx, nx) > limit:
+        return alternate()
+    best, best_t = None, float("inf")
+    for slots in combinations(range(nq + nx), nx):       # positions of the data parts
+        taken, order, qi, xi = set(slots), [], 0, 0
+        for pos in range(nq + nx):
+            if pos in taken:
+                order.append(("x", xi))
+                xi += 1
+            else:
+                order.append(("q", qi))
+                qi += 1
+        t = simulate_copy_order(order, q_rows, x_rows, a, bytes_per_value, **model)
+        if t < best_t:
+            best, best_t = order, t
+    return best
+
+
 class DistributedKNN:
     def __init__(self, device=None, impl="fused", grid=None):
         self.device = torch.device(device if device is not None else "cuda")
@@ -409,7 +472,7 @@ class DistributedKNN:
     def last_flagged(self, value):
         self._flagged_host = value
 
-    def ensure_repaired(self):
+    def ensure_repaired(self, force=False):
         """End-of-step check: up to REPAIR_CAP flagged queries are repaired on the device by the step
         itself; only beyond that (never seen on the generator's distributions) the host steps in,
         re-runs every flagged query on the direct kernel and finalizes again.  Returns the count."""
@@ -419,7 +482,7 @@ class DistributedKNN:
             t = torch.tensor([flagged], dtype=torch.int32, device=self.device)
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.col_group)
             worst = int(t.item())
-        if worst <= K.REPAIR_CAP:
+        if worst <= K.REPAIR_CAP and not force:
             return flagged
         if self.peer_fused:
             self._repair_flagged_host()
@@ -523,7 +586,7 @@ class DistributedKNN:
         return self.final[0][:self.nq], self.final[1][:self.nq]
 
     # ---------------------------------------------------------------- end to end
-    E2E_CHUNK_ROWS = 18944   # 74 cluster rows of 256 queries: whole waves of the filter GEMM
+    E2E_CHUNK_ROWS = 9472    # 37 cluster rows of 256 queries x 2 chunks: one whole wave of the filter GEMM
 
     def stage_host_inputs(self, wire="auto"):
         """The loader's output: this rank's inputs in pinned host memory, plus the value
@@ -568,35 +631,61 @@ class DistributedKNN:
             rows = min(int(os.environ.get("DMLP_E2E_QROWS", self.E2E_CHUNK_ROWS)), max(self.nq, 1))
             self.chunk_rows = rows
             if use_dec:
-                self.x_wire = torch.empty(self.x_part.shape, dtype=torch.int32, device=dev)
-                self.q_wire = [torch.empty((rows, self.a), dtype=torch.int32, device=dev) for _ in range(2)]
+                # two complete sets of wire buffers: the copies of step s + 1 run while step s computes
+                self.x_wire = [torch.empty(self.x_part.shape, dtype=torch.int32, device=dev) for _ in range(2)]
+                self.q_wire = [torch.empty((max(self.nq, 1), self.a), dtype=torch.int32, device=dev) for _ in range(2)]
+                self.l_wire = [torch.empty_like(self.labels_part) for _ in range(2)]
+                self.k_wire = [torch.empty_like(self.k_slice) for _ in range(2)]
+            self._e2e_step, self._prefetched = 0, None
             nchunks = max(1, -(-max(self.nq, 1) // rows))
             self.nflag_chunks = torch.zeros(nchunks, dtype=torch.int32, device=dev)
             self.flagged_rows_chunks = torch.zeros((nchunks, K.REPAIR_CAP), dtype=torch.int32, device=dev)
             self.host_nflag = torch.zeros(nchunks, dtype=torch.int32).pin_memory()
             self.d2h_bytes_per_step += self.host_nflag.numel() * 4
             self._cand_by_rows = {}
-            self.x_parts = max(1, int(os.environ.get("DMLP_E2E_XPARTS", "4")))
-            if self.shard_rows < 4096 * self.x_parts:
-                self.x_parts = 1
+            self.x_parts = max(1, int(os.environ.get("DMLP_E2E_XPARTS", "8")))
+            while self.x_parts > 1 and self.shard_rows < 4096 * self.x_parts:
+                self.x_parts //= 2
             self._tiled = None
             torch.cuda.synchronize(dev)
 
-    def run_from_host(self):
+    def run_from_host(self, prefetch_next=False):
         """Public end-to-end call: pinned host inputs -> device -> job -> host results.
-        With a single-rank column the copy of the next query chunk overlaps the
-        kernels of the current one (two streams)."""
+        With a single-rank column the copies overlap the kernels (two streams).  With
+        `prefetch_next` (decimal6 wire only) the call also starts the host-to-device copies of the
+        NEXT call's inputs (the staged host buffers) into the second set of wire buffers before it
+        waits for its own results -- the input pipeline of a serving loop: PCIe stays busy while
+        the GPU finishes this step's tail."""
         with torch.cuda.device(self.device):
             self._flagged_host = None
-            if getattr(self, "streamed", False) and self.world == 1 and self.x_parts > 1:
-                label, checksum = self._run_tiled()
-            elif getattr(self, "streamed", False):
-                label, checksum = self._run_streamed()
+            self._want_prefetch = bool(prefetch_next) and self.wire == "decimal6" and getattr(self, "streamed", False)
+            streamed = getattr(self, "streamed", False)
+            pipelined = streamed and self._prefetched is not None and self._prefetched[0] == (self._e2e_step & 1)
+            if pipelined:
+                # this step's inputs were copied (or are being copied) into wire set `slot` during the
+                # previous call: start the next call's copies first, so PCIe never idles, then run the
+                # whole-size kernels on what has arrived -- a two-stage pipeline, copy | compute
+                slot, pieces, events = self._prefetched
+                nxt = (slot ^ 1, pieces, self._copy_pieces(pieces, slot ^ 1)) if self._want_prefetch else None
+                label, checksum = self._run_from_wire(slot, events)
+                self._e2e_step += 1
+                self._prefetched = nxt
             else:
-                label, checksum = self._run_copy_then_compute()
+                if streamed and self.world == 1 and self.x_parts > 1:
+                    label, checksum = self._run_tiled()
+                elif streamed:
+                    label, checksum = self._run_streamed()
+                else:
+                    label, checksum = self._run_copy_then_compute()
+                if streamed:
+                    self._e2e_step += 1
+                    self._prefetched = None
+                    if self._want_prefetch:
+                        slot = self._e2e_step & 1
+                        self._prefetched = (slot, self._pieces, self._copy_pieces(self._pieces, slot))
             self.host_out[0].copy_(label, non_blocking=True)
             self.host_out[1].copy_(checksum, non_blocking=True)
-            streamed = getattr(self, "streamed", False)
+            streamed = streamed and not pipelined      # (which flagged-query counter this step used)
             counted = self._flagged_host is None and self.fused_ok and self.impl == "fused"
             if counted and streamed:
                 self.host_nflag.copy_(self.nflag_chunks, non_blocking=True)
@@ -607,11 +696,23 @@ class DistributedKNN:
                 worst = int(self.host_nflag.max()) if streamed else int(self.host_nflag[0])
                 self._flagged_host = int(self.host_nflag.sum()) if streamed else worst
                 if worst > K.REPAIR_CAP:   # beyond what the step repairs by itself (not seen in practice)
-                    self._flagged_host = None
-                    self.ensure_repaired()
+                    self.ensure_repaired(force=True)
                     self.host_out[0].copy_(self.final[0][:self.nq])
                     self.host_out[1].copy_(self.final[1][:self.nq])
             return self.host_out
+
+    def _run_from_wire(self, slot, events):
+        """A step whose inputs already sit (decimal6) in wire set `slot`: expand them and run the
+        resident pipeline at full size."""
+        main = torch.cuda.current_stream()
+        main.wait_event(events[-1])            # one copy stream, in order: the last piece closes the set
+        self._wait_part_readers()              # the row's peers may still be pulling the previous step's rows
+        self._install_small(slot, events)
+        K.expand_decimal6(self.x_wire[slot], self.x_part)
+        K.expand_decimal6(self.q_wire[slot][: self.nq], self.q_slice)
+        K.stats_set(self.stats, *self.host_range)
+        self.launch_count += 2
+        return self.run_resident()
 
     def _rerank_chunk(self, i, b, e, cand):
         """Re-rank + folded vote + device-side repair of query rows [b, e) (chunk i of a streamed step)."""
@@ -637,12 +738,10 @@ class DistributedKNN:
         h = self.host
         self._wait_part_readers()
         if self.wire == "decimal6":
-            self.x_wire.copy_(h["x"], non_blocking=True)
-            K.expand_decimal6(self.x_wire, self.x_part)
-            for b in range(0, self.nq, self.chunk_rows):
-                e = min(b + self.chunk_rows, self.nq)
-                self.q_wire[0][: e - b].copy_(h["q"][b:e], non_blocking=True)
-                K.expand_decimal6(self.q_wire[0][: e - b], self.q_slice[b:e])
+            self.x_wire[0].copy_(h["x"], non_blocking=True)
+            K.expand_decimal6(self.x_wire[0], self.x_part)
+            self.q_wire[0][: self.nq].copy_(h["q"], non_blocking=True)
+            K.expand_decimal6(self.q_wire[0][: self.nq], self.q_slice)
         else:
             self.x_part.copy_(h["x"], non_blocking=True)
             self.q_slice.copy_(h["q"], non_blocking=True)
@@ -669,30 +768,66 @@ class DistributedKNN:
                 acc += K.topk_plan(e - b, pe - pb, self.a_pad, kmax=self.kmax)["chunks"]
             bases.append(base)
             cands.append(torch.empty((e - b, acc, K.KP), dtype=torch.int64, device=self.device))
-        # copy order: q0, x0, then alternate data parts and query chunks
-        order, xi, qi = [("q", 0), ("x", 0)], 1, 1
-        while xi < len(xparts) or qi < len(qch):
-            if xi < len(xparts):
-                order.append(("x", xi))
-                xi += 1
-            if qi < len(qch):
-                order.append(("q", qi))
-                qi += 1
+        # copy order: the interleaving with the smallest simulated makespan (the work is a product
+        # of queries x data, so what arrives last decides how much is left to do after the copies)
+        order = best_copy_order([e - b for b, e in qch], [pe - pb for pb, pe in xparts], self.a,
+                                4 if self.wire == "decimal6" else 8)
         self._tiled = (xparts, qch, cands, bases, order)
         return self._tiled
 
+    def _copy_pieces(self, pieces, slot):
+        """Enqueue on the copy stream, in order, the host-to-device copies of `pieces` -- (kind, begin,
+        end) row ranges of the data part ("x") or of the queries ("q") -- into wire set `slot`
+        (decimal6) or straight into the compute buffers (fp64 wire).  One event per piece."""
+        h, cs, dec = self.host, self.copy_stream, self.wire == "decimal6"
+        events = []
+        with torch.cuda.stream(cs):
+            for kind, b, e in pieces:
+                if kind == "x":
+                    (self.x_wire[slot] if dec else self.x_part)[b:e].copy_(h["x"][b:e], non_blocking=True)
+                elif kind == "q":
+                    (self.q_wire[slot] if dec else self.q_slice)[b:e].copy_(h["q"][b:e], non_blocking=True)
+                elif kind == "l":     # labels and k travel first, in the same queue as everything else
+                    (self.l_wire[slot] if dec else self.labels_part).copy_(h["labels"], non_blocking=True)
+                else:
+                    (self.k_wire[slot] if dec else self.k_slice).copy_(h["k"], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                events.append(ev)
+        return events
+
+    def _step_copies(self, pieces):
+        """Events of this step's copies: the ones a previous call prefetched, or enqueued now."""
+        slot = self._e2e_step & 1
+        self._pieces = pieces
+        if self._prefetched is not None and self._prefetched[0] == slot and self._prefetched[1] == pieces:
+            return slot, self._prefetched[2]
+        if self.wire != "decimal6":
+            self.copy_stream.wait_stream(torch.cuda.current_stream())   # the compute buffers themselves are the target
+        return slot, self._copy_pieces(pieces, slot)
+
+    def _install_small(self, slot, events):
+        """Labels and k of this step: they were copied first (pieces 0 and 1); on the decimal6 path
+        they sit in the wire set and are moved into place by two small kernels (not by copies: a
+        copy would queue behind the large transfers the copy engine is working through)."""
+        main = torch.cuda.current_stream()
+        main.wait_event(events[1])
+        if self.wire == "decimal6":
+            torch.add(self.l_wire[slot], 0, out=self.labels_part)
+            torch.add(self.k_wire[slot], 0, out=self.k_slice)
+
+    def _small_pieces(self):
+        return [("l", 0, int(self.labels_part.numel())), ("k", 0, int(self.k_slice.numel()))]
+
     def _run_tiled(self):
-        h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream
+        main = torch.cuda.current_stream()
         dec = self.wire == "decimal6"
         xparts, qch, cands, bases, order = self._tiled_schedule()
-        od, oi, ol, flags, nflag = self.lists
-        cs.wait_stream(main)                      # previous step's readers of the buffers are done
+        pieces = self._small_pieces() + [("x",) + tuple(xparts[i]) if kind == "x" else ("q",) + tuple(qch[i])
+                                         for kind, i in order]
         self.epoch += 1
-        e_small = torch.cuda.Event()
-        with torch.cuda.stream(cs):
-            self.labels_part.copy_(h["labels"], non_blocking=True)
-            self.k_slice.copy_(h["k"], non_blocking=True)
-            e_small.record(cs)
+        slot, events = self._step_copies(pieces)
+        self._install_small(slot, events)
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
@@ -700,36 +835,18 @@ class DistributedKNN:
         self.launch_count += 2
         have_x, have_q = set(), set()
         done, reranked = set(), set()
-        e_free, n_qcopies = [None, None], 0
-        for kind, idx in order:
-            ev = torch.cuda.Event()
+        for (kind, idx), ev in zip(order, events[2:]):
+            main.wait_event(ev)
             if kind == "x":
                 pb, pe = xparts[idx]
-                with torch.cuda.stream(cs):
-                    (self.x_wire if dec else self.x_part)[pb:pe].copy_(h["x"][pb:pe], non_blocking=True)
-                    ev.record(cs)
-                main.wait_event(ev)
                 if dec:
-                    K.expand_decimal6(self.x_wire[pb:pe], self.x_part[pb:pe])
+                    K.expand_decimal6(self.x_wire[slot][pb:pe], self.x_part[pb:pe])
                 K.pack(self.x[pb:pe], self.stats, self.stats, out=(self.xh[pb:pe], self.xn[pb:pe], self.xe[pb:pe]))
                 have_x.add(idx)
             else:
                 b, e = qch[idx]
-                slot = n_qcopies & 1
-                n_qcopies += 1
-                with torch.cuda.stream(cs):
-                    if dec:
-                        if e_free[slot] is not None:
-                            cs.wait_event(e_free[slot])      # the expand two chunks ago has drained this buffer
-                        self.q_wire[slot][: e - b].copy_(h["q"][b:e], non_blocking=True)
-                    else:
-                        self.q_slice[b:e].copy_(h["q"][b:e], non_blocking=True)
-                    ev.record(cs)
-                main.wait_event(ev)
                 if dec:
-                    K.expand_decimal6(self.q_wire[slot][: e - b], self.q_slice[b:e])
-                    e_free[slot] = torch.cuda.Event()
-                    e_free[slot].record(main)
+                    K.expand_decimal6(self.q_wire[slot][b:e], self.q_slice[b:e])
                 K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(self.qh[b:e], self.qn[b:e], self.qe_[b:e]))
                 have_q.add(idx)
             self.launch_count += 1 + (1 if dec else 0)
@@ -744,31 +861,30 @@ class DistributedKNN:
                     done.add((i, p_))
                     self.launch_count += 1
                 if i not in reranked and all((i, p_) in done for p_ in range(len(xparts))):
-                    main.wait_event(e_small)
                     self._rerank_chunk(i, b, e, cands[i])
                     reranked.add(i)
         return self.final[0][:self.nq], self.final[1][:self.nq]
 
     def _run_streamed(self):
-        h, main, cs = self.host, torch.cuda.current_stream(), self.copy_stream
+        main = torch.cuda.current_stream()
         dec = self.wire == "decimal6"
         nq, rows = self.nq, self.chunk_rows
         chunks = [(b, min(b + rows, nq)) for b in range(0, nq, rows)]
-        cs.wait_stream(main)                      # previous step's readers of the buffers are done
-        e_x = torch.cuda.Event()
-        e_q = [torch.cuda.Event() for _ in chunks]
-        e_free = [None, None]
-        with torch.cuda.stream(cs):
+        n_part = self.part_rows[1] - self.part_rows[0]
+        pieces = self._small_pieces() + [("x", 0, n_part)] + [("q", b, e) for b, e in chunks]
+        # the rows, labels and packed rows of this rank's part are what the row's peers pull from: nothing
+        # may overwrite them before every peer has finished with the previous step's copy
+        if not dec:
             self._wait_part_readers()
-            (self.x_wire if dec else self.x_part).copy_(h["x"], non_blocking=True)
-            self.labels_part.copy_(h["labels"], non_blocking=True)
-            self.k_slice.copy_(h["k"], non_blocking=True)
-            e_x.record(cs)
-        # data shard: expand, all-gather along the row, pack
+        slot, events = self._step_copies(pieces)
         self.epoch += 1
-        main.wait_event(e_x)
+        main.wait_event(events[2])
         if dec:
-            K.expand_decimal6(self.x_wire, self.x_part)
+            self._wait_part_readers(self.epoch - 1)
+        self._install_small(slot, events)
+        # data shard: expand, all-gather along the row, pack
+        if dec:
+            K.expand_decimal6(self.x_wire[slot], self.x_part)
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
@@ -781,19 +897,9 @@ class DistributedKNN:
         K.zero_(self.nflag_chunks)
         self.launch_count += 4 + (1 if dec else 0)
         for i, (b, e) in enumerate(chunks):
-            with torch.cuda.stream(cs):
-                if dec:
-                    if e_free[i & 1] is not None:
-                        cs.wait_event(e_free[i & 1])          # the expand of chunk i-2 has drained this buffer
-                    self.q_wire[i & 1][: e - b].copy_(h["q"][b:e], non_blocking=True)
-                else:
-                    self.q_slice[b:e].copy_(h["q"][b:e], non_blocking=True)
-                e_q[i].record(cs)
-            main.wait_event(e_q[i])
+            main.wait_event(events[3 + i])
             if dec:
-                K.expand_decimal6(self.q_wire[i & 1][: e - b], self.q_slice[b:e])
-                e_free[i & 1] = torch.cuda.Event()
-                e_free[i & 1].record(main)
+                K.expand_decimal6(self.q_wire[slot][b:e], self.q_slice[b:e])
             qh, qn, qe = self.qh[b:e], self.qn[b:e], self.qe_[b:e]
             K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(qh, qn, qe))
             key = e - b

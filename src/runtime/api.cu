@@ -20,6 +20,10 @@ using namespace dmlp::k;
 
 static_assert(sizeof(PackStats) <= DMLP_STATS_BYTES, "stats block size");
 
+static __global__ void stats_set_kernel(PackStats *st, double neg_lo, double hi) {
+  if (threadIdx.x == 0) { st->neg_lo = neg_lo; st->hi = hi; }
+}
+
 // An empty shard has no neighbours to offer: every list is padding, no query is flagged.
 static __global__ void __launch_bounds__(256) fill_empty_lists_kernel(double *dist, int *id, int *label, int *flags,
                                                                long long slots, int q) {
@@ -121,8 +125,10 @@ int dmlp_encode_decimal6(const double *src, int *dst, int64_t count, int *bad, v
 }
 
 int dmlp_stats_set(void *stats, double lo, double hi, void *stream) {
-  const double v[2] = {-lo, hi};
-  DMLP_CUDA_OK(cudaMemcpyAsync(stats, v, sizeof v, cudaMemcpyHostToDevice, st(stream)));
+  // a kernel, not a copy: a host-to-device copy would queue behind whatever large transfers the
+  // copy engine is busy with (the end-to-end loop keeps it busy all the time)
+  stats_set_kernel<<<1, 32, 0, st(stream)>>>(static_cast<PackStats *>(stats), -lo, hi);
+  DMLP_CUDA_OK(cudaGetLastError());
   return 0;
 }
 

@@ -211,3 +211,18 @@ def test_blocked_simd_kernel_matches_a_numpy_restatement(n, q, a, kmax, seed):
         assert np.array_equal(od, want_d)      # bit for bit
         real = oi >= 0
         assert np.array_equal(ol[real], labels[oi[real] - 11])
+
+
+def test_copy_order_planner_beats_plain_alternation():
+    """End-to-end schedule: the simulated makespan of the chosen interleaving of query chunks and
+    data parts is never worse than plain alternation, and every piece appears exactly once."""
+    from dmlp_b200.parallel.engine import best_copy_order, simulate_copy_order
+    q, x = [9472] * 6 + [65536 - 6 * 9472], [8192] * 8
+    order = best_copy_order(q, x, 8192)
+    assert sorted(order) == sorted([("q", i) for i in range(7)] + [("x", i) for i in range(8)])
+    assert [i for k, i in order if k == "q"] == list(range(7)) and [i for k, i in order if k == "x"] == list(range(8))
+    alt = [("q", 0), ("x", 0)] + [p for i in range(1, 8) for p in ([("x", i)] + ([("q", i)] if i < 7 else []))]
+    assert simulate_copy_order(order, q, x, 8192) <= simulate_copy_order(alt, q, x, 8192)
+    # too many interleavings to enumerate: falls back to alternation, still a valid order
+    big = best_copy_order([100] * 20, [100] * 20, 64)
+    assert len(big) == 40 and big[0] == ("q", 0) and big[1] == ("x", 0)

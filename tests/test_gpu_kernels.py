@@ -337,7 +337,7 @@ def test_decimal6_wire_round_trip(K):
     assert not K.encode_decimal6(big)[1]
 
 
-@pytest.mark.parametrize("n_total,parts", [(9000, 1), (20000, 4)])
+@pytest.mark.parametrize("n_total,parts", [(3000, 1), (9000, 2), (20000, 4)])
 def test_streamed_end_to_end_single_gpu(K, n_total, parts):
     """run_from_host: copies overlapped with compute; with a large enough shard the data is
     cut into parts and every (query chunk, data part) pair is filtered as it arrives."""
@@ -350,7 +350,7 @@ def test_streamed_end_to_end_single_gpu(K, n_total, parts):
     for wire in ("auto", "fp64"):
         eng.stage_host_inputs(wire=wire)
         assert eng.streamed and eng.wire == ("decimal6" if wire == "auto" else "fp64") and eng.x_parts == parts
-        for _ in range(2):
-            _, chk = eng.run_from_host()
+        for step in range(4):      # steps 0 and 1 also start the next step's copies (second wire set)
+            _, chk = eng.run_from_host(prefetch_next=step < 2)
             assert (chk.numpy() == ref).all(), wire
     assert eng.verify_against_oracle(200) == 200
