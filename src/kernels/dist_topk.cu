@@ -159,6 +159,11 @@ using Layout1 = Layout<STAGES, B_BYTES>;            // one CTA per 128 x 256 til
 constexpr int STAGES2 = 4;
 using Layout2 = Layout<STAGES2, B_BYTES / 2>;       // CTA pair per 256 x 256 tile
 
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
@@ -198,29 +203,30 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
       const uint32_t acc_phase = (acc ? uses[1] : uses[0]) & 1;
       if (acc) ++uses[1]; else ++uses[0];
       float *xn = xn_all + (acc_it & 1) * BN;  // (not `acc`: two tiles in a row can share a stage across items)
-      // The data norms of the tile are staged while its MMAs still run -- unless the rows (and their
-      // norms) are being gathered from peer GPUs by this very kernel: then they are only known to be
-      // in place once the tile's MMAs have completed (the TMA producer waited for the tile's arrival
-      // counter), so the staging follows the accumulator wait.
+      // The data norms of the tile are staged while its MMAs still run.  When the rows (and their
+      // norms) are being gathered from peer GPUs by this very kernel, one thread first makes sure the
+      // tile has arrived (the counter the TMA producer waited on before it loaded the tile, so this
+      // hardly ever spins); staging without that check raced with the gather.
       const long long ps0 = prof ? clock64() : 0;
-      if (!plan.late_norms) {
-        for (int i = e_tid; i < BN; i += EPI_THREADS) {
-          const int col = tile * BN + i;
-          xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
+      if (plan.gate_cnt != nullptr) {
+        if (e_tid == 0) {
+          const int rows_in_tile = min(BN, plan.n - tile * BN);
+          const unsigned target = plan.gate_epoch * static_cast<unsigned>(rows_in_tile);
+          const long long t0 = clock64();
+          while (static_cast<int>(ld_acquire_gpu_u32(plan.gate_cnt + tile) - target) < 0)
+            if (clock64() - t0 > 4000000000LL) break;   // the producer's own watchdog reports a lost peer
         }
         named_barrier_sync(1, EPI_THREADS);
       }
+      for (int i = e_tid; i < BN; i += EPI_THREADS) {
+        const int col = tile * BN + i;
+        xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
+      }
+      named_barrier_sync(1, EPI_THREADS);
       const long long pw0 = prof ? clock64() : 0;
       if (prof) prof_stage += pw0 - ps0;
       mbar_wait(&tfull_bar[acc], acc_phase);
       if (prof) prof_wait += clock64() - pw0;
-      if (plan.late_norms) {
-        for (int i = e_tid; i < BN; i += EPI_THREADS) {
-          const int col = tile * BN + i;
-          xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
-        }
-        named_barrier_sync(1, EPI_THREADS);
-      }
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       // (one tcgen05.ld in flight at a time: overlapping the load of the next 32 columns with
@@ -1118,7 +1124,8 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   // skewed wide schedule (opt-in): steps an accumulator rests between two tiles (its drain; the
   // other accumulator keeps the tensor pipe busy meanwhile).  DMLP_TOPK_GAP=<steps>; the default
   // -1 is the lock-step wide tile (both accumulators fill side by side and drain while the MMA waits)
-  p.late_norms = 0;
+  p.gate_cnt = nullptr;
+  p.gate_epoch = 0;
   p.gap = -1;   // measured on B200: the skewed schedule is slower (65.9 vs 57 ms on the headline shape), see DESIGN.md
   if (const char *e = getenv("DMLP_TOPK_GAP")) p.gap = atoi(e);
   if (p.gap > p.k_blocks - 2) p.gap = p.k_blocks - 2;
@@ -1314,7 +1321,8 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   DMLP_REQUIRE(ga.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
   DataGatherArgs dg;
   if (data_gather != nullptr) dg = *data_gather;
-  plan.late_norms = dg.world > 1 ? 1 : 0;
+  plan.gate_cnt = dg.world > 1 ? dg.tile_count : nullptr;
+  plan.gate_epoch = dg.epoch;
   DMLP_REQUIRE(dg.world == 1 || plan.pair, "dist_topk: the fused data gather needs the CTA-pair kernel");
   DMLP_REQUIRE(dg.world <= kMaxPeers, "dist_topk: at most 8 ranks share one gather");
   cfg.stream = s;

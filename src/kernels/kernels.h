@@ -65,7 +65,8 @@ struct TopkPlan {
   int chunk_base;  ///< first list index this launch writes
   int row_base;    ///< added to the row ids this launch emits (the operand is a slice of a larger shard)
   int wide;        ///< pair kernel only: 1 = one query tile meets two data tiles per k-block (256 x 512 per pair; query tiles are read half as often)
-  int late_norms;  ///< 1: the data rows are gathered from peers by the kernel itself; the epilogue stages a tile's norms only after its MMAs
+  const unsigned *gate_cnt;  ///< set when the data rows are gathered from peers by the kernel itself: per-tile arrival counters the epilogue checks before it stages a tile's norms
+  unsigned gate_epoch;
   int gap;         ///< wide only: >= 0 = skewed schedule, steps an accumulator rests between tiles; -1 = lock-step wide tile
   unsigned long long *prof;  ///< diagnostics (DMLP_TOPK_PROF=1): per CTA 16 cycle counters, see dist_topk_prof_read
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
