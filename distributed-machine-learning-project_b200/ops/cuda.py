@@ -184,11 +184,11 @@ def exact_workspace_bytes(n, count, kmax):
     return int(_lib().dmlp_exact_workspace_bytes(n, count, kmax))
 
 
-def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=None, workspace=None):
+def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=None, workspace=None, x_i32=None):
     """Direct fp64 brute force (streaming bounded lists, any k) for all query rows, or the subset
     `query_rows` (int32)."""
     q, a = q_attrs.shape
-    n = x_attrs.shape[0]
+    n = (x_attrs if x_attrs is not None else x_i32).shape[0]
     dev = q_attrs.device
     count = q if query_rows is None else int(query_rows.numel())
     if out is None:
@@ -198,6 +198,16 @@ def exact(q_attrs, x_attrs, x_labels, k, kmax, id_base=0, query_rows=None, out=N
     if workspace is None:
         workspace = torch.empty(exact_workspace_bytes(n, count, kmax), dtype=torch.uint8, device=dev)
     od, oi, ol = out
+    if x_i32 is not None:      # decimal6 rows
+        lib = _lib()
+        lib.dmlp_exact_ex.argtypes = [C.POINTER(ExactArgs), _vp]
+        g = ExactArgs()
+        g.q_attrs, g.x_attrs, g.x_labels, g.k, g.query_rows = _ptr(q_attrs), 0, _ptr(x_labels), _ptr(k), _ptr(query_rows)
+        g.count, g.n, g.a, g.id_base, g.kmax = count, n, a, id_base, kmax
+        g.out_dist, g.out_id, g.out_label = _ptr(od), _ptr(oi), _ptr(ol)
+        g.workspace, g.workspace_bytes, g.x_attrs_i32 = _ptr(workspace), workspace.numel(), _ptr(x_i32)
+        _check(lib.dmlp_exact_ex(C.byref(g), _stream()))
+        return od, oi, ol
     _check(_lib().dmlp_exact(_p(q_attrs), _p(x_attrs), _p(x_labels), _p(k), _p(query_rows), count, n, a, id_base,
                              kmax, _p(od), _p(oi), _p(ol), _p(workspace), workspace.numel(), _stream()))
     return od, oi, ol
@@ -276,7 +286,7 @@ class DataGatherArgs(C.Structure):
     _fields_ = [("world", _i), ("rank", _i), ("a", _i), ("epoch", C.c_uint32), ("peer_base", _vp * 8),
                 ("off_xh", _u64), ("off_xn", _u64), ("off_xe", _u64), ("off_x64", _u64), ("off_labels", _u64),
                 ("off_pack_flags", _u64), ("part_begin", _i * 9), ("tile_count", _vp), ("status", _vp),
-                ("timeout_seconds", _dbl), ("done_signal", _vp)]
+                ("timeout_seconds", _dbl), ("done_signal", _vp), ("x_i32", _i)]
 
 
 def dist_topk_rows(qh, n, cand, gather, kmax=0):
@@ -357,7 +367,7 @@ class RerankArgs(C.Structure):
                 ("a", _i), ("a_pad", _i), ("id_base", _i), ("kmax", _i), ("out_dist", _vp), ("out_id", _vp),
                 ("out_label", _vp), ("flags", _vp), ("num_flagged", _vp), ("flagged_rows", _vp), ("flagged_cap", _i),
                 ("final_label", _vp), ("final_checksum", _vp), ("scatter", C.POINTER(ScatterArgs)),
-                ("signal", C.POINTER(SignalArgs)), ("workspace", _vp), ("workspace_bytes", _sz)]
+                ("signal", C.POINTER(SignalArgs)), ("workspace", _vp), ("workspace_bytes", _sz), ("x_attrs_i32", _vp)]
 
 
 class RepairArgs(C.Structure):
@@ -365,7 +375,14 @@ class RepairArgs(C.Structure):
                 ("num_flagged", _vp), ("cap", _i), ("q", _i), ("n", _i), ("a", _i), ("id_base", _i), ("kmax", _i),
                 ("out_dist", _vp), ("out_id", _vp), ("out_label", _vp), ("final_label", _vp), ("final_checksum", _vp),
                 ("scatter", C.POINTER(ScatterArgs)), ("signal", C.POINTER(SignalArgs)), ("workspace", _vp),
-                ("workspace_bytes", _sz)]
+                ("workspace_bytes", _sz), ("x_attrs_i32", _vp)]
+
+
+class ExactArgs(C.Structure):
+    _fields_ = [("q_attrs", _vp), ("x_attrs", _vp), ("x_labels", _vp), ("k", _vp), ("query_rows", _vp), ("count", _i),
+                ("n", _i), ("a", _i), ("id_base", _i), ("kmax", _i), ("out_dist", _vp), ("out_id", _vp),
+                ("out_label", _vp), ("scatter", C.POINTER(ScatterArgs)), ("signal", C.POINTER(SignalArgs)),
+                ("workspace", _vp), ("workspace_bytes", _sz), ("x_attrs_i32", _vp)]
 
 
 class FinalizeArgs(C.Structure):
@@ -383,17 +400,18 @@ def _ptr(t):
 
 
 def rerank_ex(cand, q_attrs, x_attrs, x_labels, k, q_norm2, q_errn, rng, x_maxima, id_base, kmax, flags, nflag,
-              out=None, final=None, flagged_rows=None, scatter=None, signal=None):
+              out=None, final=None, flagged_rows=None, scatter=None, signal=None, x_i32=None):
     """dmlp_rerank_ex: re-rank with the optional folded vote (`final` = (label, checksum) tensors, single
     data shard), flagged-row list, K5 scatter and in-kernel completion signal."""
     lib = _lib()
     lib.dmlp_rerank_ex.argtypes = [C.POINTER(RerankArgs), _vp]
     q, chunks, kp = cand.shape
-    n, a = x_attrs.shape
+    n, a = (x_attrs if x_attrs is not None else x_i32).shape
     ws = rerank_workspace(q, kmax, cand.device)
     g = RerankArgs()
     g.cand, g.chunks, g.kp = _ptr(cand), chunks, kp
     g.q_attrs, g.x_attrs, g.x_labels, g.k = _ptr(q_attrs), _ptr(x_attrs), _ptr(x_labels), _ptr(k)
+    g.x_attrs_i32 = _ptr(x_i32)   # decimal6 rows: read instead of x_attrs (which may then be None)
     g.q_norm2, g.q_errn, g.range, g.x_maxima = _ptr(q_norm2), _ptr(q_errn), _ptr(rng), _ptr(x_maxima)
     g.q, g.n, g.a, g.a_pad, g.id_base, g.kmax = q, n, a, pad64(a), id_base, kmax
     if out is not None:
@@ -415,13 +433,13 @@ _repair_ws = {}
 
 
 def repair_flagged(q_attrs, x_attrs, x_labels, k, flagged_rows, nflag, id_base, kmax, out=None, final=None,
-                   scatter=None, signal=None):
+                   scatter=None, signal=None, x_i32=None):
     """dmlp_repair_flagged: direct fp64 kernel over the first min(*nflag, cap) flagged rows; the count
     stays on the device, so the call is enqueued unconditionally."""
     lib = _lib()
     lib.dmlp_repair_flagged.argtypes = [C.POINTER(RepairArgs), _vp]
     q, a = q_attrs.shape
-    n = x_attrs.shape[0]
+    n = (x_attrs if x_attrs is not None else x_i32).shape[0]
     cap = flagged_rows.numel()
     key = (str(q_attrs.device), n, cap, kmax)
     if key not in _repair_ws:
@@ -430,6 +448,7 @@ def repair_flagged(q_attrs, x_attrs, x_labels, k, flagged_rows, nflag, id_base, 
     g = RepairArgs()
     g.q_attrs, g.x_attrs, g.x_labels, g.k = _ptr(q_attrs), _ptr(x_attrs), _ptr(x_labels), _ptr(k)
     g.flagged_rows, g.num_flagged, g.cap = _ptr(flagged_rows), _ptr(nflag), cap
+    g.x_attrs_i32 = _ptr(x_i32)
     g.q, g.n, g.a, g.id_base, g.kmax = q, n, a, id_base, kmax
     if out is not None:
         g.out_dist, g.out_id, g.out_label = _ptr(out[0]), _ptr(out[1]), _ptr(out[2])
@@ -495,3 +514,30 @@ def topk_sync_timeouts():
     out = C.c_uint(0)
     _check(lib.dmlp_topk_sync_timeouts(C.byref(out)))
     return int(out.value)
+
+
+def pack_i32(src, rng, maxima=None, out=None, wait=None, signal=None):
+    """dmlp_pack_i32: pack rows kept in decimal6 form (int32 i, value i / 1e6)."""
+    lib = _lib()
+    lib.dmlp_pack_i32.argtypes = [_vp, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(WaitArgs), C.POINTER(SignalArgs),
+                                  _vp]
+    rows, a = src.shape
+    if out is None:
+        out = (torch.empty((rows, pad64(a)), dtype=torch.float16, device=src.device),
+               torch.empty(rows, dtype=torch.float32, device=src.device),
+               torch.empty(rows, dtype=torch.float32, device=src.device))
+    h, n2, en = out
+    _check(lib.dmlp_pack_i32(_p(src), rows, a, pad64(a), _p(rng), _p(h), _p(n2), _p(en), _p(maxima),
+                             C.byref(wait) if wait is not None else None,
+                             C.byref(signal) if signal is not None else None, _stream()))
+    return h, n2, en
+
+
+def encode_decimal6_into(src, dst):
+    """Re-encode fp64 values into an existing int32 tensor (no check read back: the caller knows
+    the values are representable)."""
+    lib = _lib()
+    lib.dmlp_encode_decimal6.argtypes = [_vp, _vp, _i64, _vp, _vp]
+    bad = torch.zeros(1, dtype=torch.int32, device=src.device)
+    _check(lib.dmlp_encode_decimal6(_p(src), _p(dst), src.numel(), _p(bad), _stream()))
+    return dst

@@ -124,6 +124,7 @@ class DistributedKNN:
                 if r == self.r:
                     self.row_group = g
         self.launch_count = 0
+        self._x32_step = None
         self._flagged_host = None
         self.epoch = 0
         self.host = None
@@ -181,7 +182,21 @@ class DistributedKNN:
             self.status = torch.zeros(1, dtype=torch.int32, device=dev)
             self.stats = K.new_stats(dev)
             self.q_stats = K.new_stats(dev)
+            # Resident decimal6 rows: when every data value is i / 1e6 for a 32-bit i (the text grammar's
+            # "%.6f"), the hot path reads the data as int32 -- half the bytes of pack and of the exact
+            # re-rank, the pass that is bound by exactly those bytes -- and rebuilds the doubles bit for
+            # bit in the kernels.  The fp64 rows stay resident for the direct kernels and the API.
+            self.dec6, x_enc = False, None
+            if (self.impl == "fused" and self.fused_ok and self.a % 2 == 0 and (C == 1 or self.rows_fused)
+                    and os.environ.get("DMLP_DEC6", "1") != "0"):
+                x_enc, ok = K.encode_decimal6(x_part)
+                okt = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+                if self.world > 1:
+                    dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+                self.dec6 = bool(okt.item())
+            self._x_enc = x_enc if self.dec6 else None
             self._alloc_shard(x_part, labels_part)
+            self._x_enc = None
             if not self.rows_fused:
                 self.xh = torch.empty((n, self.a_pad), dtype=torch.float16, device=dev)
                 self.xn = torch.empty(n, dtype=torch.float32, device=dev)
@@ -215,9 +230,12 @@ class DistributedKNN:
         in which every rank of the row fills its own part and pulls the others'."""
         dev, C, n, a = self.device, self.C, self.shard_rows, self.a
         b, e = self.part_rows
+        self.x32 = self.x32_part = None
         if C == 1:
             self.x, self.labels = x_part.contiguous(), labels_part.contiguous()
             self.x_part, self.labels_part = self.x, self.labels
+            if self.dec6:
+                self.x32 = self.x32_part = self._x_enc.contiguous()
             return
         if self.peer_rows:
             lay = Layout()
@@ -230,6 +248,8 @@ class DistributedKNN:
                 lay.add("xh", n * self.a_pad * 2)
                 lay.add("xn", n * 4)
                 lay.add("xe", n * 4)
+            if self.dec6:
+                lay.add("x32", n * a * 4)
             self.row_sym = sym = SymmetricBuffer(lay, dev, self.row_group)
             self.x = sym.view("x64", torch.float64, (n, a))
             self.labels = sym.view("labels", torch.int32)
@@ -249,6 +269,8 @@ class DistributedKNN:
                 dg.part_begin[C] = n
                 dg.off_xh, dg.off_xn, dg.off_xe = lay.off["xh"], lay.off["xn"], lay.off["xe"]
                 dg.off_x64, dg.off_labels, dg.off_pack_flags = lay.off["x64"], lay.off["labels"], lay.off["pack_flags"]
+                if self.dec6:    # the re-rank reads decimal6 rows: those are what the GEMM's communication warps pull
+                    dg.off_x64, dg.x_i32 = lay.off["x32"], 1
                 dg.tile_count, dg.status, dg.timeout_seconds = self.tile_count.data_ptr(), self.status.data_ptr(), 20.0
                 self.data_gather = dg
             self._row_gather_args = []
@@ -270,6 +292,10 @@ class DistributedKNN:
         self.x_part, self.labels_part = self.x[b:e], self.labels[b:e]
         self.x_part.copy_(x_part)
         self.labels_part.copy_(labels_part)
+        if self.dec6:
+            self.x32 = self.row_sym.view("x32", torch.int32, (n, a))
+            self.x32_part = self.x32[b:e]
+            self.x32_part.copy_(self._x_enc)
 
     def _alloc_plain(self, q_slice, k_slice):
         """Column buffers for a single-rank column or for the NCCL-plumbed paths."""
@@ -398,8 +424,9 @@ class DistributedKNN:
         and its last block tells the row that the new rows are ready."""
         b, e = self.part_rows
         sym, ep = self.row_sym, self.epoch
-        K.pack_ex(self.x_part, self.stats, None, out=(self.xh[b:e], self.xn[b:e], self.xe[b:e]),
-                  wait=sym.wait_args("done_flags", ep - 1, self.status), signal=sym.signal_args("pack_flags", ep))
+        (K.pack_i32 if self.dec6 else K.pack_ex)(
+            self.x32_part if self.dec6 else self.x_part, self.stats, None, out=(self.xh[b:e], self.xn[b:e], self.xe[b:e]),
+            wait=sym.wait_args("done_flags", ep - 1, self.status), signal=sym.signal_args("pack_flags", ep))
         self.data_gather.epoch = ep
         self._done_signal = sym.signal_args("done_flags", ep)       # sent by the GEMM's last block
         self.data_gather.done_signal = C.cast(C.pointer(self._done_signal), C.c_void_p)
@@ -421,10 +448,10 @@ class DistributedKNN:
         with tr.phase("rerank+vote"):
             K.rerank_ex(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
                         self.stats, self.id_base, self.kmax, flags, nflag, out=(od, oi, ol), final=self.final,
-                        flagged_rows=self.flagged_rows)
+                        flagged_rows=self.flagged_rows, x_i32=self.x32)
         with tr.phase("repair"):
             K.repair_flagged(self.q_slice, self.x, self.labels, self.k_slice, self.flagged_rows, nflag, self.id_base,
-                             self.kmax, out=(od, oi, ol), final=self.final)
+                             self.kmax, out=(od, oi, ol), final=self.final, x_i32=self.x32)
         self.launch_count += 9   # pack, dist_topk, maxima, rerank x3, repair x3
         return self.final[0][:self.nq], self.final[1][:self.nq]
 
@@ -433,7 +460,7 @@ class DistributedKNN:
         receive buffers; the last kernel that writes them signals, the owner's finalize waits)."""
         r0, tr, ep = self.r * self.qs, self.tracer, self.epoch
         with tr.phase("pack"):
-            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+            self._pack_shard()
             K.pack_ex(self.q_slice, self.stats, self.q_stats,
                       out=(self.qh[r0:r0 + self.nq], self.qn[r0:r0 + self.nq], self.qe_[r0:r0 + self.nq]),
                       signal=self.sym.signal_args("pack_flags", ep))   # "my packed slice is ready"
@@ -444,16 +471,23 @@ class DistributedKNN:
         with tr.phase("rerank+scatter"):
             K.rerank_ex(self.cand, self.q_all, self.x, self.labels, self.k_all, self.qn, self.qe_, self.stats,
                         self.stats, self.id_base, self.kmax, self.flags, self.nflag, scatter=self.scatter,
-                        flagged_rows=self.flagged_rows)   # K5 store side
+                        flagged_rows=self.flagged_rows, x_i32=self.x32)   # K5 store side
         with tr.phase("repair+signal"):
             K.repair_flagged(self.q_all, self.x, self.labels, self.k_all, self.flagged_rows, self.nflag,
-                             self.id_base, self.kmax, scatter=self.scatter,
+                             self.id_base, self.kmax, scatter=self.scatter, x_i32=self.x32,
                              signal=self.sym.signal_args("list_flags", ep))   # "my k-lists have landed everywhere"
         with tr.phase("wait_lists+finalize"):
             K.finalize_ex(self.recv[0], self.recv[1], self.recv[2], self.k_all[r0:r0 + self.qs], out=self.final,
                           wait=self.sym.wait_args("list_flags", ep, self.status))
         self.launch_count += 9   # pack x2, dist_topk, rerank x3, repair x2, finalize
         return self.final[0][:self.nq], self.final[1][:self.nq]
+
+    def _pack_shard(self):
+        """Pack the whole (local) data shard: from the decimal6 rows when they are resident."""
+        if self.dec6:
+            K.pack_i32(self.x32, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+        else:
+            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
 
     def _nflag_tensor(self):
         return self.nflag if self.peer_fused else self.lists[4]
@@ -493,7 +527,8 @@ class DistributedKNN:
         else:
             od, oi, ol, flags, _ = self.lists
             rows = torch.nonzero(flags[: self.nq], as_tuple=False).flatten().to(torch.int32)
-            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows, out=(od, oi, ol))
+            K.exact(self.q_slice, self.x, self.labels, self.k_slice, self.kmax, self.id_base, rows, out=(od, oi, ol),
+                    x_i32=self.x32)
             K.finalize_ex(od[None], oi[None], ol[None], self.k_slice, out=self.final)
         return flagged
 
@@ -505,7 +540,8 @@ class DistributedKNN:
         tmp = (torch.empty((self.qp, km), dtype=torch.float64, device=self.device),
                torch.empty((self.qp, km), dtype=torch.int32, device=self.device),
                torch.empty((self.qp, km), dtype=torch.int32, device=self.device))
-        K.exact(self.q_all, self.x, self.labels, self.k_all, km, self.id_base, rows.to(torch.int32), out=tmp)
+        K.exact(self.q_all, self.x, self.labels, self.k_all, km, self.id_base, rows.to(torch.int32), out=tmp,
+                x_i32=self.x32)
         owners = rows // self.qs
         for o in torch.unique(owners).tolist():
             sel = rows[owners == o]
@@ -532,7 +568,7 @@ class DistributedKNN:
             # one data shard: pack, filter, re-rank with the vote folded in, device-side repair --
             # eight launches, nothing for the host to wait on
             with tr.phase("pack"):
-                K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+                self._pack_shard()
                 K.pack(self.q_slice, self.stats, self.q_stats, out=(self.qh, self.qn, self.qe_))
             with tr.phase("dist_topk"):
                 K.dist_topk(self.qh, self.xh, self.xn, cand=self.cand, kmax=self.kmax)
@@ -540,10 +576,10 @@ class DistributedKNN:
             with tr.phase("rerank+vote"):
                 K.rerank_ex(self.cand, self.q_slice, self.x, self.labels, self.k_slice, self.qn, self.qe_, self.stats,
                             self.stats, self.id_base, self.kmax, flags, nflag, out=(od, oi, ol), final=self.final,
-                            flagged_rows=self.flagged_rows)
+                            flagged_rows=self.flagged_rows, x_i32=self.x32)
             with tr.phase("repair"):
                 K.repair_flagged(self.q_slice, self.x, self.labels, self.k_slice, self.flagged_rows, nflag,
-                                 self.id_base, self.kmax, out=(od, oi, ol), final=self.final)
+                                 self.id_base, self.kmax, out=(od, oi, ol), final=self.final, x_i32=self.x32)
             self.launch_count += 9   # pack x2, dist_topk, rerank x3, repair x3
             return self.final[0][:self.nq], self.final[1][:self.nq]
         with tr.phase("query_gather"):
@@ -708,11 +744,27 @@ class DistributedKNN:
         main.wait_event(events[-1])            # one copy stream, in order: the last piece closes the set
         self._wait_part_readers()              # the row's peers may still be pulling the previous step's rows
         self._install_small(slot, events)
-        K.expand_decimal6(self.x_wire[slot], self.x_part)
+        self._install_x(self.x_wire[slot])
         K.expand_decimal6(self.q_wire[slot][: self.nq], self.q_slice)
         K.stats_set(self.stats, *self.host_range)
         self.launch_count += 2
         return self.run_resident()
+
+    def _refresh_x32(self, b=None, e=None):
+        """fp64 rows just arrived in x_part (fp64 wire) while the hot path reads decimal6 rows: re-encode."""
+        if self.dec6:
+            src = self.x_part if b is None else self.x_part[b:e]
+            K.encode_decimal6_into(src, self.x32_part if b is None else self.x32_part[b:e])
+
+    def _install_x(self, wire):
+        """This rank's part of the data shard has arrived in decimal6 form: with resident decimal6
+        rows it goes where the hot path (and, on a row of GPUs, the peers) read it -- one small
+        kernel, no expansion; the fp64 copy of the part is then NOT refreshed (the direct kernels read
+        the decimal6 rows too).  Otherwise it is expanded to fp64."""
+        if self.dec6:
+            torch.add(wire, 0, out=self.x32_part)
+        else:
+            K.expand_decimal6(wire, self.x_part)
 
     def _rerank_chunk(self, i, b, e, cand):
         """Re-rank + folded vote + device-side repair of query rows [b, e) (chunk i of a streamed step)."""
@@ -722,9 +774,9 @@ class DistributedKNN:
         fin = (self.final[0][b:e], self.final[1][b:e])
         K.rerank_ex(cand, self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], self.qn[b:e], self.qe_[b:e],
                     self.stats, self.stats, self.id_base, self.kmax, flags[b:e], nf, out=out, final=fin,
-                    flagged_rows=rows)
+                    flagged_rows=rows, x_i32=self._x32_step)
         K.repair_flagged(self.q_slice[b:e], self.x, self.labels, self.k_slice[b:e], rows, nf, self.id_base, self.kmax,
-                         out=out, final=fin)
+                         out=out, final=fin, x_i32=self._x32_step)
         self.launch_count += 6
 
     def _wait_part_readers(self, upto=None):
@@ -739,12 +791,13 @@ class DistributedKNN:
         self._wait_part_readers()
         if self.wire == "decimal6":
             self.x_wire[0].copy_(h["x"], non_blocking=True)
-            K.expand_decimal6(self.x_wire[0], self.x_part)
+            self._install_x(self.x_wire[0])
             self.q_wire[0][: self.nq].copy_(h["q"], non_blocking=True)
             K.expand_decimal6(self.q_wire[0][: self.nq], self.q_slice)
         else:
             self.x_part.copy_(h["x"], non_blocking=True)
             self.q_slice.copy_(h["q"], non_blocking=True)
+            self._refresh_x32()
         self.labels_part.copy_(h["labels"], non_blocking=True)
         self.k_slice.copy_(h["k"], non_blocking=True)
         return self.run_resident()
@@ -828,6 +881,7 @@ class DistributedKNN:
         self.epoch += 1
         slot, events = self._step_copies(pieces)
         self._install_small(slot, events)
+        self._x32_step = (self.x_wire[slot] if dec else self.x32) if self.dec6 else None
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
@@ -839,9 +893,15 @@ class DistributedKNN:
             main.wait_event(ev)
             if kind == "x":
                 pb, pe = xparts[idx]
-                if dec:
-                    K.expand_decimal6(self.x_wire[slot][pb:pe], self.x_part[pb:pe])
-                K.pack(self.x[pb:pe], self.stats, self.stats, out=(self.xh[pb:pe], self.xn[pb:pe], self.xe[pb:pe]))
+                out = (self.xh[pb:pe], self.xn[pb:pe], self.xe[pb:pe])
+                if dec and self.dec6:        # pack (and later re-rank) straight from the wire set: no expansion at all
+                    K.pack_i32(self.x_wire[slot][pb:pe], self.stats, self.stats, out=out)
+                else:
+                    if dec:
+                        K.expand_decimal6(self.x_wire[slot][pb:pe], self.x_part[pb:pe])
+                    else:
+                        self._refresh_x32(pb, pe)
+                    K.pack(self.x[pb:pe], self.stats, self.stats, out=out)
                 have_x.add(idx)
             else:
                 b, e = qch[idx]
@@ -882,9 +942,12 @@ class DistributedKNN:
         if dec:
             self._wait_part_readers(self.epoch - 1)
         self._install_small(slot, events)
-        # data shard: expand, all-gather along the row, pack
+        # data shard: expand (or install the decimal6 rows), all-gather along the row, pack
         if dec:
-            K.expand_decimal6(self.x_wire[slot], self.x_part)
+            self._install_x(self.x_wire[slot])
+        else:
+            self._refresh_x32()
+        self._x32_step = self.x32
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
@@ -893,7 +956,7 @@ class DistributedKNN:
             self._pack_part_and_signal()
         else:
             self._gather_shard()
-            K.pack(self.x, self.stats, self.stats, out=(self.xh, self.xn, self.xe))
+            self._pack_shard()
         K.zero_(self.nflag_chunks)
         self.launch_count += 4 + (1 if dec else 0)
         for i, (b, e) in enumerate(chunks):
@@ -970,7 +1033,7 @@ class DistributedKNN:
                 rows = torch.from_numpy((owners * self.qs + local).astype(np.int32)).to(dev)
             kk = k_rows[rows.long()].contiguous()
             qsel = q_rows[rows.long()].contiguous()
-            od, oi, ol = K.exact(qsel, self.x, self.labels, kk, km, self.id_base)
+            od, oi, ol = K.exact(qsel, self.x, self.labels, kk, km, self.id_base, x_i32=self.x32)
             if R > 1:
                 parts = [[torch.empty_like(t) for _ in range(R)] for t in (od, oi, ol)]
                 for t, outs in zip((od, oi, ol), parts):
@@ -994,7 +1057,10 @@ class DistributedKNN:
             else:
                 idx = torch.from_numpy(owners * self.qs + local).to(dev)
                 qsel, ksel = self.q_all[idx].cpu().numpy(), self.k_all[idx].cpu().numpy()
-            lists = cpu.local_lists(self.x.cpu().numpy(), self.labels.cpu().numpy(), self.id_base, qsel, ksel, km)
+            # (with resident decimal6 rows the fp64 copy only holds this rank's own part)
+            x_host = (K.expand_decimal6(self.x32, torch.empty(self.x32.shape, dtype=torch.float64, device=dev))
+                      if self.dec6 else self.x).cpu().numpy()
+            lists = cpu.local_lists(x_host, self.labels.cpu().numpy(), self.id_base, qsel, ksel, km)
             mine = {int(j): (int(fin_label[local[j]]), int(fin_sum[local[j]])) for j in range(n_cpu)
                     if owners[j] == self.r}
             if R > 1:

@@ -224,6 +224,7 @@ typedef struct dmlp_data_gather_args {
   double timeout_seconds;
   const struct dmlp_signal_args *done_signal;  /* optional: "I have finished reading your parts", stored by
                                                   the kernel's last block (see dmlp_signal_args below) */
+  int x_i32;   /* 1: the region at off_x64 holds decimal6 rows (a int32 per row, a even) instead of fp64 rows */
 } dmlp_data_gather_args;
 int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms, int kmax, uint64_t *cand,
                         const dmlp_data_gather_args *g, void *stream);
@@ -271,6 +272,13 @@ struct dmlp_wait_args;
 int dmlp_pack_ex(const double *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
                  float *errn, void *maxima, const struct dmlp_wait_args *wait, const struct dmlp_signal_args *signal,
                  void *stream);
+/* The same with the source rows in decimal6 form: int32 i per value, value = i / 1e6 (the loader's
+ * wire format kept resident).  The kernel rebuilds the parser's double exactly (one multiply and a
+ * two-FMA correction step, checked against IEEE division for every 32-bit i) and reads half the
+ * bytes.  wait / signal may be NULL. */
+int dmlp_pack_i32(const int *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
+                  float *errn, void *maxima, const struct dmlp_wait_args *wait, const struct dmlp_signal_args *signal,
+                  void *stream);
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream (counters, flags) without a library kernel. */
 int dmlp_zero(void *ptr, size_t bytes, void *stream);
 
@@ -311,6 +319,8 @@ typedef struct dmlp_rerank_args {
   const dmlp_signal_args *signal;
   void *workspace;
   size_t workspace_bytes;
+  const int *x_attrs_i32;   /* optional: the data rows in decimal6 form (int32 i, value i / 1e6), read
+                               instead of x_attrs: half the bytes of the exact pass.  Needs an even a. */
 } dmlp_rerank_args;
 int dmlp_rerank_ex(const dmlp_rerank_args *r, void *stream);
 
@@ -328,6 +338,7 @@ typedef struct dmlp_repair_args {
   const dmlp_signal_args *signal;
   void *workspace;
   size_t workspace_bytes;
+  const int *x_attrs_i32;   /* optional, as in dmlp_rerank_args */
 } dmlp_repair_args;
 int dmlp_repair_flagged(const dmlp_repair_args *r, void *stream);
 
@@ -344,6 +355,7 @@ typedef struct dmlp_exact_args {
   const dmlp_signal_args *signal;
   void *workspace;
   size_t workspace_bytes;
+  const int *x_attrs_i32;   /* optional, as in dmlp_rerank_args */
 } dmlp_exact_args;
 int dmlp_exact_ex(const dmlp_exact_args *g, void *stream);
 

@@ -688,8 +688,9 @@ __device__ void data_gather_warp(const TopkPlan &plan, const DataGatherArgs &dg,
     wait_peer(owner);
     if (dead) break;
     const unsigned char *peer = dg.peer_base[owner];
-    const long long e0 = static_cast<long long>(dg.part_begin[owner]) * dg.a;       // first double of the part
-    const long long e1 = static_cast<long long>(dg.part_begin[owner + 1]) * dg.a;   // one past its last
+    const int units = dg.x_units > 0 ? dg.x_units : dg.a;                            // 8-byte units per row (fp64 or decimal6 rows)
+    const long long e0 = static_cast<long long>(dg.part_begin[owner]) * units;      // first unit of the part
+    const long long e1 = static_cast<long long>(dg.part_begin[owner + 1]) * units;  // one past its last
     const double *src = reinterpret_cast<const double *>(peer + dg.off_x64);
     double *dst = reinterpret_cast<double *>(own + dg.off_x64);
     long long lo = e0, hi = e1;

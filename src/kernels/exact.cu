@@ -41,6 +41,7 @@ __host__ __device__ inline int list_stride(int kmax) { return pow2_at_least(2 * 
 
 struct ScanArgs {
   const double *q_attrs, *x_attrs;
+  const int *x_i32;   // optional: the data rows in decimal6 form, read instead of x_attrs
   const int *k, *query_rows, *count_dev;
   int qbase, count, n, a, kmax, splits, stride;
   double *l_dist;  // [count][splits][stride]
@@ -153,7 +154,8 @@ __global__ void __launch_bounds__(EX_THREADS) exact_scan_kernel(const ScanArgs a
       for (int i = tid; i < EX_XR * EX_CH; i += EX_THREADS) {
         const int r = i / EX_CH, c = i - r * EX_CH;
         const int row = x0 + r, col = c0 + c;
-        xs[r][c] = (row < r_end && col < a.a) ? a.x_attrs[static_cast<long long>(row) * a.a + col] : 0.0;
+        const long long at = static_cast<long long>(row) * a.a + col;
+        xs[r][c] = (row < r_end && col < a.a) ? (a.x_i32 ? dec6_to_double(a.x_i32[at]) : a.x_attrs[at]) : 0.0;
       }
       for (int i = tid; i < EX_QB * EX_CH; i += EX_THREADS) {
         const int r = i / EX_CH, c = i - r * EX_CH;
@@ -320,6 +322,7 @@ int launch_exact(const ExactArgs &args, cudaStream_t s) {
     ScanArgs sa;
     sa.q_attrs = args.q_attrs; sa.x_attrs = args.x_attrs; sa.k = args.k; sa.query_rows = args.query_rows;
     sa.count_dev = args.count_dev;
+    sa.x_i32 = args.x_attrs_i32;
     sa.qbase = base; sa.count = cnt; sa.n = args.n; sa.a = args.a; sa.kmax = args.kmax;
     sa.splits = splits; sa.stride = stride;
     sa.l_dist = l_dist; sa.l_id = l_id; sa.l_cnt = l_cnt;

@@ -101,9 +101,10 @@ struct WaitArgs {
 // pack.cu
 int launch_stats_reset(PackStats *st, cudaStream_t s);
 int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t s);
-int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
+/// src: fp64 rows, or (src_i32) the same rows in decimal6 form: int32 i with value i / 1e6
+int launch_pack(const void *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
                 float *norm2, float *errn, PackStats *maxima, cudaStream_t s, const WaitArgs *wait = nullptr,
-                const SignalArgs *signal = nullptr);
+                const SignalArgs *signal = nullptr, bool src_i32 = false);
 
 /// Cross-GPU operand gather fused into the filter GEMM (K4).  Every rank owns
 /// `slice_rows` query rows and has packed them into its own symmetric buffer;
@@ -138,6 +139,7 @@ struct DataGatherArgs {
   int *status = nullptr;
   long long timeout_cycles = 0;
   SignalArgs done;                     ///< optional: "I have finished reading your parts", sent when the launch ends
+  int x_units = 0;                     ///< 8-byte units per row of the region at off_x64 (a for fp64 rows, a / 2 for decimal6 rows; 0 = a)
 };
 
 /// Where the exact k-lists go (K5): straight into the owner rank's receive
@@ -182,6 +184,7 @@ struct RerankArgs {
   int chunks, kp;
   const double *q_attrs;           // [q][a] original fp64
   const double *x_attrs;           // [n][a]
+  const int *x_attrs_i32 = nullptr;  // optional [n][a]: the same rows in decimal6 form (int32 i, value i / 1e6); read instead of x_attrs
   const int *x_labels;             // [n]
   const int *k;                    // [q]
   const float *q_norm2;            // [q]  ||q^||^2 (scaled units)
@@ -237,6 +240,7 @@ int launch_finalize(const FinalizeArgs &args, cudaStream_t s);
 struct ExactArgs {
   const double *q_attrs;  // [q][a]
   const double *x_attrs;  // [n][a]
+  const int *x_attrs_i32 = nullptr;  // optional: the rows in decimal6 form, read instead of x_attrs
   const int *x_labels;
   const int *k;           // [q]
   const int *query_rows;  // optional [count] subset of query rows (nullptr = all q rows)

@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(256) stats_kernel(const double *__restrict__ s
 
 // One warp per row, grid-stride over rows.  Lanes own adjacent column pairs so
 // the fp16 stores are 4-byte, 128 B per warp instruction.
-__global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ src, long long rows, int a,
+template <bool I32>
+__global__ void __launch_bounds__(256) pack_kernel(const void *__restrict__ src_v, long long rows, int a,
                                                    int a_pad, const PackStats *__restrict__ range,
                                                    __half *__restrict__ dst, float *__restrict__ norm2,
                                                    float *__restrict__ errn, PackStats *maxima, const WaitArgs wait,
@@ -69,11 +70,15 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
   const int lane = threadIdx.x & 31;
   const long long warp_global = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  const bool vec_ok = (a & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  // I32: the rows are resident in the decimal6 form (int32, value = i / 1e6), half the bytes to read
+  const double *src = static_cast<const double *>(src_v);
+  const int *src_i = static_cast<const int *>(src_v);
+  const bool vec_ok = (a & 1) == 0 && (reinterpret_cast<uintptr_t>(src_v) & (I32 ? 7 : 15)) == 0;
   float my_max_norm = 0.f, my_max_err = 0.f;
 
   for (long long r = warp_global; r < rows; r += warps_total) {
     const double *in = src + r * a;
+    const int *in_i = src_i + r * a;
     __half2 *out = reinterpret_cast<__half2 *>(dst + r * a_pad);
     double nsum = 0.0, esum = 0.0, xsum = 0.0;
     auto one = [&](double v0, double v1, bool in0, bool in1, int c) {
@@ -81,10 +86,12 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
       double x1 = in1 ? __dmul_rn(__dsub_rn(v1, sp.center), sp.scale) : 0.0;
       __half h0 = __double2half(x0), h1 = __double2half(x1);
       double f0 = static_cast<double>(__half2float(h0)), f1 = static_cast<double>(__half2float(h1));
-      double d0 = x0 - f0, d1 = x1 - f1;
-      nsum += f0 * f0 + f1 * f1;
-      esum += d0 * d0 + d1 * d1;
-      xsum += x0 * x0 + x1 * x1;
+      // explicit operations: every instantiation of the kernel (fp64 or decimal6 source, block or tail
+      // loop) must round the same way, or the same rows would get different norms
+      double d0 = __dsub_rn(x0, f0), d1 = __dsub_rn(x1, f1);
+      nsum = __fma_rn(f1, f1, __fma_rn(f0, f0, nsum));
+      esum = __fma_rn(d1, d1, __fma_rn(d0, d0, esum));
+      xsum = __fma_rn(x1, x1, __fma_rn(x0, x0, xsum));
       out[c >> 1] = __halves2half2(h0, h1);
     };
     int c0 = 0;
@@ -92,18 +99,29 @@ __global__ void __launch_bounds__(256) pack_kernel(const double *__restrict__ sr
       // whole 512-column blocks: eight independent 16-byte loads per lane are issued before any of
       // them is used (8 KB in flight per warp), each a fully coalesced 512-byte warp access
       for (; c0 + 512 <= a; c0 += 512) {
-        double2 t[8];
+        if (I32) {
+          int2 t[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) t[j] = __ldcs(reinterpret_cast<const double2 *>(in + c0 + j * 64 + lane * 2));
+          for (int j = 0; j < 8; ++j) t[j] = __ldcs(reinterpret_cast<const int2 *>(in_i + c0 + j * 64 + lane * 2));
 #pragma unroll
-        for (int j = 0; j < 8; ++j) one(t[j].x, t[j].y, true, true, c0 + j * 64 + lane * 2);
+          for (int j = 0; j < 8; ++j) one(dec6_to_double(t[j].x), dec6_to_double(t[j].y), true, true, c0 + j * 64 + lane * 2);
+        } else {
+          double2 t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = __ldcs(reinterpret_cast<const double2 *>(in + c0 + j * 64 + lane * 2));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) one(t[j].x, t[j].y, true, true, c0 + j * 64 + lane * 2);
+        }
       }
     }
 #pragma unroll 2
     for (int c = c0 + lane * 2; c < a_pad; c += 64) {
       double v0 = 0.0, v1 = 0.0;
       bool in0 = c < a, in1 = c + 1 < a;
-      if (vec_ok && in1) {
+      if (I32) {
+        if (in0) v0 = dec6_to_double(in_i[c]);
+        if (in1) v1 = dec6_to_double(in_i[c + 1]);
+      } else if (vec_ok && in1) {
         double2 t = *reinterpret_cast<const double2 *>(in + c);
         v0 = t.x; v1 = t.y;
       } else {
@@ -144,7 +162,7 @@ __global__ void __launch_bounds__(256) expand_decimal6_kernel(const int *__restr
                                                               long long count) {
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride)
-    dst[i] = __ddiv_rn(static_cast<double>(src[i]), 1e6);
+    dst[i] = dec6_to_double(src[i]);   // == __ddiv_rn((double)src[i], 1e6), see common.cuh
 }
 
 // Checks that every value survives the decimal6 round trip and emits the integers.
@@ -229,9 +247,9 @@ int launch_stats(const double *src, long long count, PackStats *st, cudaStream_t
   return 0;
 }
 
-int launch_pack(const double *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
+int launch_pack(const void *src, long long rows, int a, int a_pad, const PackStats *range, __half *dst,
                 float *norm2, float *errn, PackStats *maxima, cudaStream_t s, const WaitArgs *wait,
-                const SignalArgs *signal) {
+                const SignalArgs *signal, bool src_i32) {
   const WaitArgs wa = wait ? *wait : WaitArgs();
   const SignalArgs sg = signal ? *signal : SignalArgs();
   if (rows <= 0 && sg.world <= 0) return 0;
@@ -240,8 +258,12 @@ int launch_pack(const double *src, long long rows, int a, int a_pad, const PackS
   long long blocks = (rows + 7) / 8;  // 8 warps per block
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  pack_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn, maxima, wa,
-                                                           sg);
+  if (src_i32)
+    pack_kernel<true><<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn, maxima,
+                                                                   wa, sg);
+  else
+    pack_kernel<false><<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, a_pad, range, dst, norm2, errn,
+                                                                    maxima, wa, sg);
   DMLP_CUDA_OK(cudaGetLastError());
   return 0;
 }

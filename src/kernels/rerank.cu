@@ -291,7 +291,15 @@ constexpr int XQ = 8;
 constexpr int XD_ROWS = 32 + XQ;
 constexpr int XD_STAGE = XD_ROWS * XSTR;
 constexpr int XD_SMEM = X_WARPS * 2 * XD_STAGE * 8;
+// XI32: the data rows are resident in decimal6 form (int32 i, value i / 1e6): half the bytes of
+// the pass, which is bound by exactly those bytes.  A stage then holds 32 int rows (stride XSTRI)
+// followed by the XQ query rows (fp64); the value is rebuilt with dec6_to_double (3 fp64 operations).
+constexpr int XSTRI = XC + 2;                                  // ints; rows stay 8-byte aligned
+constexpr int XI_DATA_BYTES = 32 * XSTRI * 4;                  // 4352
+constexpr int XI_STAGE_BYTES = XI_DATA_BYTES + XQ * XSTR * 8;  // + 2176
+constexpr int XI_SMEM = X_WARPS * 2 * XI_STAGE_BYTES;
 
+template <bool XI32>
 __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const RerankArgs a, const Scratch sc) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -300,7 +308,8 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
   const long long p0 = (static_cast<long long>(blockIdx.x) * X_WARPS + warp) * 32;
   if (p0 >= total) return;
   const int cnt = (total - p0) < 32 ? static_cast<int>(total - p0) : 32;
-  double *ring = reinterpret_cast<double *>(rr_smem) + static_cast<size_t>(warp) * 2 * XD_STAGE;
+  constexpr int STAGE_BYTES = XI32 ? XI_STAGE_BYTES : XD_STAGE * 8;
+  unsigned char *ring = rr_smem + static_cast<size_t>(warp) * 2 * STAGE_BYTES;
   const bool have = lane < cnt;
   const int my_qi = have ? sc.pair_q[p0 + lane] : -1;
   const long long my_x = have ? static_cast<long long>(sc.pair_id[p0 + lane]) * a.a : 0;
@@ -313,7 +322,7 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
   const int start_lane = lane < distinct ? static_cast<int>(__fns(starts, 0, lane + 1)) : 0;
   const long long slot_q = static_cast<long long>(__shfl_sync(0xFFFFFFFFu, my_qi, start_lane)) * a.a;
   const int nchunks = (a.a + XC - 1) / XC;
-  const int sub = lane >> 4, seg = lane & 15;  // 16 lanes x 16 B cover one 32-column row segment
+  const int sub = lane >> 4, seg = lane & 15;  // 16 lanes cover one 32-column row segment
 
   double acc = 0.0;
   for (int base = 0; base < distinct; base += XQ) {
@@ -322,19 +331,24 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
     const int nq = min(XQ, distinct - base);
     auto issue = [&](int chunk) {
       if (chunk < nchunks) {
-        double *stage = ring + (chunk & 1) * XD_STAGE;
+        unsigned char *stage = ring + (chunk & 1) * STAGE_BYTES;
+        double *qstage = reinterpret_cast<double *>(stage + (XI32 ? XI_DATA_BYTES : 32 * XSTR * 8));
         const int col = chunk * XC + seg * 2;
         const bool in = col + 2 <= a.a;
         for (int r0 = 0; r0 < cnt; r0 += 2) {  // data rows of the lanes handled in this pass
           const int r = r0 + sub;
           const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r < cnt ? r : 0);
-          if (r < cnt && ((amask >> r) & 1u))
-            cp_async_zfill<16>(stage + r * XSTR + seg * 2, a.x_attrs + xo + (in ? col : 0), in);
+          if (r < cnt && ((amask >> r) & 1u)) {
+            if (XI32)
+              cp_async_zfill<8>(reinterpret_cast<int *>(stage) + r * XSTRI + seg * 2, a.x_attrs_i32 + xo + (in ? col : 0), in);
+            else
+              cp_async_zfill<16>(reinterpret_cast<double *>(stage) + r * XSTR + seg * 2, a.x_attrs + xo + (in ? col : 0), in);
+          }
         }
         for (int s0 = 0; s0 < nq; s0 += 2) {   // one copy of each query row
           const int sl = s0 + sub;
           const long long qo = __shfl_sync(0xFFFFFFFFu, slot_q, base + (sl < nq ? sl : 0));
-          if (sl < nq) cp_async_zfill<16>(stage + (32 + sl) * XSTR + seg * 2, a.q_attrs + qo + (in ? col : 0), in);
+          if (sl < nq) cp_async_zfill<16>(qstage + sl * XSTR + seg * 2, a.q_attrs + qo + (in ? col : 0), in);
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");  // always commit: keeps the group count uniform
@@ -345,13 +359,23 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
       asm volatile("cp.async.wait_group 1;" ::: "memory");
       __syncwarp();
       if (active) {
-        const double *stage = ring + (chunk & 1) * XD_STAGE;
-        const double *xs = stage + lane * XSTR;
-        const double *qs = stage + (32 + slot - base) * XSTR;
+        const unsigned char *stage = ring + (chunk & 1) * STAGE_BYTES;
+        const double *qs = reinterpret_cast<const double *>(stage + (XI32 ? XI_DATA_BYTES : 32 * XSTR * 8)) + (slot - base) * XSTR;
+        if (XI32) {
+          const int *xs = reinterpret_cast<const int *>(stage) + lane * XSTRI;
 #pragma unroll 8
-        for (int i = 0; i < XC; ++i) {
-          const double d = __dsub_rn(qs[i], xs[i]);
-          acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
+          for (int i = 0; i < XC; ++i) {
+            // (a zero-filled tail is the integer 0 -> 0.0 against a query value of 0.0: adds +0.0 exactly)
+            const double d = __dsub_rn(qs[i], dec6_to_double(xs[i]));
+            acc = __dadd_rn(acc, __dmul_rn(d, d));
+          }
+        } else {
+          const double *xs = reinterpret_cast<const double *>(stage) + lane * XSTR;
+#pragma unroll 8
+          for (int i = 0; i < XC; ++i) {
+            const double d = __dsub_rn(qs[i], xs[i]);
+            acc = __dadd_rn(acc, __dmul_rn(d, d));  // zero-filled tail adds +0.0 exactly
+          }
         }
       }
       __syncwarp();
@@ -510,9 +534,16 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
     const char *e = getenv("DMLP_RERANK_DEDUP");  // 0: stage a query row per pair (the first version)
     return e == nullptr || atoi(e) != 0;
   }();
-  if (vec2 && dedup) {
-    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, XD_SMEM));
-    rerank_exact_dedup_kernel<<<blocks, X_WARPS * 32, XD_SMEM, s>>>(args, sc);
+  DMLP_REQUIRE(args.x_attrs_i32 == nullptr ||
+                   ((args.a % 2 == 0) && reinterpret_cast<uintptr_t>(args.x_attrs_i32) % 8 == 0 &&
+                    reinterpret_cast<uintptr_t>(args.q_attrs) % 16 == 0),
+               "rerank: decimal6 rows need an even row length and aligned buffers");
+  if (args.x_attrs_i32 != nullptr) {
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XI_SMEM));
+    rerank_exact_dedup_kernel<true><<<blocks, X_WARPS * 32, XI_SMEM, s>>>(args, sc);
+  } else if (vec2 && dedup) {
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XD_SMEM));
+    rerank_exact_dedup_kernel<false><<<blocks, X_WARPS * 32, XD_SMEM, s>>>(args, sc);
   } else if (vec2) {
     DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, X_SMEM));
     rerank_exact_kernel<true><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);

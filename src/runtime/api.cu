@@ -111,6 +111,17 @@ int dmlp_pack_ex(const double *src, int64_t rows, int a, int a_pad, const void *
                      norm2, errn, static_cast<PackStats *>(maxima), st(stream), &wa, &sg);
 }
 
+int dmlp_pack_i32(const int *src, int64_t rows, int a, int a_pad, const void *range, void *dst_fp16, float *norm2,
+                  float *errn, void *maxima, const dmlp_wait_args *wait, const dmlp_signal_args *signal, void *stream) {
+  DMLP_REQUIRE(a_pad % 64 == 0, "pack: a_pad must be a multiple of 64");
+  WaitArgs wa;
+  SignalArgs sg;
+  if (int rc = fill_wait(wait, &wa)) return rc;
+  if (int rc = fill_signal(signal, &sg)) return rc;
+  return launch_pack(src, rows, a, a_pad, static_cast<const PackStats *>(range), static_cast<__half *>(dst_fp16),
+                     norm2, errn, static_cast<PackStats *>(maxima), st(stream), &wa, &sg, /*src_i32=*/true);
+}
+
 int dmlp_zero(void *ptr, size_t bytes, void *stream) {
   DMLP_CUDA_OK(cudaMemsetAsync(ptr, 0, bytes, st(stream)));
   return 0;
@@ -173,6 +184,7 @@ int dmlp_rerank_ex(const dmlp_rerank_args *g, void *stream) {
   r.flagged_rows = g->flagged_rows; r.flagged_cap = g->flagged_rows ? g->flagged_cap : 0;
   r.final_label = g->final_label;
   r.final_checksum = reinterpret_cast<unsigned long long *>(g->final_checksum);
+  r.x_attrs_i32 = g->x_attrs_i32;
   if (g->scatter != nullptr) {
     const dmlp_scatter_args *sc = g->scatter;
     DMLP_REQUIRE(sc->world >= 2 && sc->world <= kMaxPeers, "rerank: scatter world must be in [2, 8]");
@@ -258,6 +270,8 @@ int dmlp_dist_topk_rows(const void *q_fp16, int q, int n, int a_pad, int num_sms
   dg.tile_count = g->tile_count; dg.status = g->status;
   dg.timeout_cycles = static_cast<long long>((g->timeout_seconds > 0 ? g->timeout_seconds : 20.0) * 1.5e9);
   if (int rc = fill_signal(g->done_signal, &dg.done)) return rc;
+  dg.x_units = g->x_i32 ? g->a / 2 : g->a;
+  DMLP_REQUIRE(!g->x_i32 || g->a % 2 == 0, "dist_topk_rows: decimal6 rows need an even row length");
   const __half *xh = reinterpret_cast<const __half *>(dg.peer_base[dg.rank] + dg.off_xh);
   const float *xn = reinterpret_cast<const float *>(dg.peer_base[dg.rank] + dg.off_xn);
   return launch_dist_topk(static_cast<const __half *>(q_fp16), xh, xn, p,
@@ -289,6 +303,7 @@ int dmlp_repair_flagged(const dmlp_repair_args *g, void *stream) {
   ExactArgs e;
   e.q_attrs = g->q_attrs; e.x_attrs = g->x_attrs; e.x_labels = g->x_labels; e.k = g->k;
   e.query_rows = g->flagged_rows; e.count = g->cap; e.count_dev = g->num_flagged;
+  e.x_attrs_i32 = g->x_attrs_i32;
   e.n = g->n; e.a = g->a; e.id_base = g->id_base; e.kmax = g->kmax;
   e.out_dist = g->out_dist; e.out_id = g->out_id; e.out_label = g->out_label;
   e.workspace = g->workspace; e.workspace_bytes = g->workspace_bytes;
@@ -345,6 +360,7 @@ int dmlp_exact_ex(const dmlp_exact_args *g, void *stream) {
   e.count = g->count; e.n = g->n; e.a = g->a; e.id_base = g->id_base; e.kmax = g->kmax;
   e.out_dist = g->out_dist; e.out_id = g->out_id; e.out_label = g->out_label;
   e.workspace = g->workspace; e.workspace_bytes = g->workspace_bytes;
+  e.x_attrs_i32 = g->x_attrs_i32;
   if (g->scatter != nullptr) {
     if (int rc = fill_scatter(g->scatter, &e.scatter)) return rc;
   } else {

@@ -226,3 +226,26 @@ def test_copy_order_planner_beats_plain_alternation():
     # too many interleavings to enumerate: falls back to alternation, still a valid order
     big = best_copy_order([100] * 20, [100] * 20, 64)
     assert len(big) == 40 and big[0] == ("q", 0) and big[1] == ("x", 0)
+
+
+def test_decimal6_correction_step_equals_division():
+    """value = i / 1e6: one multiply by RN(1e-6) plus the exact-remainder correction step gives the
+    correctly rounded quotient (what the kernels compute with three fp64 operations).  All 2^32
+    integers were checked once in C++; here a dense sample plus the extremes, with numpy's
+    float64 (math.fma is not available before Python 3.13, so the remainder is formed exactly
+    with integers)."""
+    from fractions import Fraction
+    rng = np.random.default_rng(5)
+    ints = np.concatenate([rng.integers(-2**31, 2**31, 20000), np.arange(-1000, 1000),
+                           np.array([-2**31, 2**31 - 1, 10**8, -10**8, 99999999, 123456789])])
+    y = 1e-6
+    for i in ints.tolist():
+        v0 = float(i) * y
+        # r = fma(-1e6, v0, i) is exact: compute it in rationals and check it is a double
+        r_exact = Fraction(i) - Fraction(10**6) * Fraction(v0)
+        r = float(r_exact)
+        assert Fraction(r) == r_exact
+        # v = fma(r, y, v0): one rounding of the exact sum
+        v_exact = Fraction(r) * Fraction(y) + Fraction(v0)
+        v = float(v_exact)          # Fraction -> float rounds to nearest even
+        assert v == i / 1e6, i

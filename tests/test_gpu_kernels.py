@@ -253,6 +253,41 @@ def test_finalize_merges_long_lists(K, shards, kmin, kmax):
     assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
 
 
+@pytest.mark.parametrize("n,q,a,kmax", [(5000, 300, 64, 16), (2049, 257, 1030, 9)])
+def test_decimal6_rows_give_identical_pack_rerank_and_exact(K, n, q, a, kmax):
+    """Resident decimal6 rows (int32 i, value i / 1e6): pack, the exact re-rank and the direct kernel
+    must produce, bit for bit, what they produce from the fp64 rows."""
+    data, labels, queries, k = cpu.synth(n, q, a, -100.0, 100.0, 1, kmax, 5, seed=19)
+    x, qq, lab, kk = _dev(data), _dev(queries), _dev(labels), _dev(k)
+    xi, ok = K.encode_decimal6(x)
+    assert ok and torch.equal(K.expand_decimal6(xi, torch.empty_like(x)), x)
+    st = K.new_stats()
+    K.stats_update(x, st)
+    K.stats_update(qq, st)
+    st2 = st.clone()
+    h0, n0, e0 = K.pack(x, st, st)
+    h1, n1, e1 = K.pack_i32(xi, st2, st2)
+    torch.cuda.synchronize()
+    assert torch.equal(h0, h1) and torch.equal(n0, n1) and torch.equal(e0, e1)
+    assert torch.equal(st.view(torch.int64)[:3], st2.view(torch.int64)[:3])   # range and row maxima (bit patterns)
+    qst = K.new_stats()
+    qh, qn, qe = K.pack(qq, st, qst)
+    cand = K.dist_topk(qh, h0, n0, kmax=kmax)
+    ref = K.rerank(cand, qq, x, lab, kk, qn, qe, st, st, 0, kmax)
+    dev = x.device
+    out = (torch.empty_like(ref[0]), torch.empty_like(ref[1]), torch.empty_like(ref[2]))
+    flags, nflag = torch.empty(q, dtype=torch.int32, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+    K.rerank_ex(cand, qq, None, lab, kk, qn, qe, st, st, 0, kmax, flags, nflag, out=out, x_i32=xi)
+    torch.cuda.synchronize()
+    assert int(nflag.item()) == 0 and int(ref[4].item()) == 0
+    for r, o in zip(ref[:3], out):
+        assert torch.equal(r, o)
+    e_ref = K.exact(qq, x, lab, kk, kmax)
+    e_i32 = K.exact(qq, None, lab, kk, kmax, x_i32=xi)
+    for r, o in zip(e_ref, e_i32):
+        assert torch.equal(r, o)
+
+
 def test_duplicates_tie_break_on_gpu(K):
     rng = np.random.default_rng(0)
     base = rng.uniform(-1, 1, (50, 16))
