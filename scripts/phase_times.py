@@ -18,6 +18,7 @@ p.add_argument("--n", type=int, default=65536)
 p.add_argument("--kmin", type=int, default=4)
 p.add_argument("--kmax", type=int, default=16)
 p.add_argument("--reps", type=int, default=5)
+p.add_argument("--dec6", action="store_true", help="data rows resident in decimal6 form (int32)")
 args = p.parse_args()
 A, Q, N = args.a, args.q, args.n
 x = K.synth_attrs(N, A, 0, -100.0, 100.0, 42, 0)
@@ -25,6 +26,9 @@ lab = K.synth_labels(N, 0, 10, 42)
 qq = K.synth_attrs(Q, A, 0, -100.0, 100.0, 42, 2)
 k = K.synth_k(Q, 0, args.kmin, args.kmax, 42)
 st, qst = K.new_stats(), K.new_stats()
+xi = K.encode_decimal6(x)[0] if args.dec6 else None
+flags_t, nflag_t = torch.empty(Q, dtype=torch.int32, device="cuda"), torch.zeros(1, dtype=torch.int32, device="cuda")
+lists_t = (torch.empty((Q, args.kmax), dtype=torch.float64, device="cuda"), torch.empty((Q, args.kmax), dtype=torch.int32, device="cuda"), torch.empty((Q, args.kmax), dtype=torch.int32, device="cuda"))
 times = {}
 
 
@@ -44,10 +48,16 @@ for rep in range(args.reps + 2):
     K.stats_reset(st)
     K.stats_reset(qst)
     timed("stats", lambda: (K.stats_update(x, st), K.stats_update(qq, st)))
-    xh, xn, xe = timed("pack_x", lambda: K.pack(x, st, st))
+    xh, xn, xe = timed("pack_x", lambda: K.pack_i32(xi, st, st) if args.dec6 else K.pack(x, st, st))
     qh, qn, qe = timed("pack_q", lambda: K.pack(qq, st, qst))
     cand = timed("dist_topk", lambda: K.dist_topk(qh, xh, xn, kmax=args.kmax))
-    od, oi, ol, flags, nflag = timed("rerank", lambda: K.rerank(cand, qq, x, lab, k, qn, qe, st, st, 0, args.kmax))
+    if args.dec6:
+        nflag_t.zero_()
+        timed("rerank", lambda: K.rerank_ex(cand, qq, None, lab, k, qn, qe, st, st, 0, args.kmax, flags_t, nflag_t,
+                                            out=lists_t, x_i32=xi))
+        od, oi, ol, flags, nflag = lists_t + (flags_t, nflag_t)
+    else:
+        od, oi, ol, flags, nflag = timed("rerank", lambda: K.rerank(cand, qq, x, lab, k, qn, qe, st, st, 0, args.kmax))
     timed("finalize", lambda: K.finalize(od[None], oi[None], ol[None], k))
 import ctypes
 wbuf = torch.zeros(Q, dtype=torch.int32, device="cuda")

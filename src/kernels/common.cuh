@@ -77,7 +77,9 @@ __host__ __device__ inline int key_id(unsigned long long key) {
 // IEEE division for all 2^32 values of a 32-bit i (tests/test_cpu_oracle.py runs a sample).
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ double dec6_to_double(int i) {
-  const double x = static_cast<double>(i);
+  // (double)i without the conversion pipe: 2^52 + 2^31 + i has the bits {0x43300000, i ^ 0x80000000};
+  // subtracting 2^52 + 2^31 is exact
+  const double x = __dsub_rn(__hiloint2double(0x43300000, i ^ static_cast<int>(0x80000000u)), 4503601774854144.0);
   const double v0 = __dmul_rn(x, 1e-6);
   const double r = __fma_rn(-1e6, v0, x);
   return __fma_rn(r, 1e-6, v0);

@@ -294,12 +294,17 @@ constexpr int XD_SMEM = X_WARPS * 2 * XD_STAGE * 8;
 // XI32: the data rows are resident in decimal6 form (int32 i, value i / 1e6): half the bytes of
 // the pass, which is bound by exactly those bytes.  A stage then holds 32 int rows (stride XSTRI)
 // followed by the XQ query rows (fp64); the value is rebuilt with dec6_to_double (3 fp64 operations).
-constexpr int XSTRI = XC + 2;                                  // ints; rows stay 8-byte aligned
-constexpr int XI_DATA_BYTES = 32 * XSTRI * 4;                  // 4352
+constexpr int XSTRI = XC + 4;                                  // ints; rows stay 16-byte aligned (and LDS.128 by 8 lanes is conflict-free)
+constexpr int XI_DATA_BYTES = 32 * XSTRI * 4;                  // 4608
 constexpr int XI_STAGE_BYTES = XI_DATA_BYTES + XQ * XSTR * 8;  // + 2176
 constexpr int XI_SMEM = X_WARPS * 2 * XI_STAGE_BYTES;
+// XMODE 0: fp64 rows.  1: decimal6 rows, staged two rows per warp instruction (8-byte pieces, any even a).
+// 2: decimal6 rows with a % 4 == 0: four rows per warp instruction (16-byte pieces) and the lanes read
+// their row back four values at a time (LDS.128, conflict-free at this row stride) -- fewer instructions,
+// which is what bounds the pass once the bytes are halved.  (Letting every lane copy its own row segment
+// -- no shuffles at all -- was 6x slower: 32 scattered 16-byte requests per instruction.)
 
-template <bool XI32>
+template <int XMODE>
 __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const RerankArgs a, const Scratch sc) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -308,6 +313,7 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
   const long long p0 = (static_cast<long long>(blockIdx.x) * X_WARPS + warp) * 32;
   if (p0 >= total) return;
   const int cnt = (total - p0) < 32 ? static_cast<int>(total - p0) : 32;
+  constexpr bool XI32 = XMODE != 0;
   constexpr int STAGE_BYTES = XI32 ? XI_STAGE_BYTES : XD_STAGE * 8;
   unsigned char *ring = rr_smem + static_cast<size_t>(warp) * 2 * STAGE_BYTES;
   const bool have = lane < cnt;
@@ -335,6 +341,18 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
         double *qstage = reinterpret_cast<double *>(stage + (XI32 ? XI_DATA_BYTES : 32 * XSTR * 8));
         const int col = chunk * XC + seg * 2;
         const bool in = col + 2 <= a.a;
+        if (XMODE == 2) {
+          // 8 lanes x 16 B cover one 32-column row segment: four rows per warp instruction, coalesced
+          const int sub4 = lane >> 3, seg4 = lane & 7;
+          const int col4 = chunk * XC + seg4 * 4;
+          const bool in4 = col4 + 4 <= a.a;
+          for (int r0 = 0; r0 < cnt; r0 += 4) {
+            const int r = r0 + sub4;
+            const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r < cnt ? r : 0);
+            if (r < cnt && ((amask >> r) & 1u))
+              cp_async_zfill<16>(reinterpret_cast<int *>(stage) + r * XSTRI + seg4 * 4, a.x_attrs_i32 + xo + (in4 ? col4 : 0), in4);
+          }
+        } else
         for (int r0 = 0; r0 < cnt; r0 += 2) {  // data rows of the lanes handled in this pass
           const int r = r0 + sub;
           const long long xo = __shfl_sync(0xFFFFFFFFu, my_x, r < cnt ? r : 0);
@@ -361,7 +379,23 @@ __global__ void __launch_bounds__(X_WARPS * 32) rerank_exact_dedup_kernel(const 
       if (active) {
         const unsigned char *stage = ring + (chunk & 1) * STAGE_BYTES;
         const double *qs = reinterpret_cast<const double *>(stage + (XI32 ? XI_DATA_BYTES : 32 * XSTR * 8)) + (slot - base) * XSTR;
-        if (XI32) {
+        if (XMODE == 2) {
+          const int4 *xs4 = reinterpret_cast<const int4 *>(reinterpret_cast<const int *>(stage) + lane * XSTRI);
+          const double2 *qs2 = reinterpret_cast<const double2 *>(qs);
+#pragma unroll 4
+          for (int i = 0; i < XC / 4; ++i) {
+            const int4 xv = xs4[i];
+            const double2 qa = qs2[2 * i], qb = qs2[2 * i + 1];
+            double d = __dsub_rn(qa.x, dec6_to_double(xv.x));
+            acc = __dadd_rn(acc, __dmul_rn(d, d));
+            d = __dsub_rn(qa.y, dec6_to_double(xv.y));
+            acc = __dadd_rn(acc, __dmul_rn(d, d));
+            d = __dsub_rn(qb.x, dec6_to_double(xv.z));
+            acc = __dadd_rn(acc, __dmul_rn(d, d));
+            d = __dsub_rn(qb.y, dec6_to_double(xv.w));
+            acc = __dadd_rn(acc, __dmul_rn(d, d));
+          }
+        } else if (XI32) {
           const int *xs = reinterpret_cast<const int *>(stage) + lane * XSTRI;
 #pragma unroll 8
           for (int i = 0; i < XC; ++i) {
@@ -538,12 +572,15 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
                    ((args.a % 2 == 0) && reinterpret_cast<uintptr_t>(args.x_attrs_i32) % 8 == 0 &&
                     reinterpret_cast<uintptr_t>(args.q_attrs) % 16 == 0),
                "rerank: decimal6 rows need an even row length and aligned buffers");
-  if (args.x_attrs_i32 != nullptr) {
-    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XI_SMEM));
-    rerank_exact_dedup_kernel<true><<<blocks, X_WARPS * 32, XI_SMEM, s>>>(args, sc);
+  if (args.x_attrs_i32 != nullptr && args.a % 4 == 0 && reinterpret_cast<uintptr_t>(args.x_attrs_i32) % 16 == 0) {
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, XI_SMEM));
+    rerank_exact_dedup_kernel<2><<<blocks, X_WARPS * 32, XI_SMEM, s>>>(args, sc);
+  } else if (args.x_attrs_i32 != nullptr) {
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, XI_SMEM));
+    rerank_exact_dedup_kernel<1><<<blocks, X_WARPS * 32, XI_SMEM, s>>>(args, sc);
   } else if (vec2 && dedup) {
-    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XD_SMEM));
-    rerank_exact_dedup_kernel<false><<<blocks, X_WARPS * 32, XD_SMEM, s>>>(args, sc);
+    DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_dedup_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, XD_SMEM));
+    rerank_exact_dedup_kernel<0><<<blocks, X_WARPS * 32, XD_SMEM, s>>>(args, sc);
   } else if (vec2) {
     DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_exact_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, X_SMEM));
     rerank_exact_kernel<true><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);
