@@ -533,6 +533,37 @@ def pack_i32(src, rng, maxima=None, out=None, wait=None, signal=None):
     return h, n2, en
 
 
+def wire_words(a, bits):
+    """32-bit words per row of `a` values at `bits` bits each."""
+    return (a * bits + 31) // 32
+
+
+def pack_bits(src_i32, bits, out=None):
+    """dmlp_pack_bits: int32 [rows, a] -> int32-typed words [rows, wire_words(a, bits)]."""
+    lib = _lib()
+    lib.dmlp_pack_bits.argtypes = [_vp, _i64, _i, _i, _i, _vp, _vp]
+    rows, a = src_i32.shape
+    words = wire_words(a, bits)
+    if out is None:
+        out = torch.empty((rows, words), dtype=torch.int32, device=src_i32.device)
+    _check(lib.dmlp_pack_bits(_p(src_i32), rows, a, bits, words, _p(out), _stream()))
+    return out
+
+
+def unpack_bits(src_words, a, bits, dst):
+    """dmlp_unpack_bits: words [rows, wire_words(a, bits)] -> int32 or float64 [rows, a] (by dst's dtype)."""
+    lib = _lib()
+    lib.dmlp_unpack_bits.argtypes = [_vp, _i64, _i, _i, _i, _vp, _vp, _vp]
+    rows, words = src_words.shape
+    assert words == wire_words(a, bits) and tuple(dst.shape) == (rows, a) and dst.is_contiguous()
+    assert src_words.is_contiguous()
+    is_f64 = dst.dtype == torch.float64
+    assert is_f64 or dst.dtype == torch.int32
+    _check(lib.dmlp_unpack_bits(_p(src_words), rows, a, bits, words, None if is_f64 else _p(dst),
+                                _p(dst) if is_f64 else None, _stream()))
+    return dst
+
+
 def encode_decimal6_into(src, dst):
     """Re-encode fp64 values into an existing int32 tensor (no check read back: the caller knows
     the values are representable)."""

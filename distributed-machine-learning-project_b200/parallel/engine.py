@@ -630,7 +630,9 @@ class DistributedKNN:
 
         wire = "fp64" keeps doubles on the wire; "decimal6" sends the six-decimal values of
         the text grammar as 32-bit integers (half the PCIe bytes, expanded bit-exactly on
-        the device); "auto" picks decimal6 when every value on every rank round-trips."""
+        the device); "auto" picks decimal6 when every value on every rank round-trips.  When the
+        integers need fewer than 32 bits (values in [-100, 100]: 28) the rows travel bit-packed
+        (`wire_bits` per value, K.pack_bits / K.unpack_bits; DMLP_WIRE_BITS=0 keeps int32)."""
         dev = self.device
         with torch.cuda.device(dev):
             use_dec = False
@@ -652,6 +654,20 @@ class DistributedKNN:
                 dist.all_reduce(rng, op=dist.ReduceOp.MAX)
             self.host_range = (-rng[0].item(), rng[1].item())
             self.wire = "decimal6" if use_dec else "fp64"
+            self.wire_bits = 0
+            if use_dec and os.environ.get("DMLP_WIRE_BITS", "auto") != "0":
+                big = torch.tensor([max(int(xi.abs().max().item()) if xi.numel() else 0,
+                                        int(qi.abs().max().item()) if qi.numel() else 0)], dtype=torch.int64, device=dev)
+                if self.world > 1:
+                    dist.all_reduce(big, op=dist.ReduceOp.MAX)
+                bits = max(int(big.item()).bit_length() + 1, 2)       # i + 2^(bits-1) in [0, 2^bits)
+                forced = os.environ.get("DMLP_WIRE_BITS", "auto")
+                if forced != "auto":
+                    bits = max(bits, int(forced))
+                if bits < 32 and K.wire_words(self.a, bits) < self.a:
+                    self.wire_bits = bits
+                    xi, qi = K.pack_bits(xi, bits), K.pack_bits(qi, bits)
+            self.wire_cols = K.wire_words(self.a, self.wire_bits) if self.wire_bits else self.a
             self.host = {
                 "x": (xi if use_dec else self.x_part).cpu().pin_memory(),
                 "labels": self.labels_part.cpu().pin_memory(),
@@ -668,8 +684,10 @@ class DistributedKNN:
             self.chunk_rows = rows
             if use_dec:
                 # two complete sets of wire buffers: the copies of step s + 1 run while step s computes
-                self.x_wire = [torch.empty(self.x_part.shape, dtype=torch.int32, device=dev) for _ in range(2)]
-                self.q_wire = [torch.empty((max(self.nq, 1), self.a), dtype=torch.int32, device=dev) for _ in range(2)]
+                self.x_wire = [torch.empty((self.x_part.shape[0], self.wire_cols), dtype=torch.int32, device=dev)
+                               for _ in range(2)]
+                self.q_wire = [torch.empty((max(self.nq, 1), self.wire_cols), dtype=torch.int32, device=dev)
+                               for _ in range(2)]
                 self.l_wire = [torch.empty_like(self.labels_part) for _ in range(2)]
                 self.k_wire = [torch.empty_like(self.k_slice) for _ in range(2)]
             self._e2e_step, self._prefetched = 0, None
@@ -745,7 +763,7 @@ class DistributedKNN:
         self._wait_part_readers()              # the row's peers may still be pulling the previous step's rows
         self._install_small(slot, events)
         self._install_x(self.x_wire[slot])
-        K.expand_decimal6(self.q_wire[slot][: self.nq], self.q_slice)
+        self._wire_to_f64(self.q_wire[slot][: self.nq], self.q_slice)
         K.stats_set(self.stats, *self.host_range)
         self.launch_count += 2
         return self.run_resident()
@@ -762,9 +780,23 @@ class DistributedKNN:
         kernel, no expansion; the fp64 copy of the part is then NOT refreshed (the direct kernels read
         the decimal6 rows too).  Otherwise it is expanded to fp64."""
         if self.dec6:
-            torch.add(wire, 0, out=self.x32_part)
+            self._wire_to_i32(wire, self.x32_part)
         else:
-            K.expand_decimal6(wire, self.x_part)
+            self._wire_to_f64(wire, self.x_part)
+
+    def _wire_to_f64(self, wire, dst):
+        """Rows that arrived in the decimal6 wire form (int32, or bit-packed words) -> fp64."""
+        if self.wire_bits:
+            K.unpack_bits(wire, self.a, self.wire_bits, dst)
+        else:
+            K.expand_decimal6(wire, dst)
+
+    def _wire_to_i32(self, wire, dst):
+        """Rows that arrived in the decimal6 wire form -> the resident int32 rows."""
+        if self.wire_bits:
+            K.unpack_bits(wire, self.a, self.wire_bits, dst)
+        else:
+            torch.add(wire, 0, out=dst)
 
     def _rerank_chunk(self, i, b, e, cand):
         """Re-rank + folded vote + device-side repair of query rows [b, e) (chunk i of a streamed step)."""
@@ -793,7 +825,7 @@ class DistributedKNN:
             self.x_wire[0].copy_(h["x"], non_blocking=True)
             self._install_x(self.x_wire[0])
             self.q_wire[0][: self.nq].copy_(h["q"], non_blocking=True)
-            K.expand_decimal6(self.q_wire[0][: self.nq], self.q_slice)
+            self._wire_to_f64(self.q_wire[0][: self.nq], self.q_slice)
         else:
             self.x_part.copy_(h["x"], non_blocking=True)
             self.q_slice.copy_(h["q"], non_blocking=True)
@@ -824,7 +856,7 @@ class DistributedKNN:
         # copy order: the interleaving with the smallest simulated makespan (the work is a product
         # of queries x data, so what arrives last decides how much is left to do after the copies)
         order = best_copy_order([e - b for b, e in qch], [pe - pb for pb, pe in xparts], self.a,
-                                4 if self.wire == "decimal6" else 8)
+                                (self.wire_bits / 8.0 if self.wire_bits else 4) if self.wire == "decimal6" else 8)
         self._tiled = (xparts, qch, cands, bases, order)
         return self._tiled
 
@@ -881,7 +913,10 @@ class DistributedKNN:
         self.epoch += 1
         slot, events = self._step_copies(pieces)
         self._install_small(slot, events)
-        self._x32_step = (self.x_wire[slot] if dec else self.x32) if self.dec6 else None
+        # int32 wire: pack and re-rank read the wire set itself (no expansion at all); bit-packed wire:
+        # each arriving part is unpacked into the resident int32 rows first
+        direct = dec and self.dec6 and not self.wire_bits
+        self._x32_step = (self.x_wire[slot] if direct else self.x32) if self.dec6 else None
         K.stats_reset(self.stats)
         K.stats_reset(self.q_stats)
         K.stats_set(self.stats, *self.host_range)
@@ -894,11 +929,14 @@ class DistributedKNN:
             if kind == "x":
                 pb, pe = xparts[idx]
                 out = (self.xh[pb:pe], self.xn[pb:pe], self.xe[pb:pe])
-                if dec and self.dec6:        # pack (and later re-rank) straight from the wire set: no expansion at all
-                    K.pack_i32(self.x_wire[slot][pb:pe], self.stats, self.stats, out=out)
+                if dec and self.dec6:
+                    if not direct:
+                        self._wire_to_i32(self.x_wire[slot][pb:pe], self.x32[pb:pe])
+                        self.launch_count += 1
+                    K.pack_i32(self._x32_step[pb:pe], self.stats, self.stats, out=out)
                 else:
                     if dec:
-                        K.expand_decimal6(self.x_wire[slot][pb:pe], self.x_part[pb:pe])
+                        self._wire_to_f64(self.x_wire[slot][pb:pe], self.x_part[pb:pe])
                     else:
                         self._refresh_x32(pb, pe)
                     K.pack(self.x[pb:pe], self.stats, self.stats, out=out)
@@ -906,7 +944,7 @@ class DistributedKNN:
             else:
                 b, e = qch[idx]
                 if dec:
-                    K.expand_decimal6(self.q_wire[slot][b:e], self.q_slice[b:e])
+                    self._wire_to_f64(self.q_wire[slot][b:e], self.q_slice[b:e])
                 K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(self.qh[b:e], self.qn[b:e], self.qe_[b:e]))
                 have_q.add(idx)
             self.launch_count += 1 + (1 if dec else 0)
@@ -962,7 +1000,7 @@ class DistributedKNN:
         for i, (b, e) in enumerate(chunks):
             main.wait_event(events[3 + i])
             if dec:
-                K.expand_decimal6(self.q_wire[slot][b:e], self.q_slice[b:e])
+                self._wire_to_f64(self.q_wire[slot][b:e], self.q_slice[b:e])
             qh, qn, qe = self.qh[b:e], self.qn[b:e], self.qe_[b:e]
             K.pack(self.q_slice[b:e], self.stats, self.q_stats, out=(qh, qn, qe))
             key = e - b

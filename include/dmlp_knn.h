@@ -50,6 +50,14 @@ int dmlp_stats_set(void *stats, double lo, double hi, void *stream);
 int dmlp_encode_decimal6(const double *src, int *dst, int64_t count, int *bad, void *stream);
 int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *stream);
 
+/* Bit-packed decimal6: when every |i| < 2^(bits-1), a row of `a` integers travels as a little-endian
+ * stream of `bits`-bit numbers i + 2^(bits-1), padded to `words` 32-bit words per row (words * 32 >=
+ * a * bits).  Values in [-100, 100] need 28 bits: 12.5 % fewer PCIe bytes than int32.  unpack
+ * writes either the integers (dst_i32) or the expanded doubles (dst_f64); exactly one is non-NULL. */
+int dmlp_pack_bits(const int *src, int64_t rows, int a, int bits, int words, uint32_t *dst, void *stream);
+int dmlp_unpack_bits(const uint32_t *src, int64_t rows, int a, int bits, int words, int *dst_i32, double *dst_f64,
+                     void *stream);
+
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
  * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
  * candidate buffer holds q * chunks * kp 64-bit keys.  kmax = the largest k any query

@@ -152,6 +152,10 @@ struct ScatterArgs {
 };
 
 int launch_expand_decimal6(const int *src, double *dst, long long count, cudaStream_t s);
+/// bit-packed decimal6 wire format (pack.cu): `bits` per value, `words` 32-bit words per row
+int launch_pack_bits(const int *src, long long rows, int a, int bits, int words, unsigned *dst, cudaStream_t s);
+int launch_unpack_bits(const unsigned *src, long long rows, int a, int bits, int words, int *dst_i32, double *dst_f64,
+                       cudaStream_t s);
 int launch_encode_decimal6(const double *src, int *dst, long long count, int *bad, cudaStream_t s);
 
 /// max row norm / error norm over packed rows, from the norm arrays (after a gather)

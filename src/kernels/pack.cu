@@ -185,6 +185,88 @@ __global__ void __launch_bounds__(256) encode_decimal6_kernel(const double *__re
   if (local_bad) atomicExch(bad, 1);
 }
 
+// Bit-packed decimal6 wire: a value i with |i| < 2^(bits-1) travels as the `bits`-bit unsigned
+// number i + 2^(bits-1); a row of `a` values is a little-endian bit stream padded to whole 32-bit
+// words (`words` per row).  Values in [-100, 100] with six decimals need 28 bits: 12.5 % fewer
+// bytes over PCIe than int32, 56 % fewer than fp64.
+__global__ void __launch_bounds__(256) pack_bits_kernel(const int *__restrict__ src, long long rows, int a, int bits,
+                                                        int words, unsigned *__restrict__ dst) {
+  const long long total = rows * words;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const unsigned long long mask = (1ULL << bits) - 1ULL;
+  const unsigned bias = 1u << (bits - 1);
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+    const long long r = t / words;
+    const int w = static_cast<int>(t - r * words);
+    const int *row = src + r * a;
+    const long long bit0 = 32LL * w;
+    unsigned word = 0;
+    for (int c = static_cast<int>(bit0 / bits); c < a && static_cast<long long>(c) * bits < bit0 + 32; ++c) {
+      const unsigned long long u = static_cast<unsigned long long>(static_cast<unsigned>(row[c]) + bias) & mask;
+      const long long sh = static_cast<long long>(c) * bits - bit0;   // position of the value's bit 0 in this word
+      word |= sh >= 0 ? static_cast<unsigned>(u << sh) : static_cast<unsigned>(u >> (-sh));
+    }
+    dst[t] = word;
+  }
+}
+
+template <bool TO_F64>
+__global__ void __launch_bounds__(256) unpack_bits_kernel(const unsigned *__restrict__ src, long long rows, int a,
+                                                          int bits, int words, int rows_per_chunk,
+                                                          int *__restrict__ dst_i, double *__restrict__ dst_d) {
+  const unsigned long long mask = (1ULL << bits) - 1ULL;
+  const unsigned bias = 1u << (bits - 1);
+  const long long chunks = (rows + rows_per_chunk - 1) / rows_per_chunk;
+  for (long long ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+    const long long r0 = ch * rows_per_chunk;
+    const unsigned nrows = static_cast<unsigned>(rows - r0 < rows_per_chunk ? rows - r0 : rows_per_chunk);
+    const unsigned *in = src + r0 * words;
+    const long long out0 = r0 * a;
+    for (unsigned idx = threadIdx.x; idx < nrows * static_cast<unsigned>(a); idx += 256) {   // 32-bit index math
+      const unsigned r = idx / static_cast<unsigned>(a), c = idx - r * static_cast<unsigned>(a);
+      const unsigned off = c * static_cast<unsigned>(bits);
+      const unsigned w = off >> 5, sh = off & 31u;
+      const unsigned *row = in + r * static_cast<unsigned>(words);
+      unsigned long long v = row[w];
+      if (sh + bits > 32) v |= static_cast<unsigned long long>(row[w + 1]) << 32;   // (w + 1 < words whenever bits are left)
+      const int i = static_cast<int>(static_cast<unsigned>((v >> sh) & mask) - bias);
+      if (TO_F64) dst_d[out0 + idx] = dec6_to_double(i);
+      else dst_i[out0 + idx] = i;
+    }
+  }
+}
+
+int launch_pack_bits(const int *src, long long rows, int a, int bits, int words, unsigned *dst, cudaStream_t s) {
+  if (rows <= 0) return 0;
+  DMLP_REQUIRE(bits >= 2 && bits <= 32 && static_cast<long long>(words) * 32 >= static_cast<long long>(a) * bits,
+               "pack_bits: bits must be in [2, 32] and the row must fit its words");
+  long long blocks = (rows * words + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_bits_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, bits, words, dst);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_unpack_bits(const unsigned *src, long long rows, int a, int bits, int words, int *dst_i32, double *dst_f64,
+                       cudaStream_t s) {
+  if (rows <= 0) return 0;
+  DMLP_REQUIRE(bits >= 2 && bits <= 32 && static_cast<long long>(words) * 32 >= static_cast<long long>(a) * bits,
+               "unpack_bits: bits must be in [2, 32] and the row must fit its words");
+  DMLP_REQUIRE((dst_i32 != nullptr) != (dst_f64 != nullptr), "unpack_bits: exactly one destination");
+  DMLP_REQUIRE(a >= 1 && a <= (1 << 20), "unpack_bits: 1 <= a <= 2^20");
+  const int rpc = a >= 2048 ? 1 : 2048 / a;          // about 2048 values (8 per thread) per block and pass
+  long long blocks = (rows + rpc - 1) / rpc;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (dst_f64 != nullptr)
+    unpack_bits_kernel<true><<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, bits, words, rpc, nullptr,
+                                                                           dst_f64);
+  else
+    unpack_bits_kernel<false><<<static_cast<unsigned>(blocks), 256, 0, s>>>(src, rows, a, bits, words, rpc, dst_i32,
+                                                                            nullptr);
+  DMLP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int launch_expand_decimal6(const int *src, double *dst, long long count, cudaStream_t s) {
   if (count <= 0) return 0;
   long long blocks = (count + 256 * 8 - 1) / (256 * 8);

@@ -131,6 +131,15 @@ int dmlp_expand_decimal6(const int *src, double *dst, int64_t count, void *strea
   return launch_expand_decimal6(src, dst, count, st(stream));
 }
 
+int dmlp_pack_bits(const int *src, int64_t rows, int a, int bits, int words, uint32_t *dst, void *stream) {
+  return launch_pack_bits(src, rows, a, bits, words, dst, st(stream));
+}
+
+int dmlp_unpack_bits(const uint32_t *src, int64_t rows, int a, int bits, int words, int *dst_i32, double *dst_f64,
+                     void *stream) {
+  return launch_unpack_bits(src, rows, a, bits, words, dst_i32, dst_f64, st(stream));
+}
+
 int dmlp_encode_decimal6(const double *src, int *dst, int64_t count, int *bad, void *stream) {
   return launch_encode_decimal6(src, dst, count, bad, st(stream));
 }

@@ -372,8 +372,37 @@ def test_decimal6_wire_round_trip(K):
     assert not K.encode_decimal6(big)[1]
 
 
+@pytest.mark.parametrize("a,bits", [(64, 28), (33, 28), (5, 9), (100, 31), (7, 2), (64, 32)])
+def test_bit_packed_wire_round_trip(K, a, bits):
+    """pack_bits / unpack_bits against a host restatement of the wire format: value i travels as
+    the `bits`-bit number i + 2^(bits-1), rows are little-endian bit streams padded to 32-bit words."""
+    rng = np.random.default_rng(a * 100 + bits)
+    half = 1 << (bits - 1)
+    vals = rng.integers(-half, half, size=(301, a), dtype=np.int64)
+    vals[0, :] = -half
+    vals[1, :] = half - 1
+    src = torch.from_numpy(vals.astype(np.int32)).cuda()
+    words = K.pack_bits(src, bits)
+    assert words.shape == (301, K.wire_words(a, bits))
+    # host restatement
+    u = (vals + half).astype(object)
+    expect = np.zeros((301, K.wire_words(a, bits)), dtype=np.uint32)
+    for r in (0, 1, 2, 150, 300):
+        stream = 0
+        for c in range(a):
+            stream |= int(u[r, c]) << (c * bits)
+        for w in range(expect.shape[1]):
+            expect[r, w] = (stream >> (32 * w)) & 0xFFFFFFFF
+        assert (words[r].cpu().numpy().view(np.uint32) == expect[r]).all(), r
+    back = K.unpack_bits(words, a, bits, torch.empty_like(src))
+    assert torch.equal(back, src)
+    if bits <= 31:
+        dbl = K.unpack_bits(words, a, bits, torch.empty((301, a), dtype=torch.float64, device="cuda"))
+        assert torch.equal(dbl, K.expand_decimal6(src, torch.empty_like(dbl)))
+
+
 @pytest.mark.parametrize("n_total,parts", [(3000, 1), (9000, 2), (20000, 4)])
-def test_streamed_end_to_end_single_gpu(K, n_total, parts):
+def test_streamed_end_to_end_single_gpu(K, n_total, parts, monkeypatch):
     """run_from_host: copies overlapped with compute; with a large enough shard the data is
     cut into parts and every (query chunk, data part) pair is filtered as it arrives."""
     from dmlp_b200.parallel import DistributedKNN
@@ -382,9 +411,11 @@ def test_streamed_end_to_end_single_gpu(K, n_total, parts):
                       seed=3)
     _, ref = eng.run_resident()
     ref = ref.cpu().numpy().copy()
-    for wire in ("auto", "fp64"):
-        eng.stage_host_inputs(wire=wire)
-        assert eng.streamed and eng.wire == ("decimal6" if wire == "auto" else "fp64") and eng.x_parts == parts
+    for wire in ("auto", "int32", "fp64"):       # bit-packed decimal6, plain int32 decimal6, doubles
+        monkeypatch.setenv("DMLP_WIRE_BITS", "0" if wire == "int32" else "auto")
+        eng.stage_host_inputs(wire="auto" if wire == "int32" else wire)
+        assert eng.streamed and eng.wire == ("fp64" if wire == "fp64" else "decimal6") and eng.x_parts == parts
+        assert eng.wire_bits == (28 if wire == "auto" else 0)
         for step in range(4):      # steps 0 and 1 also start the next step's copies (second wire set)
             _, chk = eng.run_from_host(prefetch_next=step < 2)
             assert (chk.numpy() == ref).all(), wire
