@@ -85,6 +85,36 @@ __host__ __device__ __forceinline__ bool get_item(const TopkPlan &p, int t, int 
   return true;
 }
 
+// The i-th item of a cluster.  Static schedule: round-robin over the item list (whole waves of
+// co-resident groups, see make_topk_plan).  Dynamic schedule (plan.dyn_slots): the leader CTA's
+// producer thread takes the next item from an atomic counter and publishes it in the cluster's
+// slot i; every other role of both CTAs (MMA issuer, epilogue warps, the second CTA's producer)
+// reads that slot when it gets there -- the producer runs a pipeline depth ahead, so the slot is
+// normally filled long before.  Returns -1 when the cluster is done.
+__device__ __forceinline__ int next_item(const TopkPlan &plan, int cluster_id, int num_clusters, int i, int total_items,
+                                         bool grab) {
+  if (plan.dyn_slots == nullptr) {
+    const long long t = cluster_id + static_cast<long long>(i) * num_clusters;
+    return t < total_items ? static_cast<int>(t) : -1;
+  }
+  unsigned *slot = plan.dyn_slots + static_cast<size_t>(cluster_id) * plan.dyn_cap + i;
+  unsigned v;
+  if (grab) {
+    const unsigned t = atomicAdd(plan.dyn_counter, 1u);
+    v = t < static_cast<unsigned>(total_items) ? t + 2u : 1u;
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(slot), "r"(v) : "memory");
+  } else {
+    const long long t0 = clock64();
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(slot) : "memory");
+      if (v != 0) break;
+      if (clock64() - t0 > 8000000000LL) __trap();   // a lost producer: fail, never hang
+      __nanosleep(100);
+    }
+  }
+  return v == 1u ? -1 : static_cast<int>(v - 2u);
+}
+
 __device__ __forceinline__ unsigned long long shfl_xor_u64(unsigned long long v, int mask) {
   return __shfl_xor_sync(0xFFFFFFFFu, v, mask);
 }
@@ -193,7 +223,10 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
   const bool prof = plan.prof != nullptr;
   const long long prof_t0 = prof ? clock64() : 0;
 
-  for (int t = cluster_id; t < total_items; t += num_clusters) {
+  for (int i = 0;; ++i) {
+    int t = lane == 0 ? next_item(plan, cluster_id, num_clusters, i, total_items, false) : 0;
+    t = __shfl_sync(0xFFFFFFFFu, t, 0);
+    if (t < 0) break;
     Item it;
     if (!get_item(plan, t, cta_rank, &it)) continue;
     for (int tile = it.tile_begin; tile < it.tile_end; ++tile, ++acc_it) {
@@ -796,7 +829,9 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       const long long p_t0 = plan.prof ? clock64() : 0;
       const uint64_t pol_q = plan.hint_q == 2 ? kL2EvictLast : (plan.hint_q == 1 ? kL2EvictFirst : kL2EvictNormal);
       const uint64_t pol_x = plan.hint_x == 2 ? kL2EvictLast : (plan.hint_x == 1 ? kL2EvictFirst : kL2EvictNormal);
-      for (int t = cluster_id; t < total_items; t += num_clusters) {
+      for (int i = 0;; ++i) {
+        const int t = next_item(plan, cluster_id, num_clusters, i, total_items, /*grab=*/cta_rank == 0);
+        if (t < 0) break;
         Item it;
         if (!get_item(plan, t, cta_rank, &it)) continue;
         unsigned sync_epoch = 0;
@@ -932,7 +967,9 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       uint32_t uses[2] = {0, 0};  // fills of each accumulator stage (same count as the epilogue keeps)
       long long mw_full = 0, mw_tempty = 0;
       const long long m_t0 = plan.prof ? clock64() : 0;
-      for (int t = cluster_id; t < total_items; t += num_clusters) {
+      for (int i = 0;; ++i) {
+        const int t = next_item(plan, cluster_id, num_clusters, i, total_items, false);
+        if (t < 0) break;
         Item it;
         if (!get_item(plan, t, cta_rank, &it)) continue;
         if constexpr (SKEW) {
@@ -1133,6 +1170,14 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   if (p.gap >= 0 && ((p.k_blocks + p.gap) & 1)) ++p.gap;   // the half period must be whole
   if (p.gap > p.k_blocks - 2) p.gap -= 2;
   if (p.gap < 0 || !p.wide) p.gap = -1;
+  // -1 = automatic: dynamic only where the launch runs without re-alignment (short rows).  Measured on
+  // B200 (profiles/ab_dyn_r2.jsonl): +2.6 % at A = 64, +-0 at A = 512, -14..-17 % at A = 8192, where the
+  // static waves are balanced anyway and the re-alignment of co-resident clusters is worth 23 %.
+  p.dyn = -1;
+  if (const char *e = getenv("DMLP_TOPK_DYN")) p.dyn = atoi(e) != 0;
+  p.dyn_counter = nullptr;
+  p.dyn_slots = nullptr;
+  p.dyn_cap = 0;
   p.rot = 0;
   p.cand_chunks = 0;  // filled in once the chunk count is known
   p.chunk_base = 0;
@@ -1212,6 +1257,10 @@ namespace {
 constexpr int kSyncCounters = 16384;
 __device__ unsigned g_sync_counters[kSyncCounters];
 std::atomic<unsigned long long> g_sync_cursor{0};
+// Dynamic scheduler scratch: counter + per-cluster slots, handed out in slices like the counters above.
+constexpr int kDynWords = 1 << 20;
+__device__ unsigned g_dyn_words[kDynWords];
+std::atomic<unsigned long long> g_dyn_cursor{0};
 constexpr int kProfCtas = 256;
 __device__ unsigned long long g_prof[kProfCtas * 16];
 int g_prof_ctas = 0;
@@ -1277,6 +1326,32 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
       plan.sync_cnt = slice;
     } else {
       plan.sync = 0;
+    }
+  }
+  plan.dyn_counter = plan.dyn_slots = nullptr;
+  if ((plan.dyn > 0 || (plan.dyn < 0 && plan.sync == 0)) && plan.pair && (gather == nullptr || gather->world <= 1) &&
+      (data_gather == nullptr || data_gather->world <= 1)) {
+    // the gather warps of the fused multi-GPU launches walk the static item list: those stay static
+    const int groups = (plan.mc_blocks + plan.group_mc - 1) / plan.group_mc;
+    const long long total_items = static_cast<long long>(groups) * plan.group_mc * plan.chunks;
+    const long long cap = total_items + 1;     // every grab of one cluster, plus its end marker
+    const long long need = 1 + cap * (plan.grid / plan.cluster);
+    if (need <= kDynWords) {
+      void *p = nullptr;
+      DMLP_CUDA_OK(cudaGetSymbolAddress(&p, g_dyn_words));
+      unsigned long long cur = g_dyn_cursor.load(), off, next;
+      do {
+        off = cur % kDynWords;
+        if (off + need > kDynWords) off = 0;
+        next = off + need;
+      } while (!g_dyn_cursor.compare_exchange_weak(cur, next));
+      unsigned *slice = static_cast<unsigned *>(p) + off;
+      DMLP_CUDA_OK(cudaMemsetAsync(slice, 0, sizeof(unsigned) * need, s));
+      plan.dyn_counter = slice;
+      plan.dyn_slots = slice + 1;
+      plan.dyn_cap = static_cast<int>(cap);
+      plan.sync = 0;   // a group's clusters no longer start its items together
+      plan.sync_cnt = nullptr;
     }
   }
   plan.prof = nullptr;

@@ -68,6 +68,10 @@ struct TopkPlan {
   const unsigned *gate_cnt;  ///< set when the data rows are gathered from peers by the kernel itself: per-tile arrival counters the epilogue checks before it stages a tile's norms
   unsigned gate_epoch;
   int gap;         ///< wide only: >= 0 = skewed schedule, steps an accumulator rests between tiles; -1 = lock-step wide tile
+  int dyn;         ///< clusters take items from an atomic counter instead of the static round-robin: 1 always (switches the re-alignment off), 0 never, -1 (default) where the launch has no re-alignment anyway; single-GPU launches only (DMLP_TOPK_DYN)
+  unsigned *dyn_counter;   ///< next item to hand out (zeroed per launch)
+  unsigned *dyn_slots;     ///< [clusters][dyn_cap]: item + 2 of a cluster's i-th grab, 1 = no more items, 0 = not yet known
+  int dyn_cap;
   unsigned long long *prof;  ///< diagnostics (DMLP_TOPK_PROF=1): per CTA 16 cycle counters, see dist_topk_prof_read
   int rot;         ///< rotation of the cluster-row order (multi-GPU: start with the local slice)
   int hint_q, hint_x;  ///< L2 eviction hints for query / data tiles: 0 normal, 1 first, 2 last

@@ -143,6 +143,35 @@ def test_dist_topk_wide_tile_equals_narrow(K, q, n, a, chunks, gmc, sync, monkey
             assert torch.equal(ref[0], od) and torch.equal(ref[1], oi), name
 
 
+@pytest.mark.parametrize("q,n,a,chunks,gmc", [(600, 5000, 64, 3, 2), (1000, 9000, 128, 5, 2), (257, 777, 128, 0, 0),
+                                              (1000, 5000, 1024, 3, 2), (5000, 20000, 64, 0, 0),
+                                              (40000, 3000, 64, 4, 3)])
+def test_dist_topk_dynamic_schedule_equals_static(K, q, n, a, chunks, gmc, monkeypatch):
+    """DMLP_TOPK_DYN=1: clusters take their items from an atomic counter (the leader's producer
+    thread grabs, every other role reads the cluster's slot).  Which cluster computes a (query block,
+    chunk) list does not change the list: the candidates must be bit-identical to the static
+    round-robin, for the narrow and the wide tile, with few and with many items per cluster."""
+    if chunks:
+        monkeypatch.setenv("DMLP_TOPK_CHUNKS", str(chunks))
+        monkeypatch.setenv("DMLP_TOPK_GMC", str(gmc))
+    data, _, queries, _ = cpu.synth(n, q, a, -100.0, 100.0, 1, 1, 2, seed=12)
+    x, qq = _dev(data), _dev(queries)
+    st = K.new_stats()
+    K.stats_update(x, st)
+    K.stats_update(qq, st)
+    xh, xn, _ = K.pack(x, st, st)
+    qh, _, _ = K.pack(qq, st)
+    for wide in ("0", "1"):
+        monkeypatch.setenv("DMLP_TOPK_WIDE", wide)
+        monkeypatch.setenv("DMLP_TOPK_DYN", "0")
+        ref = K.dist_topk(qh, xh, xn).clone()
+        monkeypatch.setenv("DMLP_TOPK_DYN", "1")
+        for _ in range(2):      # twice: the scheduler's scratch is handed out and zeroed per launch
+            got = K.dist_topk(qh, xh, xn).clone()
+            torch.cuda.synchronize()
+            assert torch.equal(ref, got), wide
+
+
 def test_knn_local_long_rows_take_the_wide_tile(K):
     # 4096 values per row: the planner picks the wide tile by itself
     n, q, a, kmax = 3000, 520, 4096, 12
