@@ -40,10 +40,11 @@ def _as_device(x, dtype, device, non_blocking=True):
 def choose_path(n, q, a, kmax, mode="auto"):
     """fused | exact.  The fused path needs kmax within the epilogue's list capacity."""
     if mode in ("fused", "exact"):
-        if mode == "fused" and kmax > K.FUSED_MAX_K:
-            raise ValueError(f"fused path supports k <= {K.FUSED_MAX_K}, got {kmax}")
+        if mode == "fused" and not K.fused_supported(kmax, max(n, 1)):
+            raise ValueError(f"fused path supports k <= {K.FUSED_MAX_K_GATHER}, or k <= {K.FUSED_MAX_K} with "
+                             f"n >= about 32 k; got k = {kmax}, n = {n}")
         return mode
-    if kmax > K.FUSED_MAX_K or n < 1 or q < 1:
+    if n < 1 or q < 1 or not K.fused_supported(kmax, n):
         return "exact"
     # tiny jobs: one tensor-core tile is mostly padding, go direct
     if n * q * max(a, 1) < (1 << 22):

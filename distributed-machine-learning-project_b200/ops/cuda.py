@@ -11,8 +11,17 @@ from .._native import knn_lib
 
 STATS_BYTES = 32
 KP = 32          # keys kept per (query, chunk) by the fused epilogue
-FUSED_MAX_K = 96  # largest k sent to the fused path: each chunk list keeps 32 keys, so larger k is
-#                   given more chunks (one per 8 of k); the re-rank recomputes up to 256 survivors
+FUSED_MAX_K = 1024        # largest k the fused path takes at all (needs n >= 32 k beyond 96, see fused_supported)
+FUSED_MAX_K_GATHER = 96   # largest k for launches that gather their operands from peers inside the kernel
+
+
+def fused_supported(kmax, n, gather=False):
+    """Does the filter + certified re-rank path take this k on a shard of n rows?  Each (query,
+    chunk) list keeps 32 keys and k gets one list per 8; beyond 256 the filter runs as several
+    launches over row ranges of the data (dmlp_fused_supported)."""
+    lib = knn_lib()
+    lib.dmlp_fused_supported.argtypes = [C.c_int, C.c_int64]
+    return lib.dmlp_fused_supported(int(kmax), int(n)) >= (2 if gather else 1)
 
 _ready = False
 _vp, _i, _i64, _u64, _sz, _dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_size_t, C.c_double

@@ -173,11 +173,15 @@ class DistributedKNN:
         dev, R, C = self.device, self.R, self.C
         n, km = self.shard_rows, self.kmax
         self.a_pad = K.pad64(self.a)
-        self.fused_ok = km <= K.FUSED_MAX_K and n > 0
+        # k <= 96: every layout; 96 < k <= 1024 (and n >= 32 k): the filter runs as several launches over
+        # row ranges of the shard, which the in-kernel gathers do not do -- a single-rank column then
+        # gathers the shard with the peer_gather kernel first, layouts with R > 1 take the direct path
+        self.fused_ok = n > 0 and K.fused_supported(km, n, gather=R > 1)
         self.peer_fused = R > 1 and self.impl == "fused" and self.fused_ok
         self.peer_rows = C > 1 and self.impl == "fused"
         # data operand gathered inside the GEMM (needs the CTA-pair kernel: >= 256 queries per column)
-        self.rows_fused = self.peer_rows and R == 1 and self.fused_ok and self.nq >= 256
+        self.rows_fused = (self.peer_rows and R == 1 and self.fused_ok and self.nq >= 256
+                           and K.fused_supported(km, n, gather=True))
         with torch.cuda.device(dev):
             self.status = torch.zeros(1, dtype=torch.int32, device=dev)
             self.stats = K.new_stats(dev)

@@ -58,11 +58,18 @@ int dmlp_pack_bits(const int *src, int64_t rows, int a, int bits, int words, uin
 int dmlp_unpack_bits(const uint32_t *src, int64_t rows, int a, int bits, int words, int *dst_i32, double *dst_f64,
                      void *stream);
 
+/* Which k the filter + certified re-rank path takes (everything else is the direct fp64 path,
+ * dmlp_exact*): 2 = yes, also for launches that gather operands from peers inside the kernel
+ * (kmax <= 96); 1 = yes for launches on resident operands (kmax <= 1024 and about n >= 32 * kmax --
+ * one 256-row tile per 8 of k, whole groups of 32 tiles beyond k = 256, where the filter runs as
+ * several launches over row ranges of the data, see dmlp_topk_plan); 0 = no. */
+int dmlp_fused_supported(int kmax, int64_t n);
+
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
  * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
  * candidate buffer holds q * chunks * kp 64-bit keys.  kmax = the largest k any query
  * asks for (0 = unknown): every chunk keeps at most 32 candidates per query, so larger k
- * is given more chunks.  The fused path is meant for kmax <= 96. */
+ * is given more chunks.  See dmlp_fused_supported for the k the fused path takes. */
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[8]);
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
                    int num_sms, int kmax, uint64_t *cand, void *stream);

@@ -238,7 +238,9 @@ Plan make_plan(int64_t N, int64_t Q, int a, int kmax, const GpuOptions &opt) {
   s.R = R; s.C = C; s.a = a; s.a_pad = pad64(a); s.kmax = std::max(kmax, 1);
   s.n_max = BlockPartition{N, R}.count(0);
   s.q_max = BlockPartition{Q, C}.count(0);
-  s.fused = !opt.exact_only && kmax <= kFusedMaxK && N >= R && Q > 0 &&   // (no empty data shard on the fused path)
+  // several devices gather operands inside the filter kernel: k <= 96 there, k <= 1024 on one device
+  s.fused = !opt.exact_only && N >= R && Q > 0 &&   // (no empty data shard on the fused path)
+            dmlp_fused_supported(kmax, N / R) >= (R * C > 1 ? 2 : 1) &&
             double(N) * double(Q) * double(std::max(a, 1)) >= double(1 << 22);
   // slices of a column: one per data shard; padded to whole 256-row tiles for the fused gather
   const int64_t per = BlockPartition{s.q_max, R}.count(0);

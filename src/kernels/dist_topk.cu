@@ -1131,8 +1131,43 @@ int make_fp16_tile_map(CUtensorMap *map, const __half *base, long long rows, int
   return 0;
 }
 
+namespace {
+TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax);
+}
+
+// Large k: every (query, chunk) list keeps 32 keys and the certified filter wants one list per 8 of
+// k (the ~1.6 k survivors then fill a list to 13 of 32 on average: a full list, which would flag the
+// query, stays a rare event).  One launch has at most 32 chunks, so for k > 256 the data rows are cut
+// into `parts` ranges of at least 32 tiles and every range gets its own launch and its own lists of
+// the shared candidate buffer.  Needs n >= 8192 * parts (about 32 k); below that the caller's exact
+// path is the better tool anyway (k is then more than 3 % of the data).
 TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax) {
+  const int c_need = (kmax + 7) / 8;
+  const int parts = (c_need + 31) / 32;
+  const int n_tiles = (n + BN - 1) / BN;
+  if (parts > 1 && n_tiles >= 32 * parts) {
+    const int part_kmax = (kmax + parts - 1) / parts;
+    const int tiles0 = (n_tiles + parts - 1) / parts;
+    TopkPlan p = make_single_plan(q_rows, tiles0 * BN, a_pad, kp, num_sms, part_kmax);
+    p.n = n;
+    p.n_tiles = n_tiles;
+    p.parts = parts;
+    p.part_chunks = p.chunks;
+    p.part_kmax = part_kmax;
+    p.chunks = parts * p.part_chunks;
+    p.cand_chunks = p.chunks;
+    return p;
+  }
+  return make_single_plan(q_rows, n, a_pad, kp, num_sms, kmax);
+}
+
+namespace {
+TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax) {
   TopkPlan p;
+  p.parts = 1;
+  p.part_chunks = 0;
+  p.part_kmax = kmax;
+  p.num_sms = num_sms;
   p.q_rows = q_rows;
   p.n = n;
   p.a_pad = a_pad;
@@ -1246,8 +1281,10 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
   // one wave = one whole group (gmc x c clusters), so that clusters sharing a chunk run side by side
   if (p.pair && static_cast<long long>(gmc) * c <= use) use = gmc * c;
   p.grid = use * cluster;
+  p.part_chunks = p.chunks;
   return p;
 }
+}  // namespace
 
 namespace {
 // Re-alignment counters: one file-scope array per device, handed out in slices.  Every launch
@@ -1304,6 +1341,24 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
                      const DataGatherArgs *data_gather) {
   TopkPlan plan = plan_in;
   if (plan.q_rows <= 0 || plan.n <= 0) return 0;
+  if (plan.parts > 1) {
+    DMLP_REQUIRE((gather == nullptr || gather->world <= 1) && (data_gather == nullptr || data_gather->world <= 1),
+                 "dist_topk: the in-kernel gathers need a single launch (k <= 256)");
+    for (int p = 0; p < plan.parts; ++p) {
+      const int t0 = static_cast<int>(static_cast<long long>(p) * plan.n_tiles / plan.parts);
+      const int t1 = static_cast<int>(static_cast<long long>(p + 1) * plan.n_tiles / plan.parts);
+      const int r0 = t0 * BN, r1 = t1 * BN < plan.n ? t1 * BN : plan.n;
+      TopkPlan sub = make_single_plan(plan.q_rows, r1 - r0, plan.a_pad, plan.kp, plan.num_sms, plan.part_kmax);
+      DMLP_REQUIRE(sub.chunks == plan.part_chunks, "dist_topk: the parts of a large-k launch must agree on their chunk count");
+      sub.cand_chunks = plan.cand_chunks;
+      sub.chunk_base = plan.chunk_base + p * plan.part_chunks;
+      sub.row_base = plan.row_base + r0;
+      if (int rc = launch_dist_topk(qh, xh + static_cast<size_t>(r0) * plan.a_pad, xnorm2 + r0, sub, cand, nullptr, s,
+                                    nullptr))
+        return rc;
+    }
+    return 0;
+  }
   {
     // per-launch tile-alignment counters (internal scratch, one set per device)
     const int groups = (plan.mc_blocks + plan.group_mc - 1) / plan.group_mc;

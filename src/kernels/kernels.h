@@ -68,6 +68,10 @@ struct TopkPlan {
   const unsigned *gate_cnt;  ///< set when the data rows are gathered from peers by the kernel itself: per-tile arrival counters the epilogue checks before it stages a tile's norms
   unsigned gate_epoch;
   int gap;         ///< wide only: >= 0 = skewed schedule, steps an accumulator rests between tiles; -1 = lock-step wide tile
+  int parts;       ///< > 1 (large k): the launch is split into `parts` launches over row ranges of the data, each writing `part_chunks` of the `chunks` lists -- a list keeps 32 keys, so k up to 1024 needs up to 128 lists per query
+  int part_chunks; ///< lists per part (= chunks when parts == 1)
+  int part_kmax;   ///< the kmax each part is planned for
+  int num_sms;     ///< what the plan was made for (the parts are planned at launch)
   int dyn;         ///< clusters take items from an atomic counter instead of the static round-robin: 1 always (switches the re-alignment off), 0 never, -1 (default) where the launch has no re-alignment anyway; single-GPU launches only (DMLP_TOPK_DYN)
   unsigned *dyn_counter;   ///< next item to hand out (zeroed per launch)
   unsigned *dyn_slots;     ///< [clusters][dyn_cap]: item + 2 of a cluster's i-th grab, 1 = no more items, 0 = not yet known

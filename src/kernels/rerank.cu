@@ -37,12 +37,15 @@ namespace k {
 namespace {
 
 constexpr int RR_THREADS = 128;
-constexpr int WMAX = 256;       // survivors recomputed per query, at most
+// survivors recomputed per query, at most: 256 for the usual small k, about 2 k beyond (k <= 1024:
+// the certified survivor set is ~1.6 k on average and its relative spread shrinks as k grows)
+inline int wmax_for(int kmax) { return kmax <= 96 ? 256 : (2 * kmax + 64 + 31) / 32 * 32; }
 
 // pair-list capacity per query on average: survivors are about 1.6 k
 inline long long pairs_per_query(int kmax) {
   long long v = 2LL * kmax + 16;
-  return v < 32 ? 32 : (v > WMAX ? WMAX : v);
+  const long long w = wmax_for(kmax);
+  return v < 32 ? 32 : (v > w ? w : v);
 }
 
 enum : int { kFlagCutoff = 1, kFlagOverflow = 2, kFlagModel = 4 };
@@ -66,7 +69,7 @@ size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 Scratch carve(void *ws, int q, int kmax) {
   Scratch s;
   unsigned char *p = static_cast<unsigned char *>(ws);
-  const long long cap = static_cast<long long>(q) * pairs_per_query(kmax) + WMAX;
+  const long long cap = static_cast<long long>(q) * pairs_per_query(kmax) + wmax_for(kmax);
   s.capacity = cap;
   s.counter = reinterpret_cast<unsigned *>(p); p += 256;
   s.q_base = reinterpret_cast<int *>(p); p += up256(sizeof(int) * q);
@@ -80,7 +83,8 @@ Scratch carve(void *ws, int q, int kmax) {
 }
 
 // ------------------------------------------------------------------ select
-__global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankArgs a, const Scratch sc, int lpad) {
+__global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankArgs a, const Scratch sc, int lpad,
+                                                                    int wmax) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   unsigned long long *keys = reinterpret_cast<unsigned long long *>(rr_smem);
   __shared__ int s_nvalid, s_w, s_flag, s_base;
@@ -159,7 +163,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_select_kernel(const RerankA
   __syncthreads();
   if (tid == 0) {
     int w = s_w;
-    if (w > WMAX) { s_flag |= kFlagOverflow; w = WMAX; }
+    if (w > wmax) { s_flag |= kFlagOverflow; w = wmax; }
     long long base = 0;
     if (w > 0) {
       base = atomicAdd(sc.counter, static_cast<unsigned>(w));
@@ -518,14 +522,22 @@ __device__ __forceinline__ void emit_query(const RerankArgs &a, const Scratch &s
 }
 
 
-__global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc) {
-  __shared__ double s_dist[RR_THREADS / 32][WMAX];
-  __shared__ int s_id[RR_THREADS / 32][WMAX];
-  __shared__ int s_fid[RR_THREADS / 32][WMAX];
-  __shared__ int s_flab[RR_THREADS / 32][WMAX];
+// shared memory per warp: wmax distances + wmax ids (the survivors), kmax ids + kmax labels (the ranked list)
+inline size_t emit_smem_per_warp(int wmax, int kmax) {
+  return static_cast<size_t>(wmax) * 12 + (static_cast<size_t>(kmax + 1) / 2 * 2) * 8;
+}
+
+__global__ void __launch_bounds__(RR_THREADS) rerank_emit_kernel(const RerankArgs a, const Scratch sc, int wmax) {
+  extern __shared__ __align__(16) unsigned char rr_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kpad = (a.kmax + 1) / 2 * 2;
+  unsigned char *mine = rr_smem + static_cast<size_t>(warp) * (static_cast<size_t>(wmax) * 12 + static_cast<size_t>(kpad) * 8);
+  double *s_dist = reinterpret_cast<double *>(mine);
+  int *s_id = reinterpret_cast<int *>(mine + static_cast<size_t>(wmax) * 8);
+  int *s_fid = s_id + wmax;
+  int *s_flab = s_fid + kpad;
   const int q = blockIdx.x * (RR_THREADS / 32) + warp;
-  if (q < a.q) emit_query(a, sc, q, lane, s_dist[warp], s_id[warp], s_fid[warp], s_flab[warp]);
+  if (q < a.q) emit_query(a, sc, q, lane, s_dist, s_id, s_fid, s_flab);
   signal_peers_when_grid_done(a.signal);  // (K5) all of this rank's lists have been stored
 }
 
@@ -537,7 +549,7 @@ void set_rerank_debug_w(int *w_out) { g_debug_w = w_out; }
 
 size_t rerank_workspace_bytes(int q, int kmax) {
   if (q < 1) q = 1;
-  const size_t cap = static_cast<size_t>(q) * pairs_per_query(kmax) + WMAX;
+  const size_t cap = static_cast<size_t>(q) * pairs_per_query(kmax) + wmax_for(kmax);
   return 256 + 2 * up256(sizeof(int) * q) + up256(sizeof(QMeta) * q) + 2 * up256(sizeof(int) * cap) +
          up256(sizeof(float) * cap) + up256(sizeof(double) * cap);
 }
@@ -558,7 +570,8 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
   while (lpad < L) lpad <<= 1;
   const size_t smem = static_cast<size_t>(lpad) * 8;
   DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  rerank_select_kernel<<<args.q, RR_THREADS, smem, s>>>(args, sc, lpad);
+  const int wmax = wmax_for(args.kmax);
+  rerank_select_kernel<<<args.q, RR_THREADS, smem, s>>>(args, sc, lpad, wmax);
   DMLP_CUDA_OK(cudaGetLastError());
   // one warp per 32 pairs; sized for the worst case, surplus warps exit at once
   const unsigned blocks = static_cast<unsigned>((sc.capacity + 32 * X_WARPS - 1) / (32 * X_WARPS));
@@ -589,7 +602,10 @@ int launch_rerank(const RerankArgs &args_in, cudaStream_t s) {
     rerank_exact_kernel<false><<<blocks, X_WARPS * 32, X_SMEM, s>>>(args, sc);
   }
   DMLP_CUDA_OK(cudaGetLastError());
-  rerank_emit_kernel<<<(args.q + RR_THREADS / 32 - 1) / (RR_THREADS / 32), RR_THREADS, 0, s>>>(args, sc);
+  const size_t emit_smem = (RR_THREADS / 32) * emit_smem_per_warp(wmax, args.kmax);
+  DMLP_REQUIRE(emit_smem <= 227 * 1024, "rerank: kmax too large for the emit kernel's shared memory");
+  DMLP_CUDA_OK(cudaFuncSetAttribute(rerank_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(emit_smem)));
+  rerank_emit_kernel<<<(args.q + RR_THREADS / 32 - 1) / (RR_THREADS / 32), RR_THREADS, emit_smem, s>>>(args, sc, wmax);
   DMLP_CUDA_OK(cudaGetLastError());
   return 0;
 }

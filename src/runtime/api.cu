@@ -159,6 +159,18 @@ int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[
   return 0;
 }
 
+int dmlp_fused_supported(int kmax, int64_t n) {
+  if (kmax < 1 || n < 1) return 0;
+  if (kmax <= 96) return 2;
+  if (kmax > 1024) return 0;
+  // beyond 96: one 32-key list per 8 of k and a list needs a data tile (256 rows) of its own; a
+  // launch has at most 32 lists, so beyond k = 256 the filter runs as several launches over row
+  // ranges of at least 32 tiles each (make_topk_plan) -- all in all n >= about 32 k
+  const int64_t n_tiles = (n + 255) / 256;
+  const int c_need = (kmax + 7) / 8, parts = (c_need + 31) / 32;
+  return (parts > 1 ? n_tiles >= 32LL * parts : n_tiles >= c_need) ? 1 : 0;
+}
+
 int dmlp_debug_topk_wide(int q, int n, int a_pad, int num_sms, int kmax) {
   return make_topk_plan(q, n, a_pad, 32, num_sms, kmax).wide;
 }

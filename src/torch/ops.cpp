@@ -26,7 +26,6 @@ namespace {
 
 using at::Tensor;
 
-constexpr int64_t kFusedMaxK = 96;      // keep in sync with ops/cuda.py FUSED_MAX_K
 
 void ok(int rc, const char *what) { TORCH_CHECK(rc == 0, what, ": ", dmlp_last_error()); }
 
@@ -55,7 +54,8 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> knn_local(const Tensor &queri
   const int64_t q = queries.size(0), a = queries.size(1), n = data.size(0);
   TORCH_CHECK(data.size(1) == a, "queries have ", a, " attributes, data has ", data.size(1));
   TORCH_CHECK(k.size(0) == q && labels.size(0) == n, "k / labels length does not match the row count");
-  TORCH_CHECK(kmax >= 1 && kmax <= kFusedMaxK, "knn_local supports 1 <= kmax <= ", kFusedMaxK, ", got ", kmax);
+  TORCH_CHECK(kmax >= 1 && (n == 0 || dmlp_fused_supported(int(kmax), n) >= 1),
+              "knn_local supports kmax <= 96, or kmax <= 1024 with n >= 32 kmax; got kmax = ", kmax, ", n = ", n);
   c10::cuda::CUDAGuard guard(queries.device());
   auto stream = at::cuda::getCurrentCUDAStream();
   const auto f64 = queries.options(), i32 = k.options();
@@ -141,7 +141,7 @@ std::tuple<Tensor, Tensor> classify(const Tensor &data, const Tensor &labels, co
                                     int64_t kmax, int64_t id_base) {
   TORCH_CHECK(kmax >= 1, "classify needs kmax >= 1");
   const int64_t q = queries.size(0), n = data.size(0), a = queries.dim() == 2 ? queries.size(1) : 0;
-  const bool fused = kmax <= kFusedMaxK && n > 0 && q > 0 &&
+  const bool fused = n > 0 && q > 0 && dmlp_fused_supported(int(kmax), n) >= 1 &&
                      double(n) * double(q) * double(std::max<int64_t>(a, 1)) >= double(1 << 22);
   Tensor od, oi, ol;
   if (fused) {

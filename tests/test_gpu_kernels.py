@@ -204,6 +204,48 @@ def test_knn_local_matches_oracle(K, n, q, a, kmin, kmax, lo, hi):
         assert (got_dist[i, :k[i]] == want_dist[off[i]:off[i + 1]]).all()   # bit-identical fp64
 
 
+@pytest.mark.parametrize("n,q,a,kmin,kmax", [(12000, 130, 24, 97, 128), (40000, 300, 32, 200, 300),
+                                             (40000, 140, 16, 900, 1024), (70000, 260, 64, 1, 600)])
+def test_fused_path_large_k_matches_oracle(K, n, q, a, kmin, kmax):
+    """96 < k <= 1024 on the filter + certified re-rank path: one 32-key list per 8 of k, so k > 256
+    runs the filter as several launches over row ranges of the data (plan `parts`); the re-rank
+    keeps about 2 k survivors per query.  Bit-identical lists, no query left to the direct path."""
+    import time
+    assert K.fused_supported(kmax, n) and not K.fused_supported(kmax, n, gather=True)
+    assert not K.fused_supported(1025, 10 ** 7) and not K.fused_supported(1024, 32512) and K.fused_supported(1024, 32513)
+    assert not K.fused_supported(300, 16128) and K.fused_supported(300, 16129) and not K.fused_supported(128, 3840)
+    data, labels, queries, k = cpu.synth(n, q, a, -100.0, 100.0, kmin, kmax, 7, seed=17)
+    want_label, want_sum, want_ids, want_dist, off = cpu.knn(data, labels, queries, k)
+    plan = K.topk_plan(q, n, K.pad64(a), kmax=kmax)
+    assert plan["chunks"] * 8 >= kmax
+    qd, kd, xd, ld = _dev(queries), _dev(k), _dev(data), _dev(labels)
+    K.knn_local(qd, kd, xd, ld, kmax)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    od, oi, ol, flags, nflag = K.knn_local(qd, kd, xd, ld, kmax)
+    label, checksum, ids, dist = K.finalize(od[None], oi[None], ol[None], kd, True)
+    torch.cuda.synchronize()
+    print(f"fused n={n} q={q} a={a} k<={kmax}: {(time.perf_counter() - t0) * 1e3:.2f} ms, lists {plan['chunks']}")
+    assert int(nflag.item()) == 0, f"filter failed to certify {int(nflag.item())} queries"
+    assert (checksum.cpu().numpy().view(np.uint64) == want_sum).all()
+    assert (label.cpu().numpy() == want_label).all()
+    got_ids, got_dist = ids.cpu().numpy(), dist.cpu().numpy()
+    for i in range(q):
+        assert (got_ids[i, :k[i]] == want_ids[off[i]:off[i + 1]]).all()
+        assert (got_dist[i, :k[i]] == want_dist[off[i]:off[i + 1]]).all()   # bit-identical fp64
+
+
+def test_classifier_takes_fused_path_for_large_k(K):
+    from dmlp_b200.models import KNNClassifier, choose_path
+    assert choose_path(40000, 500, 32, 1000) == "fused" and choose_path(20000, 500, 32, 1000) == "exact"
+    assert choose_path(40000, 500, 32, 1025) == "exact"
+    data, labels, queries, k = cpu.synth(40000, 150, 20, -100.0, 100.0, 300, 1000, 4, seed=19)
+    _, want_sum, *_ = cpu.knn(data, labels, queries, k)
+    res = KNNClassifier().fit(data, labels).classify(queries, k)
+    assert res.path.startswith("fused"), res.path
+    assert (res.checksums_u64() == want_sum).all()
+
+
 @pytest.mark.parametrize("n,q,a,kmin,kmax", [(1000, 50, 5, 1, 70), (37, 20, 3, 37, 37), (5000, 33, 16, 100, 300)])
 def test_exact_path_matches_oracle(K, n, q, a, kmin, kmax):
     data, labels, queries, k = cpu.synth(n, q, a, -5.0, 5.0, kmin, kmax, 3, seed=21)

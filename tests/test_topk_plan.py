@@ -160,3 +160,21 @@ def test_random_shapes_cover_the_work_exactly_once():
         for members in groups.values():
             cls = [c for c, _ in members]
             assert len(set(cls)) == len(cls) and all(r == len(members) for _, r in members), (q, n, a_pad, kmax, sms)
+
+
+@pytest.mark.parametrize("q,n,a_pad,kmax,parts", [(65536, 65536, 8192, 1024, 4), (600, 40000, 64, 300, 2),
+                                                  (600, 20000, 64, 300, 2), (600, 12000, 64, 128, 1),
+                                                  (600, 70000, 64, 600, 3)])
+def test_large_k_plans_split_the_data_into_parts(q, n, a_pad, kmax, parts):
+    """k > 256: the filter runs as `parts` launches over row ranges of the data, every range with
+    the same number of lists; in total at least one 32-key list per 8 of k."""
+    lib = _lib()
+    lib.dmlp_fused_supported.argtypes = [C.c_int, C.c_int64]
+    assert lib.dmlp_fused_supported(kmax, n) == 1
+    assert lib.dmlp_fused_supported(kmax, 24 * kmax) == 0 and lib.dmlp_fused_supported(96, 1) == 2
+    assert lib.dmlp_fused_supported(1024, 32512) == 0 and lib.dmlp_fused_supported(1024, 32513) == 1
+    arr = (C.c_int * 8)()
+    assert lib.dmlp_topk_plan(q, n, a_pad, SMS, kmax, C.byref(arr)) == 0
+    chunks = arr[3]
+    assert chunks % parts == 0 and chunks * 8 >= kmax and chunks // parts <= 32
+    assert arr[1] == -(-n // 256) and arr[5] <= SMS
