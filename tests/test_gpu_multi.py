@@ -35,7 +35,7 @@ for wire in ("auto", "fp64"):
         lab, chk = eng.run_from_host()
         assert (chk.numpy() == ref_chk).all(), (wire, step)
 assert eng.check_watchdog() == 0
-print(json.dumps({"rank": rank, "checked": checked, "flagged": eng.last_flagged, "peer_fused": bool(getattr(eng, "peer_fused", False))}))
+print(json.dumps({"rank": rank, "checked": checked, "flagged": eng.last_flagged, "peer_fused": bool(getattr(eng, "peer_fused", False)), "fused_ok": bool(eng.fused_ok), "rows_fused": bool(eng.rows_fused)}))
 eng.close()
 dist.destroy_process_group()
 '''
@@ -95,6 +95,11 @@ def test_distributed_large_k(tmp_path, repo_root):
     assert out.count('"checked"') == world and '"peer_fused": true' in out
     out = _run(tmp_path, repo_root, world, "fused", 2000, 300, 16, 100, 120, f"{world}x1")
     assert out.count('"checked"') == world and '"peer_fused": false' in out
+    # 96 < k <= 1024 with queries sharded (1 x C): the filter path in several launches over the shard,
+    # which the peer_gather kernel assembles first (the in-kernel gathers need a single launch)
+    out = _run(tmp_path, repo_root, world, "fused", 40000, 600, 32, 200, 300, f"1x{world}")
+    assert out.count('"checked"') == world and out.count('"fused_ok": true') == world
+    assert '"rows_fused": true' not in out
 
 
 def test_engine_binary_device_grids(tmp_path, repo_root):
