@@ -66,11 +66,17 @@ int dmlp_unpack_bits(const uint32_t *src, int64_t rows, int a, int bits, int wor
 int dmlp_fused_supported(int kmax, int64_t n);
 
 /* ---- K1 + K3 dist_topk (reference: engine.cpp:235-256) ------------------------
- * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  The
- * candidate buffer holds q * chunks * kp 64-bit keys.  kmax = the largest k any query
- * asks for (0 = unknown): every chunk keeps at most 32 candidates per query, so larger k
- * is given more chunks.  See dmlp_fused_supported for the k the fused path takes. */
+ * plan_out: {m_blocks, n_tiles, group_m, chunks, k_blocks, grid, kp, cluster}.  `chunks`
+ * is the number of candidate lists per query: the candidate buffer holds q * chunks * kp
+ * 64-bit keys.  kmax = the largest k any query asks for (0 = unknown): every list keeps at
+ * most 32 candidates per query, so larger k is given more lists.  See dmlp_fused_supported
+ * for the k the fused path takes.
+ * dmlp_topk_plan_ex adds {halves, parts, column chunks per launch, wide, lists per part,
+ * re-alignment period, dynamic scheduling (-1 = where there is no re-alignment), 0}: lists =
+ * column chunks x halves (two sets of epilogue warps on short rows) x parts (launches over row
+ * ranges of the data, k > 256). */
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[8]);
+int dmlp_topk_plan_ex(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[16]);
 int dmlp_dist_topk(const void *q_fp16, const void *x_fp16, const float *x_norm2, int q, int n, int a_pad,
                    int num_sms, int kmax, uint64_t *cand, void *stream);
 

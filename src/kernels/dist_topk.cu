@@ -176,18 +176,21 @@ __device__ __forceinline__ void compact_row(uint32_t row_addr, int rot, int r, i
 
 // Smem layout.  `STG` pipeline stages of (query tile, data tile[ half]) precede the
 // per-row candidate lists, the staged data norms and the barriers.
-template <int STG, int B_STAGE_BYTES>
+template <int STG, int B_STAGE_BYTES, int LISTS = 1>
 struct Layout {
   static constexpr int kOffA = 0;
   static constexpr int kOffB = kOffA + STG * A_BYTES;
   static constexpr int kOffList = kOffB + STG * B_STAGE_BYTES;
-  static constexpr int kOffXn = kOffList + BM * CAP * 8;
+  static constexpr int kOffXn = kOffList + LISTS * BM * CAP * 8;
   static constexpr int kOffBar = kOffXn + 2 * BN * 4;
   static constexpr int kBytes = kOffBar + 256 + 1024;  // + alignment slack
 };
 using Layout1 = Layout<STAGES, B_BYTES>;            // one CTA per 128 x 256 tile
 constexpr int STAGES2 = 4;
 using Layout2 = Layout<STAGES2, B_BYTES / 2>;       // CTA pair per 256 x 256 tile
+// short rows: the pair kernel with two sets of epilogue warps and row lists; a stage is a whole
+// tile there (one or two k-blocks) and the epilogue is what the tile waits for, so two stages do
+using Layout3 = Layout<2, B_BYTES / 2, 2>;
 
 __device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
   unsigned v;
@@ -206,14 +209,19 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
                                               uint32_t tmem_base, uint64_t *tfull_bar, uint64_t *tempty_bar,
                                               int cluster_id, int num_clusters, int cta_rank, int total_items,
                                               const float *__restrict__ xnorm2,
-                                              unsigned long long *__restrict__ cand) {
+                                              unsigned long long *__restrict__ cand, int half = 0, int nhalves = 1) {
+  // `half` of `nhalves`: with two sets of epilogue warps (short rows) set h scans columns
+  // [h * 128, h * 128 + 128) of every tile into its own row lists (`off_list` is the set's) and
+  // emits list 2 * chunk + h; the staging of the data norms is shared by all epilogue threads
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quarter = warp & 3;              // tensor-memory lane quarter this warp may read
   const int row_in_tile = quarter * 32 + lane;
   const uint32_t lists_addr = smem_u32(smem + off_list);  // [BM][CAP] keys, shared-space address
   const uint32_t keys_base = lists_addr + row_in_tile * CAP * 8;  // this row's list, shared-space address
   float *xn_all = reinterpret_cast<float *>(smem + off_xn);
-  const int e_tid = threadIdx.x - 64;
+  const int e_tid = half == 0 ? threadIdx.x - 64 : threadIdx.x - 96;   // (warp 6 is the communication warp)
+  const int epi_threads = EPI_THREADS * nhalves;
+  const int col_begin = half * (BN / nhalves), col_end = col_begin + BN / nhalves;
   const float inf = std::numeric_limits<float>::infinity();
   int cnt = 0;
   float tau = inf;
@@ -249,13 +257,13 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
           while (static_cast<int>(ld_acquire_gpu_u32(plan.gate_cnt + tile) - target) < 0)
             if (clock64() - t0 > 4000000000LL) break;   // the producer's own watchdog reports a lost peer
         }
-        named_barrier_sync(1, EPI_THREADS);
+        named_barrier_sync(1, epi_threads);
       }
-      for (int i = e_tid; i < BN; i += EPI_THREADS) {
+      for (int i = e_tid; i < BN; i += epi_threads) {
         const int col = tile * BN + i;
         xn[i] = col < plan.n ? __ldcg(xnorm2 + col) : inf;
       }
-      named_barrier_sync(1, EPI_THREADS);
+      named_barrier_sync(1, epi_threads);
       const long long pw0 = prof ? clock64() : 0;
       if (prof) prof_stage += pw0 - ps0;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -266,7 +274,7 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
       // the scoring of the current ones measured 25-80 % slower, for the MMA as well)
       const uint32_t xn_addr = smem_u32(xn);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = col_begin; c0 < col_end; c0 += 32) {
         uint32_t v[32];
         float x[32];
         const long long pl0 = prof ? clock64() : 0;
@@ -310,20 +318,31 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
             }
             if (prof) pc_blk += clock64() - pc0;
           }
-          // branch-free appends: every lane runs the same 8 predicated stores
+          // Branch-free appends: every lane runs the same 8 predicated stores.  The slot of
+          // store j is the list's fill plus the hits before j -- a small adder tree, so that the
+          // eight address computations and stores are independent of each other (a running
+          // `cnt += hit` chained them: ~200 cycles of latency per octet, for the whole warp, and
+          // with short rows about every second octet has a hit in one of its 32 rows).
+          // Hits count in units of 8 (bytes per key); a row's list is 512-byte aligned.
+          int h[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) h[j] = sc[j] < tau ? 8 : 0;
+          const int p2 = h[0] + h[1], p4 = p2 + (h[2] + h[3]), p6 = p4 + (h[4] + h[5]);
+          const int pre[8] = {0, h[0], p2, p2 + h[2], p4, p4 + h[4], p6, p6 + h[6]};
+          const int s8 = (cnt + row_in_tile) << 3;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const uint32_t addr = keys_base + (((cnt + row_in_tile) & (CAP - 1)) << 3);
-            const uint32_t ob = float_to_ordered(sc[j]);
-            const int hit = sc[j] < tau;
+            const uint32_t addr = keys_base | (static_cast<uint32_t>(s8 + pre[j]) & ((CAP - 1) << 3));
+            const uint32_t b = __float_as_uint(sc[j]);
+            const uint32_t ob = b ^ (static_cast<uint32_t>(static_cast<int>(b) >> 31) | 0x80000000u);  // float_to_ordered
             asm volatile(
                 "{\n\t.reg .pred p;\n\t"
-                "setp.ne.s32 p, %0, 0;\n\t"
-                "@p st.shared.v2.b32 [%1], {%2, %3};\n\t}" ::"r"(hit),
-                "r"(addr), "r"(id0 + 8 * o + j), "r"(ob)
+                "setp.lt.f32 p, %0, %1;\n\t"
+                "@p st.shared.v2.b32 [%2], {%3, %4};\n\t}" ::"f"(sc[j]),
+                "f"(tau), "r"(addr), "r"(id0 + 8 * o + j), "r"(ob)
                 : "memory");
-            cnt += hit;
           }
+          cnt += (p6 + (h[6] + h[7])) >> 3;
         }
         if (prof) {
           prof_compact += pc_blk;
@@ -343,7 +362,8 @@ __device__ __forceinline__ void epilogue_loop(const TopkPlan &plan, uint8_t *sme
     for (int r = 0; r < 32; ++r) {
       const long long qrow = static_cast<long long>(it.m) * BM + quarter * 32 + r;
       unsigned long long *out =
-          qrow < plan.q_rows ? cand + (qrow * plan.cand_chunks + plan.chunk_base + it.chunk) * KP : nullptr;
+          qrow < plan.q_rows ? cand + (qrow * plan.cand_chunks + plan.chunk_base + it.chunk * nhalves + half) * KP
+                             : nullptr;
       compact_row(lists_addr + (quarter * 32 + r) * CAP * 8, quarter * 32 + r, r, lane, cnt, tau, out);
     }
     cnt = 0;
@@ -527,6 +547,7 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
 }
 
 constexpr int THREADS2 = THREADS + 32;  // + one communication warp
+constexpr int THREADS3 = THREADS2 + EPI_THREADS;  // + a second set of epilogue warps (short rows, MODE 3)
 
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
   unsigned v;
@@ -754,7 +775,7 @@ __device__ __forceinline__ int skew_first_tile(int s, int K, int H) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(THREADS2, 1)
+__global__ void __launch_bounds__(MODE == 3 ? THREADS3 : THREADS2, 1)
 dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_x,
                       const float *__restrict__ xnorm2, const TopkPlan plan,
                       unsigned long long *__restrict__ cand, const GatherArgs ga, const DataGatherArgs dg) {
@@ -768,12 +789,18 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   // cyclically from wherever the (continuous) query stream is when it starts, and a tile's
   // accumulator rests for `gap` steps -- while the other one keeps the MMA busy -- before its
   // next tile begins.  The query tile of a step is still shared by both active data tiles.
-  constexpr bool WIDE = MODE >= 1;
+  // HALVES (MODE 3, short rows): the narrow tile with a second set of four epilogue warps.  With one
+  // or two k-blocks per tile the kernel is bound by the epilogue (the MMA waits for a free
+  // accumulator 90 % of the time at A = 64, profiles/topk_prof_short_r2.log), and a warp can only
+  // read its own TMEM lane quarter -- so the second set shares the rows and takes the other 128
+  // columns of every tile, with row lists of its own (two lists per query and chunk).
+  constexpr bool WIDE = MODE == 1 || MODE == 2;
   constexpr bool SKEW = MODE == 2;
-  constexpr int NST = WIDE ? STAGES : STAGES2;
+  constexpr bool HALVES = MODE == 3;
+  constexpr int NST = WIDE ? STAGES : (HALVES ? 2 : STAGES2);
   constexpr int BH_BYTES = B_BYTES / 2;  // this CTA's half of one data tile
   constexpr int BS_BYTES = WIDE ? B_BYTES : BH_BYTES;  // data bytes per stage
-  using L = Layout<NST, BS_BYTES>;
+  using L = Layout<NST, BS_BYTES, HALVES ? 2 : 1>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kOffBar);
@@ -801,7 +828,7 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       }
       for (int s = 0; s < 2; ++s) {
         mbar_init(&tfull_bar[s], 1);
-        mbar_init(&tempty_bar[s], 8);  // 4 epilogue warps in each CTA of the pair
+        mbar_init(&tempty_bar[s], HALVES ? 16 : 8);  // 4 (or 8) epilogue warps in each CTA of the pair
       }
       fence_barrier_init();
     }
@@ -1079,12 +1106,14 @@ dist_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     if (ga.world > 1) gather_warp(plan, ga, lane);
     if (dg.world > 1) data_gather_warp(plan, dg, lane);
   } else {
+    const int half = HALVES && warp > 6 ? 1 : 0;
+    const int off_list = L::kOffList + half * BM * CAP * 8;
     if (cta_rank == 0)
-      epilogue_loop<false>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
-                           num_clusters, cta_rank, total_items, xnorm2, cand);
+      epilogue_loop<false>(plan, smem, off_list, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
+                           num_clusters, cta_rank, total_items, xnorm2, cand, half, HALVES ? 2 : 1);
     else
-      epilogue_loop<true>(plan, smem, L::kOffList, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
-                          num_clusters, cta_rank, total_items, xnorm2, cand);
+      epilogue_loop<true>(plan, smem, off_list, L::kOffXn, tmem_base, tfull_bar, tempty_bar, cluster_id,
+                          num_clusters, cta_rank, total_items, xnorm2, cand, half, HALVES ? 2 : 1);
   }
 
   tc_fence_before();
@@ -1133,6 +1162,23 @@ int make_fp16_tile_map(CUtensorMap *map, const __half *base, long long rows, int
 
 namespace {
 TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax);
+
+// Sets of epilogue warps (= lists per query and column chunk).  Short rows -- one or two k-blocks
+// per tile -- are bound by the epilogue, so the CTA-pair kernel runs two sets there (MODE 3).
+int plan_halves(int q_rows, int a_pad) {
+  bool pair = (q_rows + BM - 1) / BM >= 2;
+  if (const char *e = getenv("DMLP_TOPK_PAIR")) pair = pair && atoi(e) != 0;
+  bool wide = a_pad / BK >= 64;
+  if (const char *e = getenv("DMLP_TOPK_WIDE")) wide = atoi(e) != 0;
+  // Measured on B200 (70000 x 200000, profiles/ab_append_r2.jsonl): A = 64 15.0 ms with two sets against
+  // 16.1 with one; A = 512 9.9 against 8.6, A = 1024 17.7 against 14.3.  The gain is small because the
+  // epilogue's time is mostly in the appends, and two half-width lists per row take 1.8 x the appends
+  // of one (every list warms its threshold up by itself); with more than one k-block per tile the
+  // two-stage ring of this mode costs more than the second set returns.  So: one k-block only.
+  int halves = a_pad / BK <= 1 ? 2 : 1;
+  if (const char *e = getenv("DMLP_TOPK_HALVES")) halves = atoi(e) == 2 ? 2 : 1;
+  return (pair && !wide) ? halves : 1;
+}
 }
 
 // Large k: every (query, chunk) list keeps 32 keys and the certified filter wants one list per 8 of
@@ -1142,8 +1188,9 @@ TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int
 // the shared candidate buffer.  Needs n >= 8192 * parts (about 32 k); below that the caller's exact
 // path is the better tool anyway (k is then more than 3 % of the data).
 TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int kmax) {
-  const int c_need = (kmax + 7) / 8;
-  const int parts = (c_need + 31) / 32;
+  const int c_need = (kmax + 7) / 8;   // lists
+  const int per_launch = 32 * plan_halves(q_rows, a_pad);
+  const int parts = (c_need + per_launch - 1) / per_launch;
   const int n_tiles = (n + BN - 1) / BN;
   if (parts > 1 && n_tiles >= 32 * parts) {
     const int part_kmax = (kmax + parts - 1) / parts;
@@ -1152,10 +1199,10 @@ TopkPlan make_topk_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int k
     p.n = n;
     p.n_tiles = n_tiles;
     p.parts = parts;
-    p.part_chunks = p.chunks;
+    p.part_chunks = p.lists;
     p.part_kmax = part_kmax;
-    p.chunks = parts * p.part_chunks;
-    p.cand_chunks = p.chunks;
+    p.lists = parts * p.part_chunks;
+    p.cand_chunks = p.lists;
     return p;
   }
   return make_single_plan(q_rows, n, a_pad, kp, num_sms, kmax);
@@ -1248,7 +1295,9 @@ TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int
   long long budget = budget_mb << 20;
   // the certified survivor set is about 1.6 k per query, spread over the chunks, and a
   // chunk can contribute at most 32: one chunk per 8 of k keeps every list far from full
-  int c_min = 2 > (kmax + 7) / 8 ? 2 : (kmax + 7) / 8;
+  p.halves = plan_halves(q_rows, a_pad);
+  const int c_need = ((kmax + 7) / 8 + p.halves - 1) / p.halves;
+  int c_min = 2 > c_need ? 2 : c_need;
   if (c_min > p.n_tiles) c_min = p.n_tiles > 0 ? p.n_tiles : 1;
   int c_max = p.n_tiles < 32 ? (p.n_tiles > 0 ? p.n_tiles : 1) : 32;
   if (c_max > nclusters) c_max = nclusters;
@@ -1281,7 +1330,11 @@ TopkPlan make_single_plan(int q_rows, int n, int a_pad, int kp, int num_sms, int
   // one wave = one whole group (gmc x c clusters), so that clusters sharing a chunk run side by side
   if (p.pair && static_cast<long long>(gmc) * c <= use) use = gmc * c;
   p.grid = use * cluster;
-  p.part_chunks = p.chunks;
+  // short rows (one or two k-blocks per tile) are bound by the epilogue: two sets of epilogue warps
+  if (!p.pair || p.wide) p.halves = 1;
+  p.lists = p.chunks * p.halves;
+  p.cand_chunks = p.lists;
+  p.part_chunks = p.lists;
   return p;
 }
 }  // namespace
@@ -1349,7 +1402,7 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
       const int t1 = static_cast<int>(static_cast<long long>(p + 1) * plan.n_tiles / plan.parts);
       const int r0 = t0 * BN, r1 = t1 * BN < plan.n ? t1 * BN : plan.n;
       TopkPlan sub = make_single_plan(plan.q_rows, r1 - r0, plan.a_pad, plan.kp, plan.num_sms, plan.part_kmax);
-      DMLP_REQUIRE(sub.chunks == plan.part_chunks, "dist_topk: the parts of a large-k launch must agree on their chunk count");
+      DMLP_REQUIRE(sub.lists == plan.part_chunks, "dist_topk: the parts of a large-k launch must agree on their list count");
       sub.cand_chunks = plan.cand_chunks;
       sub.chunk_base = plan.chunk_base + p * plan.part_chunks;
       sub.row_base = plan.row_base + r0;
@@ -1432,9 +1485,14 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   if (int rc = make_fp16_tile_map(&tm_q, qh, plan.q_rows, plan.a_pad, BM)) return rc;
   if (int rc = make_fp16_tile_map(&tm_x, xh, plan.n, plan.a_pad, plan.pair ? BN / 2 : BN / plan.cluster)) return rc;
   if (!plan.pair) plan.wide = 0;
-  const int smem_bytes = plan.pair ? (plan.wide ? Layout1::kBytes : Layout2::kBytes) : Layout1::kBytes;
+  if (!plan.pair || plan.wide) plan.halves = 1;
+  const bool halves = plan.halves == 2;
+  const int smem_bytes =
+      plan.pair ? (plan.wide ? Layout1::kBytes : (halves ? Layout3::kBytes : Layout2::kBytes)) : Layout1::kBytes;
   if (!plan.wide) plan.gap = -1;
-  if (plan.pair && plan.wide && plan.gap >= 0)
+  if (halves)
+    DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  else if (plan.pair && plan.wide && plan.gap >= 0)
     DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   else if (plan.pair && plan.wide)
     DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
@@ -1444,7 +1502,7 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
     DMLP_CUDA_OK(cudaFuncSetAttribute(dist_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(plan.grid);
-  cfg.blockDim = dim3(plan.pair ? THREADS2 : THREADS);
+  cfg.blockDim = dim3(plan.pair ? (halves ? THREADS3 : THREADS2) : THREADS);
   cfg.dynamicSmemBytes = smem_bytes;
   GatherArgs ga;
   if (gather != nullptr) ga = *gather;
@@ -1464,7 +1522,9 @@ int launch_dist_topk(const __half *qh, const __half *xh, const float *xnorm2, co
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (plan.pair && plan.wide && plan.gap >= 0)
+  if (halves)
+    DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<3>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
+  else if (plan.pair && plan.wide && plan.gap >= 0)
     DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<2>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));
   else if (plan.pair && plan.wide)
     DMLP_CUDA_OK(cudaLaunchKernelEx(&cfg, dist_topk_pair_kernel<1>, tm_q, tm_x, xnorm2, plan, cand, ga, dg));

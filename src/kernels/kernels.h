@@ -68,8 +68,10 @@ struct TopkPlan {
   const unsigned *gate_cnt;  ///< set when the data rows are gathered from peers by the kernel itself: per-tile arrival counters the epilogue checks before it stages a tile's norms
   unsigned gate_epoch;
   int gap;         ///< wide only: >= 0 = skewed schedule, steps an accumulator rests between tiles; -1 = lock-step wide tile
+  int halves;      ///< 2 (short rows, pair kernel): two epilogue warps per TMEM lane quarter, each scanning half of a tile's columns into a list of its own -- every (query, chunk) then yields two lists
+  int lists;       ///< lists per query this plan writes (chunks * halves, times parts): what the candidate buffer and the re-rank are sized for
   int parts;       ///< > 1 (large k): the launch is split into `parts` launches over row ranges of the data, each writing `part_chunks` of the `chunks` lists -- a list keeps 32 keys, so k up to 1024 needs up to 128 lists per query
-  int part_chunks; ///< lists per part (= chunks when parts == 1)
+  int part_chunks; ///< lists per part (= lists when parts == 1)
   int part_kmax;   ///< the kmax each part is planned for
   int num_sms;     ///< what the plan was made for (the parts are planned at launch)
   int dyn;         ///< clusters take items from an atomic counter instead of the static round-robin: 1 always (switches the re-alignment off), 0 never, -1 (default) where the launch has no re-alignment anyway; single-GPU launches only (DMLP_TOPK_DYN)

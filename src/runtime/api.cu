@@ -154,7 +154,7 @@ int dmlp_stats_set(void *stats, double lo, double hi, void *stream) {
 
 int dmlp_topk_plan(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[8]) {
   TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
-  plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.chunks;
+  plan_out[0] = p.m_blocks; plan_out[1] = p.n_tiles; plan_out[2] = p.group_m; plan_out[3] = p.lists;
   plan_out[4] = p.k_blocks; plan_out[5] = p.grid; plan_out[6] = p.kp; plan_out[7] = p.cluster;
   return 0;
 }
@@ -169,6 +169,15 @@ int dmlp_fused_supported(int kmax, int64_t n) {
   const int64_t n_tiles = (n + 255) / 256;
   const int c_need = (kmax + 7) / 8, parts = (c_need + 31) / 32;
   return (parts > 1 ? n_tiles >= 32LL * parts : n_tiles >= c_need) ? 1 : 0;
+}
+
+int dmlp_topk_plan_ex(int q, int n, int a_pad, int num_sms, int kmax, int plan_out[16]) {
+  TopkPlan p = make_topk_plan(q, n, a_pad, 32, num_sms, kmax);
+  for (int i = 0; i < 16; ++i) plan_out[i] = 0;
+  if (int rc = dmlp_topk_plan(q, n, a_pad, num_sms, kmax, plan_out)) return rc;
+  plan_out[8] = p.halves; plan_out[9] = p.parts; plan_out[10] = p.chunks; plan_out[11] = p.wide;
+  plan_out[12] = p.part_chunks; plan_out[13] = p.sync; plan_out[14] = p.dyn;
+  return 0;
 }
 
 int dmlp_debug_topk_wide(int q, int n, int a_pad, int num_sms, int kmax) {
@@ -265,7 +274,7 @@ int dmlp_dist_topk_part(const void *q_fp16, const void *x_fp16_part, const float
   if (num_sms <= 0)
     if (int rc = current_sm_count(&num_sms)) return rc;
   TopkPlan p = make_topk_plan(q, n_part, a_pad, 32, num_sms, kmax);
-  DMLP_REQUIRE(chunk_base >= 0 && chunk_base + p.chunks <= cand_chunks,
+  DMLP_REQUIRE(chunk_base >= 0 && chunk_base + p.lists <= cand_chunks,
                "dist_topk_part: this launch's lists do not fit the candidate buffer");
   p.cand_chunks = cand_chunks;
   p.chunk_base = chunk_base;
@@ -439,7 +448,7 @@ LocalLayout local_layout(int q, int n, int a, int num_sms, int kmax) {
   LocalLayout L;
   L.a_pad = pad64(a > 0 ? a : 1);
   TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, num_sms, kmax);
-  L.chunks = p.chunks;
+  L.chunks = p.lists;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
   L.stats = take(DMLP_STATS_BYTES);
@@ -450,7 +459,7 @@ LocalLayout local_layout(int q, int n, int a, int num_sms, int kmax) {
   L.xe = take(size_t(n) * 4);
   L.qn = take(size_t(q) * 4);
   L.qe = take(size_t(q) * 4);
-  L.cand = take(size_t(q) * p.chunks * 32 * 8);
+  L.cand = take(size_t(q) * p.lists * 32 * 8);
   L.rerank_bytes = rerank_workspace_bytes(q, kmax);
   L.rerank = take(L.rerank_bytes);
   L.total = off;
@@ -505,7 +514,7 @@ int dmlp_knn_local(const double *q_attrs, const int *k, int q, const double *x_a
   TopkPlan p = make_topk_plan(q, n, L.a_pad, 32, sms, kmax);
   if (int rc = launch_dist_topk(qh, xh, xn, p, cand, nullptr, s)) return rc;
   RerankArgs r;
-  r.cand = cand; r.chunks = p.chunks; r.kp = 32;
+  r.cand = cand; r.chunks = p.lists; r.kp = 32;
   r.q_attrs = q_attrs; r.x_attrs = x_attrs; r.x_labels = x_labels; r.k = k;
   r.q_norm2 = qn; r.q_errn = qe; r.range = rng; r.x_maxima = stats;
   r.q = q; r.n = n; r.a = a; r.a_pad = L.a_pad; r.id_base = id_base; r.kmax = kmax;

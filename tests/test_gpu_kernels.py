@@ -107,6 +107,7 @@ def test_dist_topk_wide_tile_equals_narrow(K, q, n, a, chunks, gmc, sync, monkey
         monkeypatch.setenv("DMLP_TOPK_GMC", str(gmc))
     if sync:  # re-alignment of the pairs that sweep a chunk, every `sync` tiles (both kernels)
         monkeypatch.setenv("DMLP_TOPK_SYNC", str(sync))
+    monkeypatch.setenv("DMLP_TOPK_HALVES", "1")   # one list per (query, chunk) in both, like the wide tile
     data, _, queries, _ = cpu.synth(n, q, a, -100.0, 100.0, 1, 1, 2, seed=11)
     x, qq = _dev(data), _dev(queries)
     st = K.new_stats()
@@ -172,6 +173,49 @@ def test_dist_topk_dynamic_schedule_equals_static(K, q, n, a, chunks, gmc, monke
             assert torch.equal(ref, got), wide
 
 
+@pytest.mark.parametrize("q,n,a,chunks,gmc", [(600, 5000, 64, 3, 2), (1000, 9000, 128, 5, 2), (257, 777, 100, 0, 0),
+                                              (5000, 30000, 64, 0, 0), (3000, 2000, 32, 2, 3)])
+def test_dist_topk_two_epilogue_sets_for_short_rows(K, q, n, a, chunks, gmc, monkeypatch):
+    """DMLP_TOPK_HALVES=2 (the default for rows of one k-block): two sets of epilogue warps, each scanning half of a tile's columns
+    into lists of its own.  Every (query, chunk) then yields two lists whose union holds the single
+    list of the one-set kernel; the re-rank must derive identical exact lists from either."""
+    if chunks:
+        monkeypatch.setenv("DMLP_TOPK_CHUNKS", str(chunks))
+        monkeypatch.setenv("DMLP_TOPK_GMC", str(gmc))
+    data, _, queries, _ = cpu.synth(n, q, a, -100.0, 100.0, 1, 1, 2, seed=14)
+    x, qq = _dev(data), _dev(queries)
+    st, qst = K.new_stats(), K.new_stats()
+    K.stats_update(x, st)
+    K.stats_update(qq, st)
+    xh, xn, _ = K.pack(x, st, st)
+    qh, qn, qe = K.pack(qq, st, qst)
+    monkeypatch.setenv("DMLP_TOPK_HALVES", "1")
+    one = K.dist_topk(qh, xh, xn).clone()
+    monkeypatch.setenv("DMLP_TOPK_HALVES", "2")
+    two = K.dist_topk(qh, xh, xn).clone()
+    torch.cuda.synchronize()
+    assert two.shape[1] == 2 * one.shape[1]
+    # a key kept by the one-set kernel is among the 32 best of its chunk, hence of its half
+    a1 = one.cpu().numpy().view(np.uint64)
+    a2 = two.cpu().numpy().view(np.uint64)
+    for row in (0, q // 2, q - 1):
+        for c in range(one.shape[1]):
+            kept = set(a1[row, c].tolist())
+            both = set(a2[row, 2 * c].tolist()) | set(a2[row, 2 * c + 1].tolist())
+            assert kept <= both, (row, c)
+    kk = torch.full((q,), 9, dtype=torch.int32, device="cuda")
+    labels = torch.zeros(n, dtype=torch.int32, device="cuda")
+    ref = None
+    for cand in (one, two):
+        od, oi, ol, flags, nflag = K.rerank(cand, qq, x, labels, kk, qn, qe, st, st, 0, 9)
+        torch.cuda.synchronize()
+        assert int(nflag.item()) == 0
+        if ref is None:
+            ref = (od.clone(), oi.clone())
+        else:
+            assert torch.equal(ref[0], od) and torch.equal(ref[1], oi)
+
+
 def test_knn_local_long_rows_take_the_wide_tile(K):
     # 4096 values per row: the planner picks the wide tile by itself
     n, q, a, kmax = 3000, 520, 4096, 12
@@ -233,6 +277,29 @@ def test_fused_path_large_k_matches_oracle(K, n, q, a, kmin, kmax):
     for i in range(q):
         assert (got_ids[i, :k[i]] == want_ids[off[i]:off[i + 1]]).all()
         assert (got_dist[i, :k[i]] == want_dist[off[i]:off[i + 1]]).all()   # bit-identical fp64
+
+
+def test_engine_binary_large_k_single_gpu(repo_root):
+    """`./engine` on one GPU with k up to 400: the C++ runtime takes the fused path too, output equal to its CPU backend."""
+    import json
+    import os
+    import subprocess
+    exe = os.path.join(repo_root, "engine")
+    if not os.path.exists(exe):
+        pytest.skip("engine not built")
+    args = [exe, "--json", "--synth", "40000", "300", "24", "-100", "100", "200", "400", "5", "9"]
+
+    def run(backend):
+        res = subprocess.run(args, capture_output=True, text=True, timeout=240,
+                             env=dict(os.environ, DMLP_BACKEND=backend, DMLP_NGPU="1"))
+        assert res.returncode == 0, res.stderr[-2000:]
+        info = json.loads([ln for ln in res.stderr.splitlines() if ln.startswith("{")][-1])
+        return sorted(res.stdout.splitlines()), info
+
+    want, _ = run("cpu")
+    got, info = run("gpu")
+    assert "fused" in info["backend"], info
+    assert got == want
 
 
 def test_classifier_takes_fused_path_for_large_k(K):

@@ -22,16 +22,20 @@ def _lib():
     except OSError as e:  # CPU-only build of the repo (make NO_CUDA=1)
         pytest.skip(f"libdmlp_knn.so not built: {e}")
     lib.dmlp_topk_plan.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int * 8)]
+    lib.dmlp_topk_plan_ex.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int * 16)]
     lib.dmlp_debug_topk_items.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_int]
     return lib
 
 
 def plan_and_items(q, n, a_pad, kmax, sms=SMS):
     lib = _lib()
-    arr = (C.c_int * 8)()
-    assert lib.dmlp_topk_plan(q, n, a_pad, sms, kmax, C.byref(arr)) == 0
-    keys = ["m_blocks", "n_tiles", "group_m", "chunks", "k_blocks", "grid", "kp", "cluster"]
+    arr = (C.c_int * 16)()
+    assert lib.dmlp_topk_plan_ex(q, n, a_pad, sms, kmax, C.byref(arr)) == 0
+    keys = ["m_blocks", "n_tiles", "group_m", "lists", "k_blocks", "grid", "kp", "cluster", "halves", "parts",
+            "chunks", "wide"]
     plan = dict(zip(keys, list(arr)))
+    assert plan["lists"] == plan["chunks"] * plan["halves"] * plan["parts"]
+    assert plan["halves"] == (2 if (plan["k_blocks"] == 1 and plan["m_blocks"] >= 2) else 1)
     cap = 1 << 16
     buf = np.zeros((cap, 8), dtype=np.int32)
     cnt = lib.dmlp_debug_topk_items(q, n, a_pad, sms, kmax, buf.ctypes.data, cap)
@@ -162,9 +166,9 @@ def test_random_shapes_cover_the_work_exactly_once():
             assert len(set(cls)) == len(cls) and all(r == len(members) for _, r in members), (q, n, a_pad, kmax, sms)
 
 
-@pytest.mark.parametrize("q,n,a_pad,kmax,parts", [(65536, 65536, 8192, 1024, 4), (600, 40000, 64, 300, 2),
-                                                  (600, 20000, 64, 300, 2), (600, 12000, 64, 128, 1),
-                                                  (600, 70000, 64, 600, 3)])
+@pytest.mark.parametrize("q,n,a_pad,kmax,parts", [(65536, 65536, 8192, 1024, 4), (600, 40000, 256, 300, 2),
+                                                  (600, 20000, 64, 300, 1), (600, 12000, 64, 128, 1),
+                                                  (600, 70000, 512, 600, 3)])
 def test_large_k_plans_split_the_data_into_parts(q, n, a_pad, kmax, parts):
     """k > 256: the filter runs as `parts` launches over row ranges of the data, every range with
     the same number of lists; in total at least one 32-key list per 8 of k."""
@@ -176,5 +180,5 @@ def test_large_k_plans_split_the_data_into_parts(q, n, a_pad, kmax, parts):
     arr = (C.c_int * 8)()
     assert lib.dmlp_topk_plan(q, n, a_pad, SMS, kmax, C.byref(arr)) == 0
     chunks = arr[3]
-    assert chunks % parts == 0 and chunks * 8 >= kmax and chunks // parts <= 32
+    assert chunks % parts == 0 and chunks * 8 >= kmax and chunks // parts <= 64
     assert arr[1] == -(-n // 256) and arr[5] <= SMS
