@@ -438,7 +438,7 @@ struct KdTree {
     int far = diff < 0 ? nd.right : nd.left;
     search(near, q, heap);
     double plane = diff * diff;
-    if (!heap.full() || !(plane > heap.worst().dist)) search(far, q, heap);
+    if (heap.cap > 0 && (!heap.full() || !(plane > heap.worst().dist))) search(far, q, heap);  // (k == 0: nothing to find)
   }
 };
 
@@ -448,6 +448,7 @@ void run_kdtree(const DatasetView &data, const QueryView &qv, ResultSet *out) {
   KdTree tree(data);
   for (int64_t i = 0; i < qv.q; ++i) {
     BoundedHeap heap(lists.data() + off[i], static_cast<int>(off[i + 1] - off[i]));
+    if (heap.cap == 0) { heap.finish(); continue; }
     if (data.a > 0) tree.search(data.n > 0 ? 0 : -1, qv.attrs + i * qv.a, heap);
     else for (int64_t r = 0; r < data.n; ++r)
       heap.offer(Neighbor{0.0, data.id_base + static_cast<int>(r), data.labels[r]});
