@@ -179,7 +179,7 @@ def main():
         te = max_over_ranks(max(e0.elapsed_time(e1) / 1e3, wall))
         e2e = {"value": Q * args.steps / te, "unit": "queries/s",
                "h2d_bytes_per_step": eng.h2d_bytes_per_step * world, "d2h_bytes_per_step": eng.d2h_bytes_per_step * world,
-               "ms_per_step": te * 1e3 / args.steps, "wire": eng.wire,
+               "ms_per_step": te * 1e3 / args.steps, "wire": eng.wire, "wire_bits": int(getattr(eng, "wire_bits", 0)) or 32,
                "input_pipeline": "none" if args.no_prefetch else "next step's copies start during the current step "
                                  "(double-buffered wire buffers); none cross the ends of the timed region"}
         if args.verify > 0:   # the end-to-end answers must be the resident ones
