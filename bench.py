@@ -170,7 +170,7 @@ def main():
             # a serving loop's input pipeline: while a step finishes on the GPU, the copies of the next
             # step's inputs are already on their way (second set of wire buffers).  Nothing is
             # prefetched before the first timed step or after the last one: every timed step's
-            # 4.3 GB cross PCIe inside the timed region.
+            # inputs (h2d_bytes_per_step) cross PCIe inside the timed region.
             res = eng.run_from_host(prefetch_next=(i + 1 < args.steps) and not args.no_prefetch)
         e1.record()
         torch.cuda.synchronize()
@@ -179,7 +179,7 @@ def main():
         te = max_over_ranks(max(e0.elapsed_time(e1) / 1e3, wall))
         e2e = {"value": Q * args.steps / te, "unit": "queries/s",
                "h2d_bytes_per_step": eng.h2d_bytes_per_step * world, "d2h_bytes_per_step": eng.d2h_bytes_per_step * world,
-               "ms_per_step": te * 1e3 / args.steps, "wire": eng.wire, "wire_bits": int(getattr(eng, "wire_bits", 0)) or 32,
+               "ms_per_step": te * 1e3 / args.steps, "wire": eng.wire, "wire_bits": int(getattr(eng, "wire_bits", 0)) or (32 if eng.wire == "decimal6" else 64),
                "input_pipeline": "none" if args.no_prefetch else "next step's copies start during the current step "
                                  "(double-buffered wire buffers); none cross the ends of the timed region"}
         if args.verify > 0:   # the end-to-end answers must be the resident ones
