@@ -131,6 +131,17 @@ def parse_text(text, threads=0):
     return data, labels, queries, k
 
 
+def encode_decimal6(values, threads=0):
+    """Six-decimal values as int32 (value == i / 1e6 exactly), or None when some value is not representable."""
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    out = np.empty(v.shape, np.int32)
+    ok = C.c_int(0)
+    lib = _lib()
+    lib.dmlp_encode_decimal6_host.argtypes = [_d, C.c_int64, C.c_int, _i, C.POINTER(C.c_int)]
+    _check(lib.dmlp_encode_decimal6_host(v.reshape(-1), v.size, threads, out.reshape(-1), C.byref(ok)))
+    return out if ok.value else None
+
+
 def parse_update(line, max_attrs=1 << 16):
     """Parse one update record 'id v0 v1 ...' (reference: common.cpp:46-55).  Returns (id, values)."""
     if isinstance(line, str):

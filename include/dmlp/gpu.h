@@ -25,6 +25,7 @@ struct GpuOptions {
   int rows = 0, cols = 0;  ///< grid: data shards x query shards (0 = rows=ngpu, cols=1)
   bool exact_only = false;  ///< skip the tensor-core filter, brute force in fp64
   bool trace = false;
+  bool wire_i32 = false;    ///< the views carry attrs_i32: move 4 bytes per value to the device and expand there
   bool have_range = false;  ///< range_lo / range_hi bound every attribute value (the loader knows them);
   double range_lo = 0.0, range_hi = 0.0;  ///< otherwise the call scans the inputs on the host first
 };

@@ -50,14 +50,21 @@ class Problem {
   int *data_labels = nullptr;     ///< n
   double *query_attrs = nullptr;  ///< q x a
   int *query_k = nullptr;         ///< q
+  int32_t *data_attrs_i32 = nullptr;   ///< n x a, set by encode_decimal6
+  int32_t *query_attrs_i32 = nullptr;  ///< q x a
+
+  /// The loader's second output: every attribute as the integer i with value == double(i) / 1e6
+  /// (what the text grammar's "%.6f" holds).  Returns false, and keeps no integer form, when some
+  /// value is not such a quotient or does not fit 32 bits.  `threads` <= 0: hardware concurrency.
+  bool encode_decimal6(int threads);
 
   DatasetView dataset() const {
     DatasetView v; v.n = num_data; v.a = num_attrs; v.attrs = data_attrs;
-    v.labels = data_labels; v.id_base = 0; return v;
+    v.labels = data_labels; v.id_base = 0; v.attrs_i32 = data_attrs_i32; return v;
   }
   QueryView queries() const {
     QueryView v; v.q = num_queries; v.a = num_attrs; v.attrs = query_attrs;
-    v.k = query_k; v.id_base = 0; return v;
+    v.k = query_k; v.id_base = 0; v.attrs_i32 = query_attrs_i32; return v;
   }
 
  private:
@@ -110,6 +117,10 @@ inline double synth_attr(uint64_t h, double lo, double hi) {
   long long i = static_cast<long long>(scaled < 0 ? scaled - 0.5 : scaled + 0.5);
   return static_cast<double>(i) / 1e6;
 }
+
+/// values -> integers i with value == double(i) / 1e6 exactly (the six decimals of the text grammar);
+/// false when some value is not such a quotient or does not fit 32 bits (`out` is then undefined).
+bool encode_decimal6_values(const double *values, int64_t count, int threads, int32_t *out);
 
 /// Smallest and largest attribute value over data and queries (threads <= 0: hardware
 /// concurrency); 0, 0 for an empty problem.

@@ -26,6 +26,10 @@ struct DatasetView {
   const double *attrs = nullptr;
   const int *labels = nullptr;
   int id_base = 0;
+  /// Optional: the same values as integers i with attrs[j] == double(i) / 1e6 exactly (the text
+  /// grammar's six decimals, Problem::encode_decimal6).  A GPU backend then moves 4 bytes per
+  /// value over PCIe instead of 8 and rebuilds the doubles bit for bit on the device.
+  const int32_t *attrs_i32 = nullptr;
 };
 
 /// Read-only view of `q` queries.  Global id of row r is `id_base + r`.
@@ -35,6 +39,7 @@ struct QueryView {
   const double *attrs = nullptr;
   const int *k = nullptr;
   int id_base = 0;
+  const int32_t *attrs_i32 = nullptr;  ///< optional decimal6 form, see DatasetView
 };
 
 /// One candidate neighbour.  16 bytes; this is the "wire type" exchanged

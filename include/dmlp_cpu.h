@@ -48,6 +48,11 @@ int dmlp_parse_header(const char *text, size_t len, int64_t *n, int64_t *q, int 
 int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attrs, int *data_labels,
                     double *query_attrs, int *query_k);
 
+/* The loader's integer form of six-decimal inputs: out[i] = values[i] * 1e6 as a 32-bit integer,
+ * *ok = 1 when every value equals double(out[i]) / 1e6 exactly (then a GPU backend can move 4
+ * bytes per value over PCIe and rebuild the doubles bit for bit), 0 otherwise. */
+int dmlp_encode_decimal6_host(const double *values, int64_t count, int threads, int32_t *out, int *ok);
+
 /* One update record "id v0 v1 ..." (reference: parse_update, common.cpp:46-55; unused by its
  * engine).  *count receives the number of values found; at most `capacity` are stored. */
 int dmlp_parse_update(const char *text, size_t len, int *id, double *attrs, int capacity, int *count);

@@ -43,6 +43,9 @@ struct EngineConfig {
   /// scan of the inputs inside the call).
   bool have_range = false;
   double range_lo = 0.0, range_hi = 0.0;
+  /// The views given to KNNFlat will carry the decimal6 integer form (DatasetView::attrs_i32):
+  /// lets Prepare size the device staging buffers before the first call.
+  bool wire_i32 = false;
   static EngineConfig from_env();
 };
 

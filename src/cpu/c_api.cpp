@@ -152,6 +152,10 @@ int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attr
   });
 }
 
+int dmlp_encode_decimal6_host(const double *values, int64_t count, int threads, int32_t *out, int *ok) {
+  return guarded([&] { *ok = dmlp::encode_decimal6_values(values, count, threads, out) ? 1 : 0; });
+}
+
 int dmlp_parse_update(const char *text, size_t len, int *id, double *attrs, int capacity, int *count) {
   return guarded([&] {
     std::vector<double> v;

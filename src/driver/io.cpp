@@ -28,9 +28,12 @@ void Problem::free_all() {
     if (data_labels) alloc_.release(data_labels);
     if (query_attrs) alloc_.release(query_attrs);
     if (query_k) alloc_.release(query_k);
+    if (data_attrs_i32) alloc_.release(data_attrs_i32);
+    if (query_attrs_i32) alloc_.release(query_attrs_i32);
   }
   data_attrs = query_attrs = nullptr;
   data_labels = query_k = nullptr;
+  data_attrs_i32 = query_attrs_i32 = nullptr;
 }
 
 Problem::Problem(Problem &&o) noexcept { *this = std::move(o); }
@@ -42,8 +45,10 @@ Problem &Problem::operator=(Problem &&o) noexcept {
     num_data = o.num_data; num_queries = o.num_queries; num_attrs = o.num_attrs;
     data_attrs = o.data_attrs; data_labels = o.data_labels;
     query_attrs = o.query_attrs; query_k = o.query_k;
+    data_attrs_i32 = o.data_attrs_i32; query_attrs_i32 = o.query_attrs_i32;
     o.data_attrs = o.query_attrs = nullptr;
     o.data_labels = o.query_k = nullptr;
+    o.data_attrs_i32 = o.query_attrs_i32 = nullptr;
     o.num_data = o.num_queries = 0; o.num_attrs = 0;
   }
   return *this;
@@ -188,6 +193,55 @@ void read_problem(std::FILE *f, int threads, Problem *out) {
     used += got;
   }
   parse_problem(buf.data(), used, threads, out);
+}
+
+bool encode_decimal6_values(const double *v, int64_t n, int threads, int32_t *out) {
+  if (threads <= 0) threads = int(std::thread::hardware_concurrency());
+  if (threads < 1) threads = 1;
+  if (n < (1 << 16)) threads = 1;
+  std::vector<char> bad(size_t(threads), 0);
+  auto work = [&](int t) {
+    for (int64_t i = n * t / threads, e = n * (t + 1) / threads; i < e; ++i) {
+      const double scaled = v[i] * 1e6;
+      if (!(scaled >= -2147483647.0 && scaled <= 2147483647.0)) { bad[size_t(t)] = 1; return; }   // (also rejects NaN)
+      const long long k = std::llrint(scaled);
+      // the device rebuilds the correctly rounded quotient k / 1e6: it must be this very double
+      // (-0.0 comes back as +0.0: no difference or square can tell them apart)
+      if (static_cast<double>(k) / 1e6 != v[i]) { bad[size_t(t)] = 1; return; }
+      out[i] = static_cast<int32_t>(k);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; ++t) pool.emplace_back(work, t);
+  work(0);
+  for (auto &th : pool) th.join();
+  for (char b : bad)
+    if (b) return false;
+  return true;
+}
+
+bool Problem::encode_decimal6(int threads) {
+  if (alloc_.release) {
+    if (data_attrs_i32) alloc_.release(data_attrs_i32);
+    if (query_attrs_i32) alloc_.release(query_attrs_i32);
+  }
+  data_attrs_i32 = query_attrs_i32 = nullptr;
+  const int64_t nd = num_data * num_attrs, nq = num_queries * num_attrs;
+  if (nd + nq == 0) return false;
+  int32_t *xi = static_cast<int32_t *>(alloc_.alloc(sizeof(int32_t) * size_t(nd > 0 ? nd : 1)));
+  int32_t *qi = static_cast<int32_t *>(alloc_.alloc(sizeof(int32_t) * size_t(nq > 0 ? nq : 1)));
+  const bool ok = xi != nullptr && qi != nullptr && encode_decimal6_values(data_attrs, nd, threads, xi) &&
+                  encode_decimal6_values(query_attrs, nq, threads, qi);
+  if (!ok) {
+    if (alloc_.release) {
+      if (xi) alloc_.release(xi);
+      if (qi) alloc_.release(qi);
+    }
+    return false;
+  }
+  data_attrs_i32 = xi;
+  query_attrs_i32 = qi;
+  return true;
 }
 
 void value_range(const Problem &p, int threads, double *lo, double *hi) {

@@ -78,6 +78,9 @@ int main(int argc, char **argv) {
       eng.config.have_range = true;
       eng.config.range_lo = lo;
       eng.config.range_hi = hi;
+      // the six-decimal values as integers: half the bytes over PCIe (DMLP_WIRE_I32=0 keeps doubles)
+      const char *w = std::getenv("DMLP_WIRE_I32");
+      if (w == nullptr || std::string(w) != "0") eng.config.wire_i32 = prob.encode_decimal6(eng.config.cpu.threads);
       eng.Prepare(params, kmax);
     }
     auto t_prep1 = std::chrono::steady_clock::now();

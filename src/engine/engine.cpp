@@ -77,6 +77,7 @@ void Engine::KNNFlat(const DatasetView &data, const QueryView &queries, ResultSe
     go.have_range = config.have_range;
     go.range_lo = config.range_lo;
     go.range_hi = config.range_hi;
+    go.wire_i32 = data.attrs_i32 != nullptr && queries.attrs_i32 != nullptr;
     gpu::knn_gpu(data, queries, go, rs, &last_backend);
   }
 
@@ -105,6 +106,7 @@ void Engine::Prepare(const Params &p, int kmax) {
   go.rows = config.grid_rows;
   go.cols = config.grid_cols;
   go.exact_only = (config.backend == Backend::kGpuExact);
+  go.wire_i32 = config.wire_i32;
   gpu::prepare(p.num_data, p.num_queries, p.num_attrs, kmax, go);
 }
 

@@ -140,6 +140,7 @@ struct Shape {
   int64_t qs = 0;       // slice stride: queries per owner inside a column (padded to 256 when R > 1)
   int64_t qp = 0;       // R * qs
   bool fused = true;
+  bool wire32 = false;  // inputs cross PCIe as decimal6 integers (views' attrs_i32) and are expanded on the device
 };
 
 struct Layout {
@@ -147,7 +148,7 @@ struct Layout {
   size_t pack_flags = 0, list_flags = 128, done_flags = 256, counters = 384, status = 512, nflag = 516;
   size_t stats = 768, q_stats = 1024;
   size_t x64, labels, xh, xn, xe, q64, k, qh, qn, qe, cand, rr_ws, fix_ws, od, oi, ol, flags, frows, final_label,
-      final_sum, fid, fdist, tile_count, rb_count, total;
+      final_sum, fid, fdist, xw = 0, qw = 0, tile_count, rb_count, total;
   int chunks = 2;
   size_t rr_bytes = 0, fix_bytes = 0;
 };
@@ -192,6 +193,10 @@ Layout make_layout(const Shape &s, int sms) {
   L.final_sum = take(static_cast<size_t>(s.qs) * 8);
   L.fid = take(static_cast<size_t>(s.qs) * km * 4);
   L.fdist = take(static_cast<size_t>(s.qs) * km * 8);
+  if (s.wire32) {   // staging for the int32 form of the attributes (same element offsets as x64 / q64)
+    L.xw = take(n * s.a * 4);
+    L.qw = take(qp * s.a * 4);
+  }
   L.tile_count = take((n / 256 + 2) * 4);
   L.rb_count = take((qp / 128 + 2) * 4);
   L.total = off;
@@ -246,6 +251,7 @@ Plan make_plan(int64_t N, int64_t Q, int a, int kmax, const GpuOptions &opt) {
   const int64_t per = BlockPartition{s.q_max, R}.count(0);
   s.qs = R > 1 ? round_up(std::max<int64_t>(per, 1), 256) : std::max<int64_t>(s.q_max, 1);
   s.qp = s.qs * R;
+  s.wire32 = opt.wire_i32;
   // the fused data-row gather needs the CTA-pair kernel (>= 256 queries per column)
   p.ndev = R * C;
   Runtime &rt = Runtime::get();
@@ -255,8 +261,8 @@ Plan make_plan(int64_t N, int64_t Q, int a, int kmax, const GpuOptions &opt) {
     p.bytes = std::max(p.bytes, p.layout.back().total);
   }
   char buf[160];
-  std::snprintf(buf, sizeof buf, "%dx%d a=%d k=%d n=%lld q=%lld N=%lld Q=%lld f=%d", R, C, a, s.kmax, (long long)s.n_max,
-                (long long)s.qp, (long long)N, (long long)Q, int(s.fused));
+  std::snprintf(buf, sizeof buf, "%dx%d a=%d k=%d n=%lld q=%lld N=%lld Q=%lld f=%d w=%d", R, C, a, s.kmax,
+                (long long)s.n_max, (long long)s.qp, (long long)N, (long long)Q, int(s.fused), int(s.wire32));
   p.key = buf;
   return p;
 }
@@ -337,6 +343,8 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
 
   Plan plan = make_plan(N, Q, a, kmax, opt);
   const Shape &S = plan.shape;
+  if (S.wire32 && (data.attrs_i32 == nullptr || queries.attrs_i32 == nullptr))
+    throw std::runtime_error("gpu: wire_i32 needs attrs_i32 in both views");
   const int R = S.R, C = S.C;
   if (path) {
     char buf[96];
@@ -402,8 +410,22 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
       // -- host -> device: only this device's share
       BlockPartition parts{n, C};   // rows_fused: part c of the shard
       const int64_t pb = rows_fused ? parts.begin(c) : 0, pn = rows_fused ? parts.count(c) : n;
+      // attributes: doubles, or (wire32) the loader's decimal6 integers -- half the bytes -- expanded
+      // on the device into the very doubles the parser produced (dec6_to_double, common.cuh)
+      int *xw = S.wire32 ? at<int>(B, L.xw) : nullptr, *qw = S.wire32 ? at<int>(B, L.qw) : nullptr;
+      auto h2d_attrs = [&](double *dst, int *stage, const double *src64, const int32_t *src32, int64_t rows) {
+        const size_t count = size_t(rows) * size_t(a);
+        if (count == 0) return;
+        if (S.wire32) {
+          CK(cudaMemcpyAsync(stage, src32, sizeof(int32_t) * count, cudaMemcpyHostToDevice, st));
+          check_rc(dmlp_expand_decimal6(stage, dst, int64_t(count), st), "expand_decimal6");
+        } else {
+          CK(cudaMemcpyAsync(dst, src64, sizeof(double) * count, cudaMemcpyHostToDevice, st));
+        }
+      };
       if (pn > 0) {
-        CK(cudaMemcpyAsync(x64 + pb * a, data.attrs + (nb + pb) * a, sizeof(double) * size_t(pn) * a, cudaMemcpyHostToDevice, st));
+        h2d_attrs(x64 + pb * a, xw ? xw + pb * a : nullptr, data.attrs + (nb + pb) * a,
+                  S.wire32 ? data.attrs_i32 + (nb + pb) * a : nullptr, pn);
         CK(cudaMemcpyAsync(xl + pb, data.labels + nb + pb, sizeof(int) * size_t(pn), cudaMemcpyHostToDevice, st));
       }
       if (R > 1) {
@@ -414,12 +436,12 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
           if (S.fused && rr != r) continue;
           const int64_t cnt = sl.count(rr), bg = sl.begin(rr);
           if (cnt == 0) continue;
-          CK(cudaMemcpyAsync(q64 + rr * S.qs * a, queries.attrs + (qcb + bg) * a, sizeof(double) * size_t(cnt) * a,
-                             cudaMemcpyHostToDevice, st));
+          h2d_attrs(q64 + rr * S.qs * a, qw ? qw + rr * S.qs * a : nullptr, queries.attrs + (qcb + bg) * a,
+                    S.wire32 ? queries.attrs_i32 + (qcb + bg) * a : nullptr, cnt);
           CK(cudaMemcpyAsync(qk + rr * S.qs, queries.k + qcb + bg, sizeof(int) * size_t(cnt), cudaMemcpyHostToDevice, st));
         }
       } else if (qc > 0) {
-        CK(cudaMemcpyAsync(q64, queries.attrs + qcb * a, sizeof(double) * size_t(qc) * a, cudaMemcpyHostToDevice, st));
+        h2d_attrs(q64, qw, queries.attrs + qcb * a, S.wire32 ? queries.attrs_i32 + qcb * a : nullptr, qc);
         CK(cudaMemcpyAsync(qk, queries.k + qcb, sizeof(int) * size_t(qc), cudaMemcpyHostToDevice, st));
       }
       CK(cudaMemsetAsync(nflag, 0, sizeof(int), st));

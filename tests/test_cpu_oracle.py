@@ -249,3 +249,20 @@ def test_decimal6_correction_step_equals_division():
         v_exact = Fraction(r) * Fraction(y) + Fraction(v0)
         v = float(v_exact)          # Fraction -> float rounds to nearest even
         assert v == i / 1e6, i
+
+
+def test_host_decimal6_encoding():
+    """The loader's integer form (Problem::encode_decimal6, used by `./engine` to halve its PCIe
+    bytes): exact for generator / text-grammar values, refused for anything else."""
+    data, _, queries, _ = cpu.synth(3000, 50, 37, -100.0, 100.0, 1, 1, 2, seed=3)
+    enc = cpu.encode_decimal6(data)
+    assert enc is not None and enc.dtype == np.int32
+    assert (enc.astype(np.float64) / 1e6 == data).all()
+    assert (enc == np.rint(data * 1e6).astype(np.int64)).all()
+    big = np.random.default_rng(1).integers(-2147483647, 2147483647, size=200000).astype(np.float64) / 1e6
+    enc = cpu.encode_decimal6(big, threads=3)                 # threaded path, the whole int32 range
+    assert enc is not None and (enc.astype(np.float64) / 1e6 == big).all()
+    assert cpu.encode_decimal6(np.array([0.0, -0.0, 1.5])) is not None     # -0.0 travels as 0
+    assert cpu.encode_decimal6(np.array([0.1234567])) is None               # seven decimals
+    assert cpu.encode_decimal6(np.array([1.0, 5000.0])) is None             # 5e9 does not fit
+    assert cpu.encode_decimal6(np.array([np.nan])) is None and cpu.encode_decimal6(np.array([np.inf])) is None
