@@ -14,7 +14,7 @@ LIBDIR  = distributed-machine-learning-project_b200/lib
 
 HOST_CPP   = src/driver/report.cpp src/driver/io.cpp src/engine/engine.cpp src/cpu/cpu_backends.cpp
 KERNEL_CU  = $(wildcard src/kernels/*.cu) $(wildcard src/runtime/*.cu)
-ENGINE_CU  = src/engine/gpu_engine.cu
+ENGINE_CU  = src/engine/gpu_engine.cu src/engine/multicast.cu
 
 HOST_O     = $(HOST_CPP:%.cpp=$(B)/%.o)
 HOST_DBG_O = $(HOST_CPP:%.cpp=$(B)/%.dbg.o)

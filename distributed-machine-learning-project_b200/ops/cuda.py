@@ -363,7 +363,8 @@ def knn_local(q_attrs, k, x_attrs, x_labels, kmax, id_base=0, rng=None, workspac
 
 # ---- struct-based entry points: folded vote, device-side repair, in-kernel K5 signalling --------
 class SignalArgs(C.Structure):
-    _fields_ = [("peer_flags", _vp * 8), ("world", _i), ("rank", _i), ("value", C.c_uint32), ("done_counter", _vp)]
+    _fields_ = [("peer_flags", _vp * 8), ("world", _i), ("rank", _i), ("value", C.c_uint32), ("done_counter", _vp),
+                ("mc_flags", _vp)]   # NVSwitch multicast mapping of the flag arrays (None: one store per peer)
 
 
 class WaitArgs(C.Structure):

@@ -308,6 +308,9 @@ typedef struct dmlp_signal_args {
   int world, rank;
   uint32_t value;
   uint32_t *done_counter;  /* local device word, zero at set-up; counts finished blocks and resets itself */
+  uint32_t *mc_flags;      /* NULL, or the flag array through an NVSwitch multicast mapping that covers every
+                              rank's array (cuMulticast*): the signal is then ONE multimem store that the
+                              switch replicates, instead of `world` stores; peer_flags is not used */
 } dmlp_signal_args;
 
 /* The receiving side of `signal`: the kernel spins (acquire, system scope) until every one of the

@@ -26,14 +26,17 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 #include <cuda_runtime.h>
 
 #include "dmlp/cpu.h"
 #include "dmlp/gpu.h"
+#include "multicast.h"
 #include "dmlp_knn.h"
 
 namespace dmlp {
@@ -118,6 +121,18 @@ class Runtime {
     return dev.arena;
   }
   Device &dev(int d) { return devs_[static_cast<size_t>(d)]; }
+  // NVSwitch multicast pages for the flags of an all-device group (multicast.h); created once per
+  // device count, kept for the life of the process; ->ok is false where multicast is not on offer
+  McPages *mc_pages(int ndev) {
+    std::lock_guard<std::mutex> hold(lock_);
+    auto it = mc_.find(ndev);
+    if (it == mc_.end()) {
+      it = mc_.emplace(ndev, McPages::create(ndev, 4096)).first;
+      if (!it->second.ok && std::getenv("DMLP_TRACE"))
+        std::fprintf(stderr, "[dmlp] NVLS flags off for %d GPUs: %s\n", ndev, it->second.why.c_str());
+    }
+    return &it->second;
+  }
   unsigned next_epoch() { return ++epoch_; }
   // flag words live in the arenas: a re-allocation zeroes them, so epochs restart as well
   unsigned long long generation() const { return generation_; }
@@ -126,6 +141,7 @@ class Runtime {
  private:
   std::mutex lock_;
   std::vector<Device> devs_;
+  std::map<int, McPages> mc_;
   int peers_ = 0;
   unsigned epoch_ = 0;
   unsigned long long generation_ = 0;
@@ -230,6 +246,7 @@ struct Plan {
   int ndev = 1;
   std::vector<Layout> layout;   // one per device (same offsets; SM counts could differ in theory)
   size_t bytes = 0;
+  bool mc = false;              // "tell every peer" goes through NVSwitch multicast pages (one store, replicated)
   std::string key;
 };
 
@@ -260,9 +277,13 @@ Plan make_plan(int64_t N, int64_t Q, int a, int kmax, const GpuOptions &opt) {
     p.layout.push_back(make_layout(s, rt.dev(d).sms));
     p.bytes = std::max(p.bytes, p.layout.back().total);
   }
-  char buf[160];
-  std::snprintf(buf, sizeof buf, "%dx%d a=%d k=%d n=%lld q=%lld N=%lld Q=%lld f=%d w=%d", R, C, a, s.kmax,
-                (long long)s.n_max, (long long)s.qp, (long long)N, (long long)Q, int(s.fused), int(s.wire32));
+  // the signalling groups (a column when R > 1, a row when C > 1) are all devices when the other
+  // dimension is 1: then one multicast object serves them (DMLP_NVLS=0 keeps per-peer stores)
+  const char *nvls = std::getenv("DMLP_NVLS");
+  if (p.ndev > 1 && (R == 1 || C == 1) && !(nvls && std::string(nvls) == "0")) p.mc = rt.mc_pages(p.ndev)->ok;
+  char buf[176];
+  std::snprintf(buf, sizeof buf, "%dx%d a=%d k=%d n=%lld q=%lld N=%lld Q=%lld f=%d w=%d m=%d", R, C, a, s.kmax,
+                (long long)s.n_max, (long long)s.qp, (long long)N, (long long)Q, int(s.fused), int(s.wire32), int(p.mc));
   p.key = buf;
   return p;
 }
@@ -286,6 +307,7 @@ void prepare_plan(const Plan &p) {
       CK(cudaMemset(rt.dev(d).arena, 0, 4096));
       CK(cudaMemset(rt.dev(d).arena + L.tile_count, 0, L.rb_count - L.tile_count));
       CK(cudaMemset(rt.dev(d).arena + L.rb_count, 0, L.total - L.rb_count));
+      if (p.mc) CK(cudaMemset(rt.mc_pages(p.ndev)->local[d], 0, 4096));
       CK(cudaDeviceSynchronize());
     }
     rt.reset_epoch();
@@ -348,7 +370,7 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
   const int R = S.R, C = S.C;
   if (path) {
     char buf[96];
-    std::snprintf(buf, sizeof buf, "gpu:%s R=%d C=%d", S.fused ? "fused" : "exact", R, C);
+    std::snprintf(buf, sizeof buf, "gpu:%s R=%d C=%d%s", S.fused ? "fused" : "exact", R, C, plan.mc ? " nvls" : "");
     *path = buf;
   }
   if (Q == 0) return;
@@ -370,6 +392,9 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
   std::vector<unsigned char *> base(size_t(R) * C);
   for (int d = 0; d < R * C; ++d) base[size_t(d)] = rt.dev(d).arena;
   auto dev_of = [&](int r, int c) { return r * C + c; };
+  // multicast flag pages: list flags at 0, "done reading" flags at 128 (word = rank in the group = device)
+  const McPages *mcp = plan.mc ? rt.mc_pages(plan.ndev) : nullptr;
+  constexpr size_t kMcList = 0, kMcDone = 128;
   // rows_fused: one data shard whose parts are spread over the row and gathered inside the GEMM
   const char *rf_env = std::getenv("DMLP_ROWS_FUSED");   // 0: every device loads the whole shard from the host
   const bool rows_fused = S.fused && R == 1 && C > 1 && qp.count(C - 1) >= 256 && N >= C &&
@@ -455,6 +480,11 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
       dmlp_wait_args w_lists, w_done;
       fill_signal(&sg_lists, col, L.list_flags, R, r, epoch, B, L.counters, 0);
       fill_wait(&w_lists, B, L.list_flags, R, epoch, L.status);
+      if (mcp != nullptr && R > 1) {   // (C == 1: the column is every device)
+        for (int rr = 0; rr < R; ++rr) sg_lists.peer_flags[rr] = mcp->local[dev_of(rr, c)] + kMcList;
+        sg_lists.mc_flags = reinterpret_cast<uint32_t *>(mcp->mc + kMcList);
+        w_lists.flags = reinterpret_cast<const uint32_t *>(mcp->local[d] + kMcList);
+      }
 
       if (!S.fused) {
         // ---- direct fp64 path: whole column's queries against this shard
@@ -497,6 +527,11 @@ void knn_gpu(const DatasetView &data, const QueryView &queries, const GpuOptions
           fill_signal(&sg_pack, row, L.pack_flags, C, c, epoch, B, L.counters, 1);
           fill_signal(&sg_done, row, L.done_flags, C, c, epoch, B, L.counters, 2);
           fill_wait(&w_done, B, L.done_flags, C, epoch - 1, L.status);
+          if (mcp != nullptr) {   // (R == 1: the row is every device)
+            for (int cc = 0; cc < C; ++cc) sg_done.peer_flags[cc] = mcp->local[dev_of(r, cc)] + kMcDone;
+            sg_done.mc_flags = reinterpret_cast<uint32_t *>(mcp->mc + kMcDone);
+            w_done.flags = reinterpret_cast<const uint32_t *>(mcp->local[d] + kMcDone);
+          }
           check_rc(dmlp_pack_ex(x64 + pb * a, pn, a, S.a_pad, stats, static_cast<unsigned char *>(xh) + size_t(pb) * S.a_pad * 2,
                                 xn + pb, xe + pb, nullptr, &w_done, &sg_pack, st), "pack(x part)");
           check_rc(dmlp_pack(q64, qc, a, S.a_pad, stats, qh, qn, qe, q_stats, st), "pack(q)");

@@ -262,8 +262,11 @@ __device__ __forceinline__ void signal_peers_when_grid_done(const SignalT &sg) {
     if (prev == blocks - 1) {  // the last block of the launch
       *sg.done_counter = 0;    // ready for the next launch on this stream
       __threadfence_system();
-      for (int d = 0; d < sg.world; ++d)
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sg.peer_flags[d] + sg.rank), "r"(sg.value) : "memory");
+      if (sg.mc_flags != nullptr)   // NVLS: the switch replicates the store into every rank's flag array
+        asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(sg.mc_flags + sg.rank), "r"(sg.value) : "memory");
+      else
+        for (int d = 0; d < sg.world; ++d)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sg.peer_flags[d] + sg.rank), "r"(sg.value) : "memory");
     }
   }
 }

@@ -96,6 +96,7 @@ struct SignalArgs {
   int world = 0, rank = 0;
   unsigned value = 0;
   unsigned *done_counter = nullptr;
+  unsigned *mc_flags = nullptr;  ///< multicast mapping of the flag arrays (NVLS): one multimem store reaches every rank
 };
 /// "Do not start before the peers have told us": every block spins (acquire, system scope) until
 /// each of the `world` words of the local flag array has reached `value`; a wait that exceeds

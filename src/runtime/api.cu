@@ -52,6 +52,7 @@ int fill_signal(const dmlp_signal_args *sg, SignalArgs *out) {
   if (sg == nullptr || sg->world <= 0) return 0;
   DMLP_REQUIRE(sg->world <= kMaxPeers && sg->done_counter != nullptr, "signal: world must be in [1, 8] and done_counter set");
   out->world = sg->world; out->rank = sg->rank; out->value = sg->value; out->done_counter = sg->done_counter;
+  out->mc_flags = sg->mc_flags;
   for (int i = 0; i < sg->world; ++i) out->peer_flags[i] = static_cast<unsigned *>(sg->peer_flags[i]);
   return 0;
 }

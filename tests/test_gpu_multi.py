@@ -103,21 +103,32 @@ def test_distributed_large_k(tmp_path, repo_root):
 
 
 def test_engine_binary_device_grids(tmp_path, repo_root):
-    """The C++ driver (`engine`, one process for all GPUs) on R x C device grids vs its CPU backend."""
+    """The C++ driver (`engine`, one process for all GPUs) on R x C device grids vs its CPU backend.
+    Where the box offers NVSwitch multicast, the R x 1 and 1 x C layouts signal through multicast
+    flag pages (one multimem store per hand-shake, backend string "... nvls"); DMLP_NVLS=0 keeps
+    the per-peer stores.  Both must print the CPU backend's lines."""
     import hashlib
+    import json
     n_gpu = torch.cuda.device_count()
     if n_gpu < 2:
         pytest.skip("needs at least 2 GPUs")
     exe = os.path.join(repo_root, "engine")
-    args = ["--synth", "30000", "900", "48", "-100", "100", "1", "20", "7", "5"]
+    args = ["--json", "--synth", "30000", "900", "48", "-100", "100", "1", "20", "7", "5"]
 
     def run(env_extra):
         res = subprocess.run([exe, *args], capture_output=True, text=True, env=dict(os.environ, **env_extra), timeout=240)
         assert res.returncode == 0, res.stderr[-2000:]
-        return hashlib.md5("".join(sorted(res.stdout.splitlines(True))).encode()).hexdigest()
+        info = json.loads([ln for ln in res.stderr.splitlines() if ln.startswith("{")][-1])
+        return hashlib.md5("".join(sorted(res.stdout.splitlines(True))).encode()).hexdigest(), info["backend"]
 
-    want = run({"DMLP_BACKEND": "cpu"})
+    want, _ = run({"DMLP_BACKEND": "cpu"})
     grids = [f"{n_gpu}x1", f"1x{n_gpu}"] + ([f"2x{n_gpu // 2}"] if n_gpu >= 4 else [])
+    backends = []
     for g in grids:
-        assert run({"DMLP_BACKEND": "gpu", "DMLP_GRID": g}) == want, g
-    assert run({"DMLP_BACKEND": "gpu_exact", "DMLP_GRID": f"{n_gpu}x1"}) == want
+        for nvls in ("1", "0"):
+            got, backend = run({"DMLP_BACKEND": "gpu", "DMLP_GRID": g, "DMLP_NVLS": nvls, "DMLP_TRACE": "1"})
+            assert got == want, (g, nvls, backend)
+            assert nvls == "1" or "nvls" not in backend
+            backends.append(backend)
+    print("engine backends:", backends)
+    assert run({"DMLP_BACKEND": "gpu_exact", "DMLP_GRID": f"{n_gpu}x1"})[0] == want
