@@ -142,6 +142,41 @@ def encode_decimal6(values, threads=0):
     return out if ok.value else None
 
 
+_u32 = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+
+
+def decimal6_bits(values_i32):
+    """Smallest field width (bits per value) of the bit-packed wire format for these integers."""
+    v = np.ascontiguousarray(values_i32, dtype=np.int32)
+    bits = C.c_int(0)
+    lib = _lib()
+    lib.dmlp_decimal6_bits_host.argtypes = [_i, C.c_int64, C.POINTER(C.c_int)]
+    _check(lib.dmlp_decimal6_bits_host(v.reshape(-1), v.size, C.byref(bits)))
+    return bits.value
+
+
+def pack_bits(rows_i32, bits):
+    """int32 [rows, a] -> uint32 [rows, ceil(a * bits / 32)]: the host side of K.pack_bits / K.unpack_bits."""
+    v = np.ascontiguousarray(rows_i32, dtype=np.int32)
+    rows, a = v.shape
+    words = (a * bits + 31) // 32
+    out = np.empty((rows, words), np.uint32)
+    lib = _lib()
+    lib.dmlp_pack_bits_host.argtypes = [_i, C.c_int64, C.c_int, C.c_int, C.c_int, _u32]
+    _check(lib.dmlp_pack_bits_host(v.reshape(-1), rows, a, bits, words, out.reshape(-1)))
+    return out
+
+
+def unpack_bits(words_u32, a, bits):
+    w = np.ascontiguousarray(words_u32, dtype=np.uint32)
+    rows, words = w.shape
+    out = np.empty((rows, a), np.int32)
+    lib = _lib()
+    lib.dmlp_unpack_bits_host.argtypes = [_u32, C.c_int64, C.c_int, C.c_int, C.c_int, _i]
+    _check(lib.dmlp_unpack_bits_host(w.reshape(-1), rows, a, bits, words, out.reshape(-1)))
+    return out
+
+
 def parse_update(line, max_attrs=1 << 16):
     """Parse one update record 'id v0 v1 ...' (reference: common.cpp:46-55).  Returns (id, values)."""
     if isinstance(line, str):

@@ -122,6 +122,14 @@ inline double synth_attr(uint64_t h, double lo, double hi) {
 /// false when some value is not such a quotient or does not fit 32 bits (`out` is then undefined).
 bool encode_decimal6_values(const double *values, int64_t count, int threads, int32_t *out);
 
+/// Bit-packed decimal6 wire format (the device side is dmlp_pack_bits / dmlp_unpack_bits,
+/// src/kernels/pack.cu): value i travels as the `bits`-bit number i + 2^(bits-1), a row of `a`
+/// values is a little-endian bit stream padded to `words` 32-bit words.  decimal6_bits: the
+/// smallest width that holds every value (values in [-100, 100] need 28).
+int decimal6_bits(const int32_t *values, int64_t count);
+void pack_bits_rows(const int32_t *src, int64_t rows, int a, int bits, int words, uint32_t *dst);
+void unpack_bits_rows(const uint32_t *src, int64_t rows, int a, int bits, int words, int32_t *dst);
+
 /// Smallest and largest attribute value over data and queries (threads <= 0: hardware
 /// concurrency); 0, 0 for an empty problem.
 void value_range(const Problem &p, int threads, double *lo, double *hi);

@@ -52,6 +52,12 @@ int dmlp_parse_text(const char *text, size_t len, int threads, double *data_attr
  * *ok = 1 when every value equals double(out[i]) / 1e6 exactly (then a GPU backend can move 4
  * bytes per value over PCIe and rebuild the doubles bit for bit), 0 otherwise. */
 int dmlp_encode_decimal6_host(const double *values, int64_t count, int threads, int32_t *out, int *ok);
+/* The bit-packed form of those integers, as a host loader produces it (the device side is
+ * dmlp_pack_bits / dmlp_unpack_bits in dmlp_knn.h): `bits` per value (dmlp_decimal6_bits_host: the
+ * smallest width for a set of values), rows padded to `words` >= ceil(a * bits / 32) 32-bit words. */
+int dmlp_decimal6_bits_host(const int32_t *values, int64_t count, int *bits);
+int dmlp_pack_bits_host(const int32_t *src, int64_t rows, int a, int bits, int words, uint32_t *dst);
+int dmlp_unpack_bits_host(const uint32_t *src, int64_t rows, int a, int bits, int words, int32_t *dst);
 
 /* One update record "id v0 v1 ..." (reference: parse_update, common.cpp:46-55; unused by its
  * engine).  *count receives the number of values found; at most `capacity` are stored. */

@@ -156,6 +156,18 @@ int dmlp_encode_decimal6_host(const double *values, int64_t count, int threads, 
   return guarded([&] { *ok = dmlp::encode_decimal6_values(values, count, threads, out) ? 1 : 0; });
 }
 
+int dmlp_decimal6_bits_host(const int32_t *values, int64_t count, int *bits) {
+  return guarded([&] { *bits = dmlp::decimal6_bits(values, count); });
+}
+
+int dmlp_pack_bits_host(const int32_t *src, int64_t rows, int a, int bits, int words, uint32_t *dst) {
+  return guarded([&] { dmlp::pack_bits_rows(src, rows, a, bits, words, dst); });
+}
+
+int dmlp_unpack_bits_host(const uint32_t *src, int64_t rows, int a, int bits, int words, int32_t *dst) {
+  return guarded([&] { dmlp::unpack_bits_rows(src, rows, a, bits, words, dst); });
+}
+
 int dmlp_parse_update(const char *text, size_t len, int *id, double *attrs, int capacity, int *count) {
   return guarded([&] {
     std::vector<double> v;

@@ -220,6 +220,58 @@ bool encode_decimal6_values(const double *v, int64_t n, int threads, int32_t *ou
   return true;
 }
 
+int decimal6_bits(const int32_t *v, int64_t n) {
+  long long big = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const long long m = v[i] < 0 ? -static_cast<long long>(v[i]) : v[i];
+    big = m > big ? m : big;
+  }
+  int bits = 2;   // i + 2^(bits-1) must fit `bits` bits: bits = bit_length(max |i|) + 1
+  while (bits < 32 && (1LL << (bits - 1)) <= big) ++bits;
+  return bits;
+}
+
+void pack_bits_rows(const int32_t *src, int64_t rows, int a, int bits, int words, uint32_t *dst) {
+  if (bits < 2 || bits > 32 || static_cast<long long>(words) * 32 < static_cast<long long>(a) * bits)
+    throw std::invalid_argument("pack_bits: bits must be in [2, 32] and the row must fit its words");
+  const uint64_t mask = bits == 32 ? 0xFFFFFFFFULL : ((1ULL << bits) - 1ULL);
+  const uint32_t bias = 1u << (bits - 1);
+  for (int64_t r = 0; r < rows; ++r) {
+    const int32_t *row = src + r * a;
+    uint32_t *out = dst + r * words;
+    for (int w = 0; w < words; ++w) out[w] = 0;
+    uint64_t acc = 0;      // bits not yet written, little end first
+    int have = 0, w = 0;
+    for (int c = 0; c < a; ++c) {
+      acc |= ((static_cast<uint64_t>(static_cast<uint32_t>(row[c]) + bias)) & mask) << have;
+      have += bits;
+      while (have >= 32) {
+        out[w++] = static_cast<uint32_t>(acc);
+        acc >>= 32;
+        have -= 32;
+      }
+    }
+    if (have > 0) out[w] = static_cast<uint32_t>(acc);
+  }
+}
+
+void unpack_bits_rows(const uint32_t *src, int64_t rows, int a, int bits, int words, int32_t *dst) {
+  if (bits < 2 || bits > 32 || static_cast<long long>(words) * 32 < static_cast<long long>(a) * bits)
+    throw std::invalid_argument("unpack_bits: bits must be in [2, 32] and the row must fit its words");
+  const uint64_t mask = bits == 32 ? 0xFFFFFFFFULL : ((1ULL << bits) - 1ULL);
+  const uint32_t bias = 1u << (bits - 1);
+  for (int64_t r = 0; r < rows; ++r) {
+    const uint32_t *row = src + r * words;
+    for (int c = 0; c < a; ++c) {
+      const long long off = static_cast<long long>(c) * bits;
+      const int w = static_cast<int>(off >> 5), sh = static_cast<int>(off & 31);
+      uint64_t v = row[w];
+      if (sh + bits > 32) v |= static_cast<uint64_t>(row[w + 1]) << 32;
+      dst[r * a + c] = static_cast<int32_t>(static_cast<uint32_t>((v >> sh) & mask) - bias);
+    }
+  }
+}
+
 bool Problem::encode_decimal6(int threads) {
   if (alloc_.release) {
     if (data_attrs_i32) alloc_.release(data_attrs_i32);

@@ -266,3 +266,30 @@ def test_host_decimal6_encoding():
     assert cpu.encode_decimal6(np.array([0.1234567])) is None               # seven decimals
     assert cpu.encode_decimal6(np.array([1.0, 5000.0])) is None             # 5e9 does not fit
     assert cpu.encode_decimal6(np.array([np.nan])) is None and cpu.encode_decimal6(np.array([np.inf])) is None
+
+
+@pytest.mark.parametrize("a,bits", [(64, 28), (33, 28), (5, 9), (100, 31), (7, 2), (64, 32), (1, 17)])
+def test_host_bit_packing_matches_the_wire_format(a, bits):
+    """Host twin of the device's pack_bits / unpack_bits: value i travels as the `bits`-bit number
+    i + 2^(bits-1), rows are little-endian bit streams padded to whole 32-bit words."""
+    rng = np.random.default_rng(a * 100 + bits)
+    half = 1 << (bits - 1)
+    vals = rng.integers(-half, half, size=(57, a), dtype=np.int64)
+    vals[0, :] = -half
+    vals[1, :] = half - 1
+    v32 = vals.astype(np.int32)
+    words = cpu.pack_bits(v32, bits)
+    assert words.shape == (57, (a * bits + 31) // 32)
+    u = (vals + half).astype(object)
+    for r in (0, 1, 2, 30, 56):
+        stream = 0
+        for c in range(a):
+            stream |= int(u[r, c]) << (c * bits)
+        expect = [(stream >> (32 * w)) & 0xFFFFFFFF for w in range(words.shape[1])]
+        assert words[r].tolist() == expect, r
+    assert (cpu.unpack_bits(words, a, bits) == v32).all()
+    if bits < 32:    # the width rule is symmetric: bit_length(max |i|) + 1 (so -2^(bits-1) itself asks for one more)
+        assert cpu.decimal6_bits(np.maximum(v32, -(half - 1))) == bits
+        assert cpu.decimal6_bits(v32) == bits + 1
+    data, *_ = cpu.synth(200, 1, 16, -100.0, 100.0, 1, 1, 2, seed=5)
+    assert cpu.decimal6_bits(cpu.encode_decimal6(data)) == 28   # [-100, 100] with six decimals
