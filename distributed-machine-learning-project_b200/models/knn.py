@@ -3,8 +3,9 @@
 ``KNNClassifier`` runs the whole reference job on one B200: host (pinned)
 arrays -> async H2D -> pack -> tcgen05 filter GEMM with fused top-k -> exact
 fp64 re-rank -> vote + checksum -> D2H.  Queries the filter cannot certify, and
-problems outside the fused path's envelope (k > 96, tiny shapes), run on the
-direct fp64 kernel instead; the answer is bit-identical either way.
+problems outside the fused path's envelope (k > 1024, k above ~3 % of the data, tiny
+shapes: ``K.fused_supported``), run on the direct fp64 kernel instead; the answer is
+bit-identical either way.
 """
 from dataclasses import dataclass
 
