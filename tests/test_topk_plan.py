@@ -182,3 +182,30 @@ def test_large_k_plans_split_the_data_into_parts(q, n, a_pad, kmax, parts):
     chunks = arr[3]
     assert chunks % parts == 0 and chunks * 8 >= kmax and chunks // parts <= 64
     assert arr[1] == -(-n // 256) and arr[5] <= SMS
+
+
+def test_routing_rule_and_planner_agree():
+    """Wherever dmlp_fused_supported sends a k to the filter path, the planner gives it at least one
+    32-key list per 8 of k -- for any row length (one or two sets of epilogue warps, wide tile)."""
+    lib = _lib()
+    lib.dmlp_fused_supported.argtypes = [C.c_int, C.c_int64]
+    arr = (C.c_int * 16)()
+    checked = 0
+    for kmax in (1, 8, 16, 96, 97, 128, 200, 256, 257, 300, 512, 513, 777, 1000, 1024):
+        for n in (256, 4000, 8192, 16129, 20000, 32513, 70000, 300000):
+            level = lib.dmlp_fused_supported(kmax, n)
+            if level == 0:
+                assert kmax > 96
+                continue
+            assert level == (2 if kmax <= 96 else 1)
+            if kmax <= 96:
+                continue          # (small k: the planner clamps to the tiles there are; the certificate flags what overflows)
+            for a_pad in (64, 128, 1024, 8192):
+                assert lib.dmlp_topk_plan_ex(2000, n, a_pad, SMS, kmax, C.byref(arr)) == 0
+                lists, halves, parts, chunks = arr[3], arr[8], arr[9], arr[10]
+                assert lists == chunks * halves * parts
+                assert lists * 8 >= kmax, (kmax, n, a_pad, lists)
+                assert chunks <= 32 and chunks * parts <= -(-n // 256)      # a list needs a tile of its own
+                checked += 1
+    assert checked > 100
+    assert lib.dmlp_fused_supported(1025, 10 ** 9) == 0 and lib.dmlp_fused_supported(0, 100) == 0
