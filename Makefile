@@ -96,3 +96,11 @@ asan: engine.asan
 TOOL ?= memcheck
 sanitize-gpu: libs
 	compute-sanitizer --tool $(TOOL) --error-exitcode 9 python3 scripts/sanitize_case.py
+
+# ---- examples: plain C against the C ABI (needs `make libs`) -----------------------------------
+CUDA_HOME ?= /usr/local/cuda
+examples: examples/knn_local
+examples/knn_local: examples/knn_local.c include/dmlp_knn.h $(LIBDIR)/libdmlp_knn.so
+	$(CC) -std=c99 -O2 -Wall -Wextra -Iinclude -I$(CUDA_HOME)/include $< -o $@ \
+	    -L$(LIBDIR) -ldmlp_knn -L$(CUDA_HOME)/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)' -Wl,-rpath,$(CUDA_HOME)/lib64
+.PHONY: examples
